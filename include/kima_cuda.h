@@ -1,0 +1,208 @@
+/*
+ * libkima_cuda — C ABI of the B200-native batched likelihood engine for kima.
+ *
+ * This is the drop-in boundary of the hot path: the reference evaluates one
+ * particle at a time through three private RVmodel methods,
+ *
+ *     RVmodel::calculate_mu()    /root/reference/src/RVmodel.cpp:286-395
+ *     RVmodel::calculate_C()     /root/reference/src/RVmodel.cpp:170-216 (standard kernel)
+ *     RVmodel::log_likelihood()  /root/reference/src/RVmodel.cpp:827-943
+ *     kepler::kepler / true_anomaly                 src/RVmodel.cpp:1422-1475
+ *
+ * reading its inputs from the Data singleton (src/Data.h:52-108).  Here the
+ * same three steps run for a whole batch of particles ("lanes") per call.
+ * Plain C: pointers and sizes only, int status codes, no exceptions.
+ *
+ * Threading: one kc_ctx per GPU.  A context is single-caller (the sampler's
+ * step loop); different contexts may be used from different threads.
+ */
+#ifndef KIMA_CUDA_H
+#define KIMA_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KC_OK 0
+#define KC_ERR_ARG 1      /* bad argument / call order                        */
+#define KC_ERR_CUDA 2     /* CUDA runtime failure (see kc_last_error)         */
+#define KC_ERR_UNSUPPORTED 3 /* MA=true or kernel=celerite: out of scope      */
+#define KC_ERR_COMM 4     /* NCCL failure                                     */
+
+#define KC_MAX_NPMAX 32   /* planets per particle held in shared memory       */
+#define KC_MAX_KO 8
+#define KC_MAX_INST 16
+#define KC_MAX_IND 8
+
+typedef struct kc_ctx kc_ctx;
+
+/* The compile-time model flags of a kima_setup.cpp (src/RVmodel.h:16-34,
+ * src/RVConditionalPrior.h:11) plus npmax (RVmodel ctor).  They are link-time
+ * constants in the reference; the host shim reads them once and passes them
+ * here. */
+typedef struct kc_model_flags {
+    int32_t GP;               /* extern const bool GP                         */
+    int32_t MA;               /* must be 0 (out of scope)          */
+    int32_t hyperpriors;      /* P row holds log(P): P = exp(c[0]) (:357-360) */
+    int32_t trend;
+    int32_t degree;           /* 0..3                                         */
+    int32_t multi_instrument;
+    int32_t known_object;
+    int32_t n_known_object;
+    int32_t studentt;
+    int32_t npmax;            /* max planets per particle                     */
+    int32_t kernel;           /* 0 = standard QP (only one supported)         */
+} kc_model_flags;
+
+/* Row map of the SoA parameter block params[n_rows][ld] (ld >= B, column b
+ * is lane b).  A row index of -1 means "group absent for these flags". */
+typedef struct kc_layout {
+    int32_t n_rows;
+    int32_t npmax;
+    int32_t row_P;     /* npmax rows: components[j][0] (P, or log P if hyperpriors) */
+    int32_t row_K;     /* npmax rows: components[j][1]                       */
+    int32_t row_phi;   /* npmax rows: components[j][2]                       */
+    int32_t row_ecc;   /* npmax rows: components[j][3]                       */
+    int32_t row_w;     /* npmax rows: components[j][4]                       */
+    int32_t row_vsys;  /* background                                         */
+    int32_t n_jit;     /* 1 (extra_sigma) or number_instruments (jitters)    */
+    int32_t row_jit;
+    int32_t n_off;     /* number_instruments-1 if multi_instrument else 0    */
+    int32_t row_off;
+    int32_t row_trend; /* 3 rows slope,quadr,cubic if trend else -1          */
+    int32_t n_beta;    /* number_indicators                                  */
+    int32_t row_beta;
+    int32_t row_eta;   /* 4 rows eta1..eta4 if GP else -1                    */
+    int32_t row_nu;    /* 1 row if studentt else -1                          */
+    int32_t n_ko;
+    int32_t row_KO_P, row_KO_K, row_KO_e, row_KO_phi, row_KO_w; /* n_ko rows each */
+} kc_layout;
+
+/* Pure function of the flags and the data shape; shared by the library, the
+ * host mirror, the oracle and the reference harness so they cannot drift. */
+static inline void kc_layout_from_flags(const kc_model_flags* f, int n_inst,
+                                        int n_ind, kc_layout* L)
+{
+    int r = 0;
+    L->npmax = f->npmax;
+    L->row_P = r;   r += f->npmax;
+    L->row_K = r;   r += f->npmax;
+    L->row_phi = r; r += f->npmax;
+    L->row_ecc = r; r += f->npmax;
+    L->row_w = r;   r += f->npmax;
+    L->row_vsys = r; r += 1;
+    L->n_jit = f->multi_instrument ? n_inst : 1;
+    L->row_jit = r; r += L->n_jit;
+    L->n_off = f->multi_instrument ? (n_inst - 1) : 0;
+    L->row_off = L->n_off ? r : -1; r += L->n_off;
+    L->row_trend = f->trend ? r : -1; r += f->trend ? 3 : 0;
+    L->n_beta = n_ind;
+    L->row_beta = n_ind ? r : -1; r += n_ind;
+    L->row_eta = f->GP ? r : -1; r += f->GP ? 4 : 0;
+    L->row_nu = f->studentt ? r : -1; r += f->studentt ? 1 : 0;
+    L->n_ko = f->known_object ? f->n_known_object : 0;
+    L->row_KO_P = L->n_ko ? r : -1;   r += L->n_ko;
+    L->row_KO_K = L->n_ko ? r : -1;   r += L->n_ko;
+    L->row_KO_e = L->n_ko ? r : -1;   r += L->n_ko;
+    L->row_KO_phi = L->n_ko ? r : -1; r += L->n_ko;
+    L->row_KO_w = L->n_ko ? r : -1;   r += L->n_ko;
+    L->n_rows = r;
+}
+
+/* ---- lifetime ---------------------------------------------------------- */
+int kc_create(int device, kc_ctx** out);
+int kc_destroy(kc_ctx* ctx);
+/* Thread-local message of the last failing call. */
+const char* kc_last_error(void);
+/* Library / build identification, e.g. "kima_cuda 0.1 sm_100a". */
+const char* kc_version(void);
+
+/* ---- data: replaces the per-call Data::get_instance() copies ------------
+ * (src/RVmodel.cpp:173,288,829; getters src/Data.h:52-108).  Called once per
+ * data set; the library copies, the caller keeps ownership.
+ * obsi is 1-based (src/Data.cpp:263-269) and may be NULL when n_inst == 1.
+ * actind is [n_ind][N] row-major, already mean-subtracted (Data.cpp:166-173),
+ * NULL if n_ind == 0.  M0_epoch = t[0] in the reference (Data.cpp:162);
+ * t_middle = Data::get_t_middle() (Data.h:66). */
+int kc_upload_data(kc_ctx* ctx, int N, const double* t, const double* y,
+                   const double* sig, const int32_t* obsi, int n_inst,
+                   int n_ind, const double* actind, double M0_epoch,
+                   double t_middle);
+
+/* ---- model flags + batch capacity --------------------------------------- */
+int kc_configure(kc_ctx* ctx, const kc_model_flags* flags, int max_batch);
+int kc_get_layout(kc_ctx* ctx, kc_layout* out);
+
+/* Pinned host staging block params[n_rows][max_batch] and np[max_batch]
+ * (num_components of each lane's RJObject).  The sampler shim writes lane b's
+ * proposal into column b, then calls kc_eval. */
+int kc_host_params(kc_ctx* ctx, double** params, int32_t** np, int* ld);
+/* The device-resident copies (same shape), for producers that already live on
+ * the GPU and for kc_eval_device. */
+int kc_device_params(kc_ctx* ctx, double** d_params, int32_t** d_np, int* ld);
+
+/* ---- the hot path --------------------------------------------------------
+ * Scores lanes [0,B): replaces calculate_mu -> [calculate_C] -> log_likelihood
+ * for each.  logL follows RVmodel::log_likelihood exactly, including the
+ * non-finite -> +inf rule (src/RVmodel.cpp:938-941); DNest4's LikelihoodType
+ * then maps that to -1e300 (LikelihoodType.cpp:20-21).
+ * kc_eval: H2D of the staged block, kernels, D2H into logL_host, synchronous.
+ * kc_eval_async / kc_wait: same, split so the host can perturb the next
+ * half-batch meanwhile (logL_host must be pinned or will be staged).
+ * kc_eval_device: parameters already in the device block; result stays on the
+ * device (d_logL, B doubles); asynchronous on the context stream. */
+int kc_eval(kc_ctx* ctx, int B, double* logL_host);
+int kc_eval_async(kc_ctx* ctx, int B, double* logL_host);
+int kc_wait(kc_ctx* ctx);
+int kc_eval_device(kc_ctx* ctx, int B, double* d_logL);
+int kc_sync(kc_ctx* ctx);
+/* cudaStream_t of the context, as void*. */
+int kc_stream(kc_ctx* ctx, void** stream);
+
+/* ---- tuning (all have safe defaults) -------------------------------------
+ * kepler_mode: 0 = algebraic true-anomaly form (default, no acos),
+ *              1 = the reference's operation chain (acos + cos(f+w)). */
+int kc_set_option(kc_ctx* ctx, const char* key, int value);
+
+/* ---- instrumentation ---------------------------------------------------- */
+/* Device time (CUDA events on the context stream) of the kernels of the last
+ * evaluation call, and the number of kernel launches since kc_create. */
+int kc_last_kernel_ms(kc_ctx* ctx, float* keplerian_ms, float* gp_ms);
+int64_t kc_launch_count(kc_ctx* ctx);
+/* FP64 peak microbenchmarks run on the context's device: vector DFMA and
+ * tensor DMMA TFLOP/s (best of `reps`). */
+int kc_measure_fp64_peak(kc_ctx* ctx, int reps, double* dfma_tflops,
+                         double* dmma_tflops);
+
+/* ---- test hooks (parity tests call these; not on the hot path) ----------- */
+/* E = kepler::kepler(M, ecc)  (src/RVmodel.cpp:1422-1445), n scalars. */
+int kc_kepler_E(kc_ctx* ctx, int n, const double* M, const double* ecc,
+                double* E);
+/* f = kepler::true_anomaly(t, P, ecc, Tp)  (src/RVmodel.cpp:1457-1475). */
+int kc_true_anomaly(kc_ctx* ctx, int n, const double* t, const double* P,
+                    const double* ecc, const double* Tp, double* f);
+/* mu[N] of lane `lane` of the currently staged host block (calculate_mu). */
+int kc_model_mu(kc_ctx* ctx, int lane, double* mu);
+/* C[N][N] (column-major, full symmetric) of lane `lane` (calculate_C). */
+int kc_gp_cov(kc_ctx* ctx, int lane, double* C);
+
+/* ---- multi-GPU: the level-creation barrier of DNest4 ----------------------
+ * (DNest4/code/SamplerImpl.h:306-329).  One rank per GPU. */
+/* Fills 128 bytes with an NCCL unique id (rank 0 calls, then broadcasts). */
+int kc_comm_unique_id(void* id128);
+int kc_comm_init(kc_ctx* ctx, int rank, int nranks, const void* id128);
+/* Gather every rank's `above` list of (value, tiebreaker) pairs.
+ * pairs: n*2 doubles from this rank; out: capacity max_total*2 doubles,
+ * rank-major; counts[nranks] receives each rank's n. */
+int kc_allgather_above(kc_ctx* ctx, const double* pairs, int n, double* out,
+                       int max_total, int* counts);
+/* Sum the per-level accepts/tries/visits/exceeds deltas over ranks. */
+int kc_allreduce_levels(kc_ctx* ctx, uint64_t* counters, int n);
+int kc_comm_destroy(kc_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KIMA_CUDA_H */
