@@ -1,0 +1,484 @@
+// libkima_cuda: the C ABI (include/kima_cuda.h) over the two kernel families.
+// Context, buffers, copies and launch order only — no arithmetic lives here.
+#include <dlfcn.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "kc_internal.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg)
+{
+    g_err = msg;
+    return code;
+}
+int fail_cuda(cudaError_t e, const char* what)
+{
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return KC_ERR_CUDA;
+}
+#define CU(call)                                                  \
+    do {                                                          \
+        cudaError_t e_ = (call);                                  \
+        if (e_ != cudaSuccess) return fail_cuda(e_, #call);       \
+    } while (0)
+
+}  // namespace
+
+struct kc_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    // data
+    int N = 0, n_inst = 1, n_ind = 0;
+    double M0_epoch = 0, t_middle = 0;
+    double *d_t = nullptr, *d_y = nullptr, *d_sig2 = nullptr, *d_actind = nullptr;
+    int32_t* d_obsi = nullptr;
+    bool have_data = false;
+    // model
+    kc_model_flags F{};
+    kc_layout L{};
+    bool configured = false;
+    int max_batch = 0, ld = 0;
+    double *h_params = nullptr, *d_params = nullptr;
+    int32_t *h_np = nullptr, *d_np = nullptr;
+    double *d_logL = nullptr, *h_logL = nullptr;
+    int* d_counter = nullptr;
+    // GP
+    double* d_resid = nullptr;
+    kc::GpWorkspace gp{nullptr, 0, 0};
+    // options / instrumentation
+    int kepler_mode = 0;
+    int gp_slots_opt = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    float last_ms = 0.f;
+    int64_t launches = 0;
+    double* pending_out = nullptr;
+    int pending_B = 0;
+    // comm
+    void* nccl_lib = nullptr;
+    void* nccl_comm = nullptr;
+    int rank = 0, nranks = 1;
+    void* d_comm_buf = nullptr;
+    size_t comm_buf_bytes = 0;
+};
+
+namespace {
+
+void free_model(kc_ctx* c)
+{
+    if (c->h_params) cudaFreeHost(c->h_params);
+    if (c->h_np) cudaFreeHost(c->h_np);
+    if (c->h_logL) cudaFreeHost(c->h_logL);
+    cudaFree(c->d_params); cudaFree(c->d_np); cudaFree(c->d_logL);
+    cudaFree(c->d_resid); cudaFree(c->gp.ws);
+    c->h_params = nullptr; c->h_np = nullptr; c->h_logL = nullptr;
+    c->d_params = nullptr; c->d_np = nullptr; c->d_logL = nullptr;
+    c->d_resid = nullptr; c->gp = {nullptr, 0, 0};
+    c->configured = false;
+}
+void free_data(kc_ctx* c)
+{
+    cudaFree(c->d_t); cudaFree(c->d_y); cudaFree(c->d_sig2); cudaFree(c->d_actind);
+    cudaFree(c->d_obsi);
+    c->d_t = c->d_y = c->d_sig2 = c->d_actind = nullptr;
+    c->d_obsi = nullptr;
+    c->have_data = false;
+}
+
+kc::KParams make_params(kc_ctx* c, int B, double* d_logL)
+{
+    kc::KParams p{};
+    p.t = c->d_t; p.y = c->d_y; p.sig2 = c->d_sig2; p.obsi = c->d_obsi; p.actind = c->d_actind;
+    p.N = c->N; p.n_inst = c->n_inst; p.n_ind = c->n_ind;
+    p.M0_epoch = c->M0_epoch; p.t_middle = c->t_middle;
+    p.F = c->F; p.L = c->L;
+    p.params = c->d_params; p.np = c->d_np; p.ld = c->ld; p.B = B;
+    p.logL = d_logL; p.resid = c->d_resid; p.counter = c->d_counter;
+    return p;
+}
+
+int run_kernels(kc_ctx* c, int B, double* d_logL)
+{
+    kc::KParams p = make_params(c, B, d_logL);
+    int n = 0;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    cudaError_t e;
+    if (c->F.GP) e = kc::launch_gp(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
+    else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
+    if (e != cudaSuccess) return fail_cuda(e, "kernel launch");
+    CU(cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->launches += n;
+    return KC_OK;
+}
+
+int check_ready(kc_ctx* c, int B)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    if (!c->have_data) return fail(KC_ERR_ARG, "kc_upload_data has not been called");
+    if (!c->configured) return fail(KC_ERR_ARG, "kc_configure has not been called");
+    if (B < 0 || B > c->max_batch) return fail(KC_ERR_ARG, "B outside [0, max_batch]");
+    return KC_OK;
+}
+
+}  // namespace
+
+namespace kc {
+CommView comm_view(kc_ctx* c)
+{
+    return {c->device, c->stream, &c->nccl_lib, &c->nccl_comm, &c->rank, &c->nranks,
+            &c->d_comm_buf, &c->comm_buf_bytes};
+}
+int comm_fail(int code, const std::string& msg) { return fail(code, msg); }
+}  // namespace kc
+
+extern "C" {
+
+const char* kc_last_error(void) { return g_err.c_str(); }
+const char* kc_version(void) { return "kima_cuda 0.1 sm_100a"; }
+
+int kc_create(int device, kc_ctx** out)
+{
+    if (!out) return fail(KC_ERR_ARG, "out is null");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(KC_ERR_CUDA, std::string("no CUDA device: libkima_cuda has no CPU fallback (") +
+                                     cudaGetErrorString(e) + ")");
+    if (device < 0 || device >= ndev) return fail(KC_ERR_ARG, "device index out of range");
+    CU(cudaSetDevice(device));
+    kc_ctx* c = new kc_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev0));
+    CU(cudaEventCreate(&c->ev1));
+    CU(cudaMalloc(&c->d_counter, 64));
+    *out = c;
+    return KC_OK;
+}
+
+int kc_destroy(kc_ctx* c)
+{
+    if (!c) return KC_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    kc_comm_destroy(c);
+    free_model(c);
+    free_data(c);
+    cudaFree(c->d_counter);
+    cudaFree(c->d_comm_buf);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return KC_OK;
+}
+
+int kc_upload_data(kc_ctx* c, int N, const double* t, const double* y, const double* sig,
+                   const int32_t* obsi, int n_inst, int n_ind, const double* actind,
+                   double M0_epoch, double t_middle)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    if (N <= 0 || !t || !y || !sig) return fail(KC_ERR_ARG, "N <= 0 or null data array");
+    if (n_inst < 1 || n_inst > KC_MAX_INST) return fail(KC_ERR_ARG, "n_inst outside [1, KC_MAX_INST]");
+    if (n_ind < 0 || n_ind > KC_MAX_IND) return fail(KC_ERR_ARG, "n_ind outside [0, KC_MAX_IND]");
+    if (n_ind > 0 && !actind) return fail(KC_ERR_ARG, "n_ind > 0 but actind is null");
+    if (n_inst > 1 && !obsi) return fail(KC_ERR_ARG, "n_inst > 1 but obsi is null");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    free_model(c);  // capacity depends on N
+    free_data(c);
+    std::vector<double> sig2(N);
+    std::vector<int32_t> ob(N);
+    for (int i = 0; i < N; i++) {
+        sig2[i] = sig[i] * sig[i];  // the product every reference call forms (:201,:900,:921)
+        ob[i] = obsi ? obsi[i] : 1;
+        if (ob[i] < 1 || ob[i] > n_inst) return fail(KC_ERR_ARG, "obsi must be 1-based ids <= n_inst");
+    }
+    size_t nb = sizeof(double) * N;
+    CU(cudaMalloc(&c->d_t, nb));
+    CU(cudaMalloc(&c->d_y, nb));
+    CU(cudaMalloc(&c->d_sig2, nb));
+    CU(cudaMalloc(&c->d_obsi, sizeof(int32_t) * N));
+    CU(cudaMemcpy(c->d_t, t, nb, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->d_y, y, nb, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->d_sig2, sig2.data(), nb, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->d_obsi, ob.data(), sizeof(int32_t) * N, cudaMemcpyHostToDevice));
+    if (n_ind > 0) {
+        CU(cudaMalloc(&c->d_actind, nb * n_ind));
+        CU(cudaMemcpy(c->d_actind, actind, nb * n_ind, cudaMemcpyHostToDevice));
+    }
+    c->N = N; c->n_inst = n_inst; c->n_ind = n_ind;
+    c->M0_epoch = M0_epoch; c->t_middle = t_middle;
+    c->have_data = true;
+    return KC_OK;
+}
+
+int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
+{
+    if (!c || !f) return fail(KC_ERR_ARG, "null argument");
+    if (!c->have_data) return fail(KC_ERR_ARG, "kc_upload_data must come before kc_configure");
+    if (max_batch < 1) return fail(KC_ERR_ARG, "max_batch < 1");
+    if (f->MA) return fail(KC_ERR_UNSUPPORTED, "MA=true is outside the accelerated path (SURVEY 8f3)");
+    if (f->kernel != 0) return fail(KC_ERR_UNSUPPORTED, "kernel=celerite is outside the accelerated path (SURVEY 8f2)");
+    if (f->npmax < 0 || f->npmax > KC_MAX_NPMAX) return fail(KC_ERR_ARG, "npmax outside [0, KC_MAX_NPMAX]");
+    if (f->known_object && (f->n_known_object < 0 || f->n_known_object > KC_MAX_KO))
+        return fail(KC_ERR_ARG, "n_known_object outside [0, KC_MAX_KO]");
+    if (f->trend && (f->degree < 1 || f->degree > 3))
+        return fail(KC_ERR_ARG, "trend=true needs degree in 1..3 (src/RVmodel.cpp:43-47)");
+    if (f->multi_instrument && c->n_inst < 1) return fail(KC_ERR_ARG, "multi_instrument without instruments");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    free_model(c);
+    c->F = *f;
+    kc_layout_from_flags(f, c->n_inst, c->n_ind, &c->L);
+    c->max_batch = max_batch;
+    c->ld = (max_batch + 3) & ~3;
+    size_t pb = sizeof(double) * (size_t)c->L.n_rows * c->ld;
+    CU(cudaMallocHost(&c->h_params, pb));
+    CU(cudaMallocHost(&c->h_np, sizeof(int32_t) * c->ld));
+    CU(cudaMallocHost(&c->h_logL, sizeof(double) * c->ld));
+    std::memset(c->h_params, 0, pb);
+    std::memset(c->h_np, 0, sizeof(int32_t) * c->ld);
+    CU(cudaMalloc(&c->d_params, pb));
+    CU(cudaMalloc(&c->d_np, sizeof(int32_t) * c->ld));
+    CU(cudaMalloc(&c->d_logL, sizeof(double) * c->ld));
+    CU(cudaMemset(c->d_params, 0, pb));
+    CU(cudaMemset(c->d_np, 0, sizeof(int32_t) * c->ld));
+    if (f->GP) {
+        CU(cudaMalloc(&c->d_resid, sizeof(double) * (size_t)c->ld * c->N));
+        c->gp.slot_doubles = kc::gp_slot_doubles(c->N);
+        int slots = c->gp_slots_opt > 0 ? c->gp_slots_opt : kc::gp_default_slots(c->N, c->sm_count);
+        if (slots > max_batch) slots = max_batch;
+        c->gp.slots = slots;
+        CU(cudaMalloc(&c->gp.ws, sizeof(double) * c->gp.slot_doubles * slots));
+    }
+    c->configured = true;
+    return KC_OK;
+}
+
+int kc_get_layout(kc_ctx* c, kc_layout* out)
+{
+    if (!c || !out) return fail(KC_ERR_ARG, "null argument");
+    if (!c->configured) return fail(KC_ERR_ARG, "kc_configure has not been called");
+    *out = c->L;
+    return KC_OK;
+}
+
+int kc_host_params(kc_ctx* c, double** params, int32_t** np, int* ld)
+{
+    if (!c || !c->configured) return fail(KC_ERR_ARG, "context not configured");
+    if (params) *params = c->h_params;
+    if (np) *np = c->h_np;
+    if (ld) *ld = c->ld;
+    return KC_OK;
+}
+
+int kc_device_params(kc_ctx* c, double** d_params, int32_t** d_np, int* ld)
+{
+    if (!c || !c->configured) return fail(KC_ERR_ARG, "context not configured");
+    if (d_params) *d_params = c->d_params;
+    if (d_np) *d_np = c->d_np;
+    if (ld) *ld = c->ld;
+    return KC_OK;
+}
+
+int kc_eval_async(kc_ctx* c, int B, double* logL_host)
+{
+    int rc = check_ready(c, B);
+    if (rc) return rc;
+    if (!logL_host) return fail(KC_ERR_ARG, "logL_host is null");
+    if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is already in flight");
+    CU(cudaSetDevice(c->device));
+    if (B == 0) return KC_OK;
+    // one strided copy moves columns [0,B) of every row
+    CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
+                         sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_np, c->h_np, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
+    rc = run_kernels(c, B, c->d_logL);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(c->h_logL, c->d_logL, sizeof(double) * B, cudaMemcpyDeviceToHost, c->stream));
+    c->pending_out = logL_host;
+    c->pending_B = B;
+    return KC_OK;
+}
+
+int kc_wait(kc_ctx* c)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->pending_out) {
+        std::memcpy(c->pending_out, c->h_logL, sizeof(double) * c->pending_B);
+        c->pending_out = nullptr;
+        c->pending_B = 0;
+    }
+    return KC_OK;
+}
+
+int kc_eval(kc_ctx* c, int B, double* logL_host)
+{
+    int rc = kc_eval_async(c, B, logL_host);
+    if (rc) return rc;
+    return kc_wait(c);
+}
+
+int kc_eval_device(kc_ctx* c, int B, double* d_logL)
+{
+    int rc = check_ready(c, B);
+    if (rc) return rc;
+    CU(cudaSetDevice(c->device));
+    if (B == 0) return KC_OK;
+    return run_kernels(c, B, d_logL ? d_logL : c->d_logL);
+}
+
+int kc_sync(kc_ctx* c)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    return KC_OK;
+}
+
+int kc_stream(kc_ctx* c, void** stream)
+{
+    if (!c || !stream) return fail(KC_ERR_ARG, "null argument");
+    *stream = (void*)c->stream;
+    return KC_OK;
+}
+
+int kc_set_option(kc_ctx* c, const char* key, int value)
+{
+    if (!c || !key) return fail(KC_ERR_ARG, "null argument");
+    std::string k(key);
+    if (k == "kepler_mode") {
+        if (value != 0 && value != 1) return fail(KC_ERR_ARG, "kepler_mode must be 0 or 1");
+        c->kepler_mode = value;
+    } else if (k == "gp_slots") {
+        if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
+        c->gp_slots_opt = value;  // takes effect at the next kc_configure
+    } else {
+        return fail(KC_ERR_ARG, "unknown option: " + k);
+    }
+    return KC_OK;
+}
+
+int kc_last_kernel_ms(kc_ctx* c, float* keplerian_ms, float* gp_ms)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    if (!c->timed) return fail(KC_ERR_ARG, "no evaluation has been timed yet");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (keplerian_ms) *keplerian_ms = c->F.GP ? 0.f : ms;
+    if (gp_ms) *gp_ms = c->F.GP ? ms : 0.f;
+    return KC_OK;
+}
+
+int64_t kc_launch_count(kc_ctx* c) { return c ? c->launches : 0; }
+
+int kc_measure_fp64_peak(kc_ctx* c, int reps, double* dfma_tflops, double* dmma_tflops)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    CU(cudaSetDevice(c->device));
+    cudaError_t e = kc::measure_fp64_peak(reps, dfma_tflops, dmma_tflops, c->stream);
+    if (e != cudaSuccess) return fail_cuda(e, "measure_fp64_peak");
+    c->launches += 2 * (reps + 1);
+    return KC_OK;
+}
+
+// ---- test hooks ------------------------------------------------------------------------
+static int hook_arrays(kc_ctx* c, int n, int n_in, const double* const* in, double* out, int which)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    if (n <= 0) return KC_OK;
+    CU(cudaSetDevice(c->device));
+    double* d = nullptr;
+    size_t nb = sizeof(double) * n;
+    CU(cudaMalloc(&d, nb * (n_in + 1)));
+    for (int k = 0; k < n_in; k++) CU(cudaMemcpyAsync(d + (size_t)k * n, in[k], nb, cudaMemcpyHostToDevice, c->stream));
+    cudaError_t e;
+    if (which == 0) e = kc::launch_kepler_E(n, d, d + n, d + 2 * (size_t)n, c->stream);
+    else e = kc::launch_true_anomaly(n, d, d + n, d + 2 * (size_t)n, d + 3 * (size_t)n, d + 4 * (size_t)n, c->stream);
+    if (e != cudaSuccess) { cudaFree(d); return fail_cuda(e, "hook launch"); }
+    c->launches += 1;
+    CU(cudaMemcpyAsync(out, d + (size_t)n_in * n, nb, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaFree(d));
+    return KC_OK;
+}
+
+int kc_kepler_E(kc_ctx* c, int n, const double* M, const double* ecc, double* E)
+{
+    const double* in[2] = {M, ecc};
+    return hook_arrays(c, n, 2, in, E, 0);
+}
+
+int kc_true_anomaly(kc_ctx* c, int n, const double* t, const double* P, const double* ecc,
+                    const double* Tp, double* f)
+{
+    const double* in[4] = {t, P, ecc, Tp};
+    return hook_arrays(c, n, 4, in, f, 1);
+}
+
+static int stage_lane(kc_ctx* c, int lane)
+{
+    int rc = check_ready(c, lane + 1);
+    if (rc) return rc;
+    if (lane < 0) return fail(KC_ERR_ARG, "lane < 0");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpy2DAsync(c->d_params + lane, sizeof(double) * c->ld, c->h_params + lane,
+                         sizeof(double) * c->ld, sizeof(double), c->L.n_rows,
+                         cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_np + lane, c->h_np + lane, sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    return KC_OK;
+}
+
+int kc_model_mu(kc_ctx* c, int lane, double* mu)
+{
+    int rc = stage_lane(c, lane);
+    if (rc) return rc;
+    if (!mu) return fail(KC_ERR_ARG, "mu is null");
+    double* d = nullptr;
+    CU(cudaMalloc(&d, sizeof(double) * c->N));
+    kc::KParams p = make_params(c, lane + 1, c->d_logL);
+    cudaError_t e = kc::launch_model_mu(p, c->kepler_mode, lane, d, c->stream);
+    if (e != cudaSuccess) { cudaFree(d); return fail_cuda(e, "model_mu launch"); }
+    c->launches += 1;
+    CU(cudaMemcpyAsync(mu, d, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaFree(d));
+    return KC_OK;
+}
+
+int kc_gp_cov(kc_ctx* c, int lane, double* C)
+{
+    int rc = stage_lane(c, lane);
+    if (rc) return rc;
+    if (!C) return fail(KC_ERR_ARG, "C is null");
+    if (!c->F.GP) return fail(KC_ERR_ARG, "kc_gp_cov needs GP=true");
+    double* d = nullptr;
+    size_t nb = sizeof(double) * (size_t)c->N * c->N;
+    CU(cudaMalloc(&d, nb));
+    kc::KParams p = make_params(c, lane + 1, c->d_logL);
+    cudaError_t e = kc::launch_gp_cov(p, lane, d, c->stream);
+    if (e != cudaSuccess) { cudaFree(d); return fail_cuda(e, "gp_cov launch"); }
+    c->launches += 1;
+    CU(cudaMemcpyAsync(C, d, nb, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaFree(d));
+    return KC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,76 @@
+// Internal declarations shared by the libkima_cuda translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include "../../include/kima_cuda.h"
+
+namespace kc {
+
+constexpr int MAX_PLANETS = KC_MAX_NPMAX + KC_MAX_KO;  // per particle, in shared memory
+constexpr int CTA_THREADS = 256;
+constexpr int CTA_WARPS = CTA_THREADS / 32;
+
+// Everything a kernel needs, passed by value (lives in the constant bank).
+struct KParams {
+    // Data singleton, uploaded once (src/Data.h:14-16)
+    const double* t;
+    const double* y;
+    const double* sig2;     // sig[i]*sig[i], the product the reference forms each call
+    const int32_t* obsi;    // 1-based
+    const double* actind;   // [n_ind][N]
+    int N, n_inst, n_ind;
+    double M0_epoch, t_middle;
+    // model
+    kc_model_flags F;
+    kc_layout L;
+    // batch
+    const double* params;   // [n_rows][ld]
+    const int32_t* np;      // [B]
+    int ld, B;
+    double* logL;           // [B]
+    double* resid;          // [B][N], GP only: y - mu
+    int* counter;           // dynamic work counter (zeroed before launch)
+};
+
+// Launchers (kc_keplerian.cu, kc_gp.cu).  All asynchronous on `stream`.
+cudaError_t launch_keplerian(const KParams& p, int kepler_mode, int sm_count, cudaStream_t stream,
+                             int* n_launches);
+cudaError_t launch_kepler_E(int n, const double* M, const double* e, double* E, cudaStream_t s);
+cudaError_t launch_true_anomaly(int n, const double* t, const double* P, const double* e,
+                                const double* Tp, double* f, cudaStream_t s);
+cudaError_t launch_model_mu(const KParams& p, int kepler_mode, int lane, double* mu, cudaStream_t s);
+
+struct GpWorkspace {
+    double* ws;          // per-slot factor storage
+    size_t slot_doubles; // doubles per slot
+    int slots;
+};
+size_t gp_slot_doubles(int N);
+int gp_default_slots(int N, int sm_count);
+cudaError_t launch_gp(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
+                      cudaStream_t stream, int* n_launches);
+cudaError_t launch_gp_cov(const KParams& p, int lane, double* C, cudaStream_t s);
+
+// The communicator state of a context, as kc_comm.cu sees it.
+struct CommView {
+    int device;
+    cudaStream_t stream;
+    void** nccl_lib;
+    void** nccl_comm;
+    int* rank;
+    int* nranks;
+    void** d_buf;
+    size_t* buf_bytes;
+};
+
+cudaError_t measure_fp64_peak(int reps, double* dfma_tflops, double* dmma_tflops, cudaStream_t s);
+
+}  // namespace kc
+
+struct kc_ctx;
+namespace kc {
+CommView comm_view(kc_ctx* c);                       // kc_api.cu
+int comm_fail(int code, const std::string& msg);     // kc_api.cu
+}  // namespace kc
