@@ -1,0 +1,88 @@
+"""CPU, build container only: the plain-C oracle and the host Data mirror against the
+UNMODIFIED reference (oracle/_ref/libkima_ref.so).  Skipped where /root/reference is
+absent (the GPU box); the committed golden vectors carry the same pin there."""
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+from conftest import relerr
+from kima_b200.data import RVData
+from kima_b200.flags import ModelFlags
+from kima_b200.synthetic import make_data, make_params
+
+EX = "/root/reference/examples"
+
+
+def test_kepler_bit_identical(port, reference):
+    rng = np.random.default_rng(99)
+    M = rng.uniform(-1e3, 1e6, 100000)
+    e = rng.uniform(0, 1, 100000)
+    assert np.array_equal(port.kepler(M, e), reference.kepler(M, e))
+
+
+FLAG_GRID = [
+    ModelFlags(npmax=0),
+    ModelFlags(npmax=4),
+    ModelFlags(npmax=4, hyperpriors=True),
+    ModelFlags(npmax=2, studentt=True),
+    ModelFlags(npmax=2, trend=True, degree=1),
+    ModelFlags(npmax=2, trend=True, degree=3, multi_instrument=True),
+    ModelFlags(npmax=1, known_object=True, n_known_object=3),
+    ModelFlags(npmax=3, studentt=True, multi_instrument=True, hyperpriors=True),
+    ModelFlags(GP=True, npmax=2),
+    ModelFlags(GP=True, npmax=2, multi_instrument=True, trend=True, degree=2),
+]
+
+
+@pytest.mark.parametrize("flags", FLAG_GRID, ids=lambda f: "-".join(
+    k for k in ("GP", "hyperpriors", "trend", "multi_instrument", "known_object", "studentt") if getattr(f, k)) or "plain")
+@pytest.mark.parametrize("shape", [(40, 1, 0), (75, 3, 2)])
+def test_port_matches_reference(port, reference, flags, shape):
+    N, n_inst, n_ind = shape
+    if flags.multi_instrument and n_inst == 1:
+        n_inst = 2
+    d = make_data(N, n_inst, n_ind, seed=N)
+    for o in (port, reference):
+        o.set_rvdata(d)
+        o.set_flags(flags)
+    assert port.layout() == reference.layout()
+    P, nps = make_params(flags, d, 24, "mix", seed=N + 1)
+    a, _ = port.eval_batch(P, nps)
+    b, _ = reference.eval_batch(P, nps)
+    assert relerr(a, b).max() <= (2e-12 if flags.GP else 0.0)
+    assert np.array_equal(port.mu(P, 3, int(nps[3])), reference.mu(P, 3, int(nps[3])))
+    if flags.GP:
+        assert np.array_equal(port.cov(P, 3), reference.cov(P, 3))
+
+
+def _same(d: RVData, r: dict):
+    assert np.array_equal(d.t, r["t"]) and np.array_equal(d.y, r["y"]) and np.array_equal(d.sig, r["sig"])
+    assert d.number_instruments == r["n_inst"] and d.number_indicators == r["n_ind"]
+    if r["n_inst"] > 1:
+        assert np.array_equal(d.obsi, r["obsi"])
+    if r["n_ind"]:
+        np.testing.assert_allclose(d.actind, r["actind"], rtol=0, atol=1e-15)
+    assert d.M0_epoch == r["M0_epoch"] and d.get_t_middle() == r["t_middle"]
+
+
+def test_data_loaders_match_reference(reference):
+    _same(RVData.load(EX + "/51Peg/51Peg.rv", "ms", 0), reference.ref_load(EX + "/51Peg/51Peg.rv", "ms", 0))
+    _same(RVData.load(EX + "/many_planets/HD10180.kms.rv", "kms", 1),
+          reference.ref_load(EX + "/many_planets/HD10180.kms.rv", "kms", 1))
+    _same(RVData.load(EX + "/CoRoT7/corot7.txt", "ms"), reference.ref_load(EX + "/CoRoT7/corot7.txt", "ms", 2))
+    j = EX + "/multi_instrument/HD106252_joined.txt"
+    _same(RVData.load_multi(j, "ms", 1), reference.ref_load_multi(j, "ms", 1))
+    files = [EX + "/multi_instrument/HD106252_%s.txt" % s for s in ("ELODIE", "HET", "HJS", "Lick")]
+    _same(RVData.load_multi(files, "ms", 2), reference.ref_load_multi(files, "ms", 2))
+    # last: Data::load_multi(one file) never clears the singleton's indicator state
+    # (src/Data.cpp:210-284), so an indicator load must not precede it in one process
+    ind = ["b", "", "indc"]
+    _same(RVData.load(EX + "/activity_correlations/simulated2.txt", "ms", 4, ind),
+          reference.ref_load(EX + "/activity_correlations/simulated2.txt", "ms", 4, ind))
+
+
+def test_likelihood_type_rule(port, reference):
+    for v in (float("inf"), float("-inf"), float("nan"), 0.0, -3.25, 1e300):
+        assert port.likelihood_type_value(v) == reference.likelihood_type_value(v)
