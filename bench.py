@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""bench.py — log-likelihood evaluations per second on the BASELINE.json workloads.
+
+    python bench.py --gpus N --steps K --warmup W            # the CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path
+
+Workloads (BASELINE.json `metric`):
+  K  Keplerian, N=1000 epochs, Np=10 planets in every lane, Gaussian white noise
+  G  quasi-periodic GP (dense Cholesky), N=1000 epochs, Np=10
+A "step" scores one batch of lanes (particles) once.  The top-level JSON keys are
+workload K; the same keys for workload G sit under "gp".  One rank per GPU; lanes
+shard with no data-path collective (weak scaling: lanes per GPU fixed).
+
+Timing: per step, the L2 is flushed (untimed), then the step is timed on the device
+with CUDA events on the stream the kernels run on (kc_last_kernel_ms); the K steps
+are bracketed by a barrier + device synchronise and the max over ranks is taken.
+`e2e` times the public call with host buffers (H2D + kernels + D2H) by wall clock.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from kima_b200.flags import ModelFlags, layout_from_flags  # noqa: E402
+from kima_b200.synthetic import make_data, make_params  # noqa: E402
+
+METRIC = "log-likelihood evals/sec: Keplerian (N=1k, Np=10) and QP-GP Cholesky (N=1k)"
+N_EPOCHS = 1000
+NP = 10
+KEP_LANES = 8192          # lanes per GPU, workload K
+GP_LANES = 1184           # lanes per GPU, workload G (8 per SM)
+REF_KEP_LANES = 4096      # bounded sample per step of the CPU arms
+REF_GP_LANES = 48
+
+
+def flops_keplerian(N, Np):
+    """F_K = N (330 Np + 45)."""
+    return N * (330.0 * Np + 45.0)
+
+
+def flops_gp(N, Np):
+    """F_G = N^3/3 + 37 N^2 + F_K."""
+    return N ** 3 / 3.0 + 37.0 * N * N + flops_keplerian(N, Np)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.rows = []
+        self.proc = None
+        self.th = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            return
+
+        def pump():
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        self.th = threading.Thread(target=pump, daemon=True)
+        self.th.start()
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                smax = float(r[2])
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if r[5 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        sm_sorted = sorted(sm)
+        # "under load": the upper half of the samples (idle samples bracket the region)
+        load = sm_sorted[len(sm_sorted) // 2:] if sm_sorted else []
+        return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": smax,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def init_dist(n_gpus: int):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def cpu_arm(kind_pref: str, flags: ModelFlags, data, lanes: int, threads: int, reps: int = 1):
+    """Time the reference's own CPU implementation (oracle/_ref, kind "reference") or,
+    where it was not built, the plain-C restatement (kind "port") on `lanes` lanes."""
+    from oracle.oracle import Oracle, have_reference
+    kind = "reference" if (kind_pref == "reference" and have_reference()) else "port"
+    o = Oracle(kind)
+    o.set_rvdata(data)
+    o.set_flags(flags)
+    P, nps = make_params(flags, data, lanes, "max")
+    best = None
+    for _ in range(reps):
+        _, secs = o.eval_batch(P, nps, threads)
+        best = secs if best is None else min(best, secs)
+    return kind, lanes / best, best
+
+
+def run_workload(eng, lanes: int, steps: int, warmup: int, flops_per_eval: float, peak_tflops: float,
+                 exch, sampler_idx: int):
+    """W warm-up + K timed steps of one workload on this rank's engine."""
+    for _ in range(max(warmup, 3)):
+        eng.flush_l2()
+        eng.log_likelihood_device(lanes)
+    eng.sync()
+    sampler = ClockSampler(sampler_idx)
+    sampler.start()
+    if exch:
+        exch.barrier()
+    n0 = eng.launch_count()
+    dev_ms = []
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        eng.flush_l2()
+        eng.log_likelihood_device(lanes)
+        eng.sync()
+        dev_ms.append(eng.last_kernel_ms())
+    eng.sync()
+    if exch:
+        exch.barrier()
+    wall = time.perf_counter() - t0
+    launches = eng.launch_count() - n0
+    clocks = sampler.stop()
+    total_ms = float(sum(dev_ms))
+    # end to end through the public call, host buffers: H2D + kernels + D2H inside the clock
+    out = np.empty(lanes)
+    eng.log_likelihood(lanes, out)
+    e2e_t = []
+    for _ in range(steps):
+        eng.flush_l2()
+        eng.sync()
+        t1 = time.perf_counter()
+        eng.log_likelihood(lanes, out)
+        e2e_t.append(time.perf_counter() - t1)
+    e2e_s = float(sum(e2e_t))
+    if exch:
+        total_ms = exch.max_float(total_ms)
+        e2e_s = exch.max_float(e2e_s)
+        launches = int(exch.sum_float(float(launches)))
+    world = exch.world if exch else 1
+    ms_per_step = total_ms / steps
+    value = world * lanes / (ms_per_step * 1e-3)
+    per_gpu = lanes / (ms_per_step * 1e-3)
+    achieved = per_gpu * flops_per_eval * 1e-12
+    n_rows = eng.layout["n_rows"]
+    res = {
+        "value": value, "ms_per_step": ms_per_step, "gpu_launches": launches,
+        "e2e": {"value": world * lanes / (e2e_s / steps), "unit": "evals/s",
+                "h2d_bytes_per_step": int(n_rows * lanes * 8 + lanes * 4),
+                "d2h_bytes_per_step": int(lanes * 8)},
+        "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
+                     "frac": achieved / peak_tflops, "traffic": None,
+                     "flops_per_eval": flops_per_eval,
+                     "peak_source": "kc_measure_fp64_peak in this run (max of DFMA / DMMA m8n8k4); "
+                                    "MEASURED_PEAKS.json has no FP64 entry"},
+        "clocks": clocks, "wall_s_timed_region": wall, "finite": bool(np.all(np.isfinite(out))),
+    }
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="kima_b200", choices=["kima_b200", "reference"])
+    ap.add_argument("--kepler-mode", type=int, default=0)
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--workloads", default="kep,gp")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    threads = os.cpu_count() or 1
+    data = make_data(N_EPOCHS)
+    fk = ModelFlags(npmax=NP)
+    fg = ModelFlags(GP=True, npmax=NP)
+    base = {"metric": METRIC, "unit": "evals/s", "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": max(a.warmup, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic"}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        out = dict(base, impl="reference")
+        res = {}
+        for key, flags, lanes in (("kep", fk, REF_KEP_LANES), ("gp", fg, REF_GP_LANES)):
+            for _ in range(1):  # one untimed pass warms the caches and the thread pool
+                cpu_arm("reference", flags, data, max(lanes // 8, threads), threads)
+            secs = []
+            kind = None
+            for _ in range(a.steps):
+                kind, _, s = cpu_arm("reference", flags, data, lanes, threads)
+                secs.append(s)
+            v = lanes * len(secs) / sum(secs)
+            res[key] = {"value": v, "unit": "evals/s", "ms_per_step": 1e3 * sum(secs) / len(secs),
+                        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": threads, "kind": kind,
+                                         "sample": "%d lanes per step, %d steps, %d host threads" % (lanes, len(secs), threads)},
+                        "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        out.update(res["kep"])
+        out["gp"] = res["gp"]
+        out["config"] = {"workload": "K: Keplerian N=1000 Np=10 Gaussian; gp: QP-GP N=1000 Np=10; "
+                                     "reference RVmodel::calculate_mu/calculate_C/log_likelihood on host cores",
+                         "lanes_per_step": REF_KEP_LANES, "gp_lanes_per_step": REF_GP_LANES}
+        print(json.dumps(out))
+        return 0
+
+    rank, world, local = init_dist(a.gpus)
+    from kima_b200 import LikelihoodEngine
+    from kima_b200.dist import TorchBarrierExchange
+    exch = None
+    if world > 1:
+        import torch
+        exch = TorchBarrierExchange(torch.device("cuda", local))
+    out = dict(base)
+    results = {}
+    peak = None
+    for key, flags, lanes, fl in (("kep", fk, KEP_LANES, flops_keplerian(N_EPOCHS, NP)),
+                                  ("gp", fg, GP_LANES, flops_gp(N_EPOCHS, NP))):
+        if key not in a.workloads.split(","):
+            continue
+        eng = LikelihoodEngine(data, flags, lanes, device=local, kepler_mode=a.kepler_mode)
+        if peak is None:
+            dfma, dmma = eng.measure_fp64_peak(5)
+            peak = max(dfma, dmma)
+        # each rank scores its own shard of the global lane set (different seeds per rank)
+        P, nps = make_params(flags, data, lanes, "max", seed=43 + rank)
+        eng.set_params(P, nps)
+        eng.log_likelihood(lanes)  # puts the block on the device
+        r = run_workload(eng, lanes, a.steps, a.warmup, fl, peak, exch, local)
+        if rank == 0 and world == 1 and not a.skip_cpu_baseline:
+            ref_lanes = REF_KEP_LANES * 4 if key == "kep" else REF_GP_LANES * 8
+            kind, v, secs = cpu_arm("reference", flags, data, ref_lanes, threads)
+            r["cpu_baseline"] = {"value": v, "unit": "evals/s", "cores": threads, "kind": kind,
+                                 "sample": "%d lanes of the same workload, %d host threads, %.1f s" % (ref_lanes, threads, secs)}
+        results[key] = r
+        eng.close()
+    first = "kep" if "kep" in results else "gp"
+    out.update(results[first])
+    if first == "kep" and "gp" in results:
+        out["gp"] = dict(results["gp"], unit="evals/s")
+    out["config"] = {"workload": "K: Keplerian N=1000 Np=10 (Np fixed at npmax), Gaussian white noise, "
+                                 "%d lanes/GPU; gp: QP-GP N=1000 Np=10, %d lanes/GPU" % (KEP_LANES, GP_LANES),
+                     "lanes_per_gpu": KEP_LANES, "gp_lanes_per_gpu": GP_LANES,
+                     "kepler_mode": a.kepler_mode, "parallelism": "lanes sharded over %d GPU(s), no data-path collective" % world,
+                     "l2": "flushed between timed iterations (256 MiB memset on the kernel stream)",
+                     "fp64_peak_tflops_measured": peak}
+    if exch:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

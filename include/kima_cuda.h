@@ -171,6 +171,9 @@ int kc_set_option(kc_ctx* ctx, const char* key, int value);
  * evaluation call, and the number of kernel launches since kc_create. */
 int kc_last_kernel_ms(kc_ctx* ctx, float* keplerian_ms, float* gp_ms);
 int64_t kc_launch_count(kc_ctx* ctx);
+/* Writes a 256 MiB scratch buffer on the context stream so that the next timed
+ * evaluation starts with a cold L2 (bench hygiene; untimed by kc_last_kernel_ms). */
+int kc_flush_l2(kc_ctx* ctx);
 /* FP64 peak microbenchmarks run on the context's device: vector DFMA and
  * tensor DMMA TFLOP/s (best of `reps`). */
 int kc_measure_fp64_peak(kc_ctx* ctx, int reps, double* dfma_tflops,

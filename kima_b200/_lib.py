@@ -47,6 +47,7 @@ SIGNATURES = {
     "kc_set_option": (ctypes.c_int, [_vp, ctypes.c_char_p, ctypes.c_int]),
     "kc_last_kernel_ms": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_float),
                                          ctypes.POINTER(ctypes.c_float)]),
+    "kc_flush_l2": (ctypes.c_int, [_vp]),
     "kc_launch_count": (ctypes.c_int64, [_vp]),
     "kc_measure_fp64_peak": (ctypes.c_int, [_vp, ctypes.c_int, _dp, _dp]),
     "kc_kepler_E": (ctypes.c_int, [_vp, ctypes.c_int, _dp, _dp, _dp]),

@@ -67,6 +67,7 @@ struct kc_ctx {
     int rank = 0, nranks = 1;
     void* d_comm_buf = nullptr;
     size_t comm_buf_bytes = 0;
+    void* d_flush = nullptr;
 };
 
 namespace {
@@ -177,6 +178,7 @@ int kc_destroy(kc_ctx* c)
     free_data(c);
     cudaFree(c->d_counter);
     cudaFree(c->d_comm_buf);
+    cudaFree(c->d_flush);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -383,6 +385,16 @@ int kc_last_kernel_ms(kc_ctx* c, float* keplerian_ms, float* gp_ms)
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     if (keplerian_ms) *keplerian_ms = c->F.GP ? 0.f : ms;
     if (gp_ms) *gp_ms = c->F.GP ? ms : 0.f;
+    return KC_OK;
+}
+
+int kc_flush_l2(kc_ctx* c)
+{
+    if (!c) return fail(KC_ERR_ARG, "null context");
+    CU(cudaSetDevice(c->device));
+    const size_t bytes = (size_t)256 << 20;  // 2x the 126 MB L2
+    if (!c->d_flush) CU(cudaMalloc(&c->d_flush, bytes));
+    CU(cudaMemsetAsync(c->d_flush, 0, bytes, c->stream));
     return KC_OK;
 }
 

@@ -143,6 +143,9 @@ class LikelihoodEngine:
         _lib.check(self.lib.kc_last_kernel_ms(self._ctx, ctypes.byref(a), ctypes.byref(b)))
         return a.value + b.value
 
+    def flush_l2(self) -> None:
+        _lib.check(self.lib.kc_flush_l2(self._ctx))
+
     def launch_count(self) -> int:
         return int(self.lib.kc_launch_count(self._ctx))
 
