@@ -42,15 +42,24 @@ cudaError_t launch_true_anomaly(int n, const double* t, const double* P, const d
                                 const double* Tp, double* f, cudaStream_t s);
 cudaError_t launch_model_mu(const KParams& p, int kepler_mode, int lane, double* mu, cudaStream_t s);
 
+struct GpLane;  // kc_gp_common.cuh
 struct GpWorkspace {
     double* ws;          // per-slot factor storage
     size_t slot_doubles; // doubles per slot
     int slots;
+    GpLane* lanes;       // blocked path: per-slot state
+    int blocked;         // 1 = one launch per block column over all lanes (kc_gp_blocked.cu)
 };
+// single-CTA-per-particle path (kc_gp.cu)
 size_t gp_slot_doubles(int N);
 int gp_default_slots(int N, int sm_count);
 cudaError_t launch_gp(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
                       cudaStream_t stream, int* n_launches);
+// blocked path (kc_gp_blocked.cu)
+size_t gpb_slot_doubles(int N);
+size_t gpb_lane_bytes();
+cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode,
+                              cudaStream_t stream, int* n_launches);
 cudaError_t launch_gp_cov(const KParams& p, int lane, double* C, cudaStream_t s);
 
 // The communicator state of a context, as kc_comm.cu sees it.
