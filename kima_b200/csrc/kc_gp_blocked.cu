@@ -32,14 +32,17 @@ constexpr int KC = 16;        // k-chunk per pipeline stage
 constexpr int STAGES = 4;
 constexpr int A_LD = R + 4;   // 132 = 4 mod 16: conflict-free fragment reads (half-warp = 4 k x 4 rows)
 constexpr int B_LD = NB + 4;  // 68  = 4 mod 16
-constexpr int S_LD = NB + 1;  // row-per-thread access in the substitution
-constexpr int LT_LD = NB + 2; // 16-byte aligned rows for paired broadcast reads
+constexpr int S_LD = NB + 1;  // diag kernel: row-per-lane access
 constexpr int STAGE_DOUBLES = KC * (A_LD + B_LD);
 constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;
-constexpr int EPI_DOUBLES = R * S_LD + NB * LT_LD + NB;
+constexpr int EPI_DOUBLES = NB * A_LD + NB * B_LD;
 static_assert(EPI_DOUBLES <= PIPE_DOUBLES, "epilogue buffers alias the pipeline stages");
+constexpr int D_THREADS = 128;
+constexpr int D_STAGES = 3;
+constexpr int H_LD = 34;      // 32x32 half-block buffers of the diag kernel
 constexpr int D_STAGE_DOUBLES = KC * B_LD;
-constexpr int D_SMEM_DOUBLES = STAGES * D_STAGE_DOUBLES + 2 * NB * S_LD;
+constexpr int D_SMEM_DOUBLES = D_STAGES * D_STAGE_DOUBLES + NB * S_LD;
+static_assert(2 * 32 * H_LD <= D_STAGES * D_STAGE_DOUBLES, "half-block buffers alias the diag pipeline");
 constexpr int PAD_DOUBLES = 256;  // tiles may read (never use) up to R rows past the last column
 }  // namespace gpb
 
@@ -98,17 +101,128 @@ gpb_prep_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
 }
 
 // ---- diag: S_JJ, its Cholesky factor, log det ------------------------------------------------
-// 8 warps = 2 k-halves x 4 row groups; row group w owns fragment rows {w, 7-w} of the
-// lower triangle (9 of the 36 lower 8x8 fragments each, so the groups are balanced).
-__global__ void __launch_bounds__(CTA_THREADS, 2)
+// 128 threads.  K loop: warp w owns fragment rows {w, 7-w} of the lower triangle (9 of the
+// 36 lower 8x8 fragments each, so the warps are balanced); the A fragment of row f is the B
+// fragment of column f, so 8 shared-memory reads feed 9 DMMAs.
+// Factorisation: 64x64 = two 32x32 Cholesky steps with the rows of the block in the lanes
+// of ONE warp (pivot and column broadcast by shuffles, no block-wide barrier per column),
+// a row-per-lane triangular solve for L21 and a 4-warp rank-32 update in between.
+
+// Unblocked Cholesky of a 32x32 block (LLT.h:313-337) by one warp, row `lane` of the block
+// in s[0..lane].  A rolled loop over the columns: every step consumes s[0] and writes the
+// updated row shifted down by one (s[k-1] <- s[k] - L(r,c) L(c+k,c)), so all register
+// indices are static and the body stays in the instruction cache.  The finished column goes
+// to HBM (Lout(c, r) = L(r, c), column-major) and, transposed, to LT (shared) if wanted.
+__device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, int nvalid,
+                                                     double& logdet, double* dinv_out,
+                                                     double* __restrict__ Lout, size_t ld,
+                                                     double* LT, int lt_ld)
+{
+    bool ok = true;
+#pragma unroll 1
+    for (int c = 0; c < 32; c++) {
+        const double d = __shfl_sync(0xffffffffu, s[0], c);
+        if (!(d > 0.0)) ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
+        // 1/sqrt(d) from the MUFU seed + two Newton steps, sqrt(d) = d/sqrt(d) + one Heron step
+        double y = rsqrt_seed(d);
+        double hy = 0.5 * y;
+        double e = kfma(-d * y, hy, 0.5);
+        y = kfma(y, e, y);
+        hy = 0.5 * y;
+        double l = d * y;
+        e = kfma(-l, hy, 0.5);
+        y = kfma(y, e, y);
+        l = kfma(kfma(-l, l, d), 0.5 * y, l);
+        const double inv = y;
+        if (c < nvalid) logdet += log(l);
+        if (lane == 0) dinv_out[c] = inv;
+        const double lrc = s[0] * inv;
+        if (lane >= c && lane < nvalid) Lout[(size_t)c * ld + lane] = (lane == c) ? l : lrc;
+        if (LT) LT[c * lt_ld + lane] = (lane > c) ? lrc : 0.0;
+#pragma unroll
+        for (int k = 1; k < 32; k++) {
+            const double lc2 = __shfl_sync(0xffffffffu, lrc, (c + k) & 31);  // L(c+k, c)
+            s[k - 1] = kfma(-lrc, lc2, s[k]);
+        }
+        s[31] = 0.0;
+    }
+    return ok;
+}
+
+// K loop of the diag kernel for the warp that owns fragment rows F0 and 7-F0 (all
+// fragment indices compile-time: 9 DMMAs per k-step, no predication), then P -> Ss.
+template <int F0>
+__device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t ld, int j0,
+                                           double* pipe, double* Ss, int tid, int lane)
+{
+    using namespace gpb;
+    constexpr int F1 = 7 - F0;
+    double acc0[F0 + 1][2], acc1[F1 + 1][2];
+#pragma unroll
+    for (int c = 0; c <= F0; c++) acc0[c][0] = acc0[c][1] = 0.0;
+#pragma unroll
+    for (int c = 0; c <= F1; c++) acc1[c][0] = acc1[c][1] = 0.0;
+    const int nk = j0 / KC;
+    auto load_stage = [&](int s, int it) {
+        double* Bs = pipe + s * D_STAGE_DOUBLES;
+        const double* src = W + (size_t)(it * KC) * ld + j0;
+        // KC x NB doubles = 512 16-byte units, 4 per thread
+#pragma unroll
+        for (int u = tid; u < KC * NB / 2; u += D_THREADS) {
+            int kk = u / (NB / 2), r2 = (u % (NB / 2)) * 2;
+            cp_async16(Bs + kk * B_LD + r2, src + (size_t)kk * ld + r2);
+        }
+    };
+#pragma unroll
+    for (int s = 0; s < D_STAGES - 1; s++) {
+        if (s < nk) load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int it = 0; it < nk; it++) {
+        cp_async_wait<D_STAGES - 2>();
+        __syncthreads();
+        if (it + D_STAGES - 1 < nk) load_stage((it + D_STAGES - 1) % D_STAGES, it + D_STAGES - 1);
+        cp_async_commit();
+        const double* Bs = pipe + (it % D_STAGES) * D_STAGE_DOUBLES;
+#pragma unroll
+        for (int k4 = 0; k4 < KC; k4 += 4) {
+            const int kk = k4 + (lane & 3);
+            double bf[F1 + 1];
+#pragma unroll
+            for (int c = 0; c <= F1; c++) bf[c] = Bs[kk * B_LD + c * 8 + (lane >> 2)];
+#pragma unroll
+            for (int c = 0; c <= F0; c++) dmma(acc0[c][0], acc0[c][1], bf[F0], bf[c]);
+#pragma unroll
+            for (int c = 0; c <= F1; c++) dmma(acc1[c][0], acc1[c][1], bf[F1], bf[c]);
+        }
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int c = 0; c <= F0; c++) {
+        const int r = F0 * 8 + (lane >> 2), cc = c * 8 + 2 * (lane & 3);
+        Ss[r * S_LD + cc] = acc0[c][0];
+        Ss[r * S_LD + cc + 1] = acc0[c][1];
+    }
+#pragma unroll
+    for (int c = 0; c <= F1; c++) {
+        const int r = F1 * 8 + (lane >> 2), cc = c * 8 + 2 * (lane & 3);
+        Ss[r * S_LD + cc] = acc1[c][0];
+        Ss[r * S_LD + cc + 1] = acc1[c][1];
+    }
+}
+
+__global__ void __launch_bounds__(gpb::D_THREADS, 3)
 gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
                 GpLane* __restrict__ lanes, int j0)
 {
     using namespace gpb;
     extern __shared__ __align__(16) double dsm[];
-    double* pipe = dsm;                                // STAGES x [KC][B_LD]
-    double* Ss = dsm + STAGES * D_STAGE_DOUBLES;       // [NB][S_LD]
-    double* Sr = Ss + NB * S_LD;                       // second k-half's partial sums
+    double* pipe = dsm;                                // D_STAGES x [KC][B_LD]
+    double* Ss = dsm + D_STAGES * D_STAGE_DOUBLES;     // [NB][S_LD]
+    double* LTs = pipe;                                // after the K loop: [32][H_LD], LTs[c][c2] = L11(c2,c)
+    double* T21 = pipe + 32 * H_LD;                    // [32][H_LD]: L21 row-major
+    __shared__ double dinv_s[NB];
+    __shared__ int fail_s;
     const int slot = blockIdx.x;
     GpLane& gl = lanes[slot];
     if (gl.fail) return;
@@ -117,132 +231,99 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
     const size_t ld = ((size_t)N + 1 + 15) & ~(size_t)15;
     double* W = ws_all + (size_t)slot * slot_doubles;
     const int nbc = min(NB, N - j0);
-    const int grp = warp >> 2, w4 = warp & 3;
-    const int fr[2] = {w4, 7 - w4};
-
-    double acc[2][8][2];
-#pragma unroll
-    for (int a = 0; a < 2; a++)
-#pragma unroll
-        for (int c = 0; c < 8; c++) acc[a][c][0] = acc[a][c][1] = 0.0;
-
-    const int nk = j0 / KC;
-    auto load_stage = [&](int s, int it) {
-        double* Bs = pipe + s * D_STAGE_DOUBLES;
-        const double* src = W + (size_t)(it * KC) * ld + j0;
-        // KC x NB doubles = 512 16-byte units, 2 per thread
-#pragma unroll
-        for (int u = tid; u < KC * NB / 2; u += CTA_THREADS) {
-            int kk = u / (NB / 2), r2 = (u % (NB / 2)) * 2;
-            cp_async16(Bs + kk * B_LD + r2, src + (size_t)kk * ld + r2);
-        }
-    };
-#pragma unroll
-    for (int s = 0; s < STAGES - 1; s++) {
-        if (s < nk) load_stage(s, s);
-        cp_async_commit();
-    }
-    for (int it = 0; it < nk; it++) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        if (it + STAGES - 1 < nk) load_stage((it + STAGES - 1) % STAGES, it + STAGES - 1);
-        cp_async_commit();
-        const double* Bs = pipe + (it % STAGES) * D_STAGE_DOUBLES;
-#pragma unroll
-        for (int k4 = 0; k4 < KC / 8; k4++) {
-            const int kk = grp * (KC / 2) + k4 * 4 + (lane & 3);
-            double bf[8];
-#pragma unroll
-            for (int c = 0; c < 8; c++) bf[c] = Bs[kk * B_LD + c * 8 + (lane >> 2)];
-#pragma unroll
-            for (int a = 0; a < 2; a++) {
-                const double af = Bs[kk * B_LD + fr[a] * 8 + (lane >> 2)];
-#pragma unroll
-                for (int c = 0; c < 8; c++)
-                    if (c <= fr[a]) dmma(acc[a][c][0], acc[a][c][1], af, bf[c]);
-            }
-        }
-    }
-    cp_async_wait<0>();
-
-    // ---- S = C_JJ - (sum of the two k-halves) ----
-    if (grp == 1) {
-#pragma unroll
-        for (int a = 0; a < 2; a++)
-#pragma unroll
-            for (int c = 0; c < 8; c++)
-                if (c <= fr[a]) {
-                    const int r = fr[a] * 8 + (lane >> 2), cc = c * 8 + 2 * (lane & 3);
-                    Sr[r * S_LD + cc] = acc[a][c][0];
-                    Sr[r * S_LD + cc + 1] = acc[a][c][1];
-                }
+    if (tid == 0) fail_s = 0;
+    switch (warp) {
+        case 0: diag_kloop<0>(W, ld, j0, pipe, Ss, tid, lane); break;
+        case 1: diag_kloop<1>(W, ld, j0, pipe, Ss, tid, lane); break;
+        case 2: diag_kloop<2>(W, ld, j0, pipe, Ss, tid, lane); break;
+        default: diag_kloop<3>(W, ld, j0, pipe, Ss, tid, lane); break;
     }
     __syncthreads();
-    if (grp == 0) {
+    {
         const GpConsts g = gl.c;
         const bool multi = p.F.multi_instrument != 0;
-#pragma unroll
-        for (int a = 0; a < 2; a++) {
-            const int r = fr[a] * 8 + (lane >> 2);
-            const int row = j0 + r;
-            const double trow = row < N ? __ldg(p.t + row) : 0.0;
-#pragma unroll
-            for (int c = 0; c < 8; c++)
-                if (c <= fr[a]) {
-#pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        const int cc = c * 8 + 2 * (lane & 3) + h;
-                        const int col = j0 + cc;
-                        double v;
-                        if (r >= nbc || cc >= nbc) {
-                            v = (r == cc) ? 1.0 : 0.0;  // identity padding of a partial block
-                        } else if (cc > r) {
-                            v = 0.0;
-                        } else {
-                            if (r == cc) {
-                                int in = multi ? __ldg(p.obsi + row) - 1 : 0;
-                                // eta1^2 * exp(-0 - 0) + sig^2 + jit^2  (:193-206)
-                                v = kadd(g.eta1sq, kadd(__ldg(p.sig2 + row), gl.jit2[in]));
-                            } else {
-                                v = qp_kernel(g, kadd(__ldg(p.t + col), -trow));
-                            }
-                            v -= acc[a][c][h] + Sr[r * S_LD + cc];
-                        }
-                        Ss[r * S_LD + cc] = v;
-                    }
+        const int r = tid & (NB - 1);
+        const int row = j0 + r;
+        const double trow = row < N ? __ldg(p.t + row) : 0.0;
+        for (int cc = tid >> 6; cc < NB; cc += D_THREADS / NB) {
+            double v;
+            if (r >= nbc || cc >= nbc) {
+                v = (r == cc) ? 1.0 : 0.0;  // identity padding of a partial block
+            } else if (cc > r) {
+                v = 0.0;
+            } else {
+                if (r == cc) {
+                    int in = multi ? __ldg(p.obsi + row) - 1 : 0;
+                    // eta1^2 * exp(-0 - 0) + sig^2 + jit^2  (:193-206)
+                    v = kadd(g.eta1sq, kadd(__ldg(p.sig2 + row), gl.jit2[in]));
+                } else {
+                    v = qp_kernel(g, kadd(__ldg(p.t + j0 + cc), -trow));
                 }
-        }
-    }
-
-    // ---- unblocked right-looking Cholesky of the 64x64 block (LLT.h:313-337) ----
-    // Column c of Ss stays unscaled and read-only once step c has begun; the scaled
-    // column goes straight to HBM, so one barrier per column suffices.
-    double logdet = 0.0;
-    bool failed = false;
-    for (int c = 0; c < NB; c++) {
-        __syncthreads();
-        const double d = Ss[c * S_LD + c];
-        if (!(d > 0.0)) { failed = true; break; }  // NaN or non-positive pivot: uniform exit
-        const double l = sqrt(d);
-        const double inv = kdiv(1.0, l);
-        if (tid == 0 && c < nbc) {
-            logdet += log(l);
-            W[(size_t)(j0 + c) * ld + j0 + c] = l;
-            gl.dinv[c] = inv;
-        }
-        if (tid == 0 && c >= nbc) gl.dinv[c] = 1.0;
-        // rows r > c: store L(r,c); update the trailing lower triangle
-        for (int r = c + 1 + (tid >> 3); r < NB; r += CTA_THREADS / 8) {
-            const double lr = Ss[r * S_LD + c] * inv;
-            if ((tid & 7) == 0 && r < nbc) W[(size_t)(j0 + c) * ld + j0 + r] = lr;
-            for (int c2 = c + 1 + (tid & 7); c2 <= r; c2 += 8) {
-                const double lc = Ss[c2 * S_LD + c] * inv;
-                Ss[r * S_LD + c2] = kfma(-lr, lc, Ss[r * S_LD + c2]);
+                v -= Ss[r * S_LD + cc];
             }
+            Ss[r * S_LD + cc] = v;
         }
     }
+    __syncthreads();
+
+    double logdet = 0.0;
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+        const int h0 = 32 * half;
+        const int nv = max(0, min(32, nbc - h0));
+        if (warp == 0) {
+            double s[32];
+#pragma unroll
+            for (int c = 0; c < 32; c++) s[c] = Ss[(h0 + lane) * S_LD + h0 + c];
+            if (!chol32_rows_in_lanes(s, lane, nv, logdet, dinv_s + h0,
+                                      W + (size_t)(j0 + h0) * ld + j0 + h0, ld,
+                                      half == 0 ? LTs : nullptr, H_LD) && lane == 0)
+                fail_s = 1;
+        }
+        __syncthreads();
+        if (half == 0) {
+            if (warp == 1) {
+                // L21 = S21 L11^-T: row 32+lane, forward substitution
+                double t[32];
+#pragma unroll
+                for (int c = 0; c < 32; c++) t[c] = Ss[(32 + lane) * S_LD + c];
+#pragma unroll
+                for (int c = 0; c < 32; c++) {
+                    t[c] *= dinv_s[c];
+#pragma unroll
+                    for (int c2 = c + 1; c2 < 32; c2++) t[c2] = kfma(-t[c], LTs[c * H_LD + c2], t[c2]);
+                }
+#pragma unroll
+                for (int c = 0; c < 32; c++) {
+                    T21[lane * H_LD + c] = t[c];
+                    if (32 + lane < nbc) W[(size_t)(j0 + c) * ld + j0 + 32 + lane] = t[c];
+                }
+            }
+            __syncthreads();
+            {
+                // S22 -= L21 L21^T: warp w takes columns [8w, 8w+8), lane = row
+                double t[32];
+#pragma unroll
+                for (int k = 0; k < 32; k++) t[k] = T21[lane * H_LD + k];
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int c2 = 8 * warp + q;
+                    const double* o = T21 + c2 * H_LD;
+                    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 32; k += 2) {
+                        a0 = kfma(t[k], o[k], a0);
+                        a1 = kfma(t[k + 1], o[k + 1], a1);
+                    }
+                    Ss[(32 + lane) * S_LD + 32 + c2] -= a0 + a1;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if (tid < NB) gl.dinv[tid] = dinv_s[tid];
     if (tid == 0) {
-        if (failed) gl.fail = 1;
+        if (fail_s) gl.fail = 1;
         else gl.logdet += logdet;
     }
 }
@@ -318,97 +399,115 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     cp_async_wait<0>();
     __syncthreads();  // every warp is done with the stages: the epilogue buffers alias them
 
-    double* Ss = usm;                    // [R][S_LD]
-    double* LT = usm + R * S_LD;         // [NB][LT_LD]: LT[c][c2] = L_JJ(c2, c)
-    double* dinv = LT + NB * LT_LD;      // [NB]
+    double* SsT = usm;                   // [NB][A_LD]: the tile, column-major (S, then X in place)
+    double* LT = usm + NB * A_LD;        // [NB][B_LD]: LT[c][c2] = L_JJ(c2, c), zero on/above the diagonal
+    __shared__ double dinv[NB];
 
-    // ---- S = C - P, generating C here (its only touch) ----
-    {
-        const GpConsts g = gl.c;
+    // P (fragment layout) -> shared memory, so that the rest is rolled loops over the tile
 #pragma unroll
-        for (int a = 0; a < 4; a++) {
-            const int rl = wr * 32 + a * 8 + (lane >> 2);
-            const int row = r0 + rl;
-            const bool row_ok = row >= row_lo && row <= N;
-            const double trow = (row_ok && row < N) ? __ldg(p.t + row) : 0.0;
+    for (int a = 0; a < 4; a++)
 #pragma unroll
-            for (int c = 0; c < 4; c++) {
+        for (int c = 0; c < 4; c++)
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int cl = wc * 32 + c * 8 + 2 * (lane & 3) + h;
-                    const int col = j0 + cl;
-                    double v = 0.0;
-                    if (row_ok && cl < nbc) {
-                        if (row == N) v = W[(size_t)col * ld + N];
-                        else v = qp_kernel(g, kadd(__ldg(p.t + col), -trow));  // t[i]-t[j], i<j (:193)
-                        v -= acc[a][c][h];
-                    }
-                    Ss[rl * S_LD + cl] = v;
-                }
-            }
-        }
-    }
+            for (int h = 0; h < 2; h++)
+                SsT[(wc * 32 + c * 8 + 2 * (lane & 3) + h) * A_LD + wr * 32 + a * 8 + (lane >> 2)] = acc[a][c][h];
     // L_JJ (transposed) and the reciprocal diagonal, identity-padded for a partial block
     for (int e = tid; e < NB * NB; e += CTA_THREADS) {
         const int c = e / NB, c2 = e % NB;  // consecutive threads -> consecutive rows of one column
         double v = 0.0;
         if (c2 > c && c2 < nbc) v = W[(size_t)(j0 + c) * ld + j0 + c2];
-        LT[c * LT_LD + c2] = v;
+        LT[c * B_LD + c2] = v;
     }
     if (tid < NB) dinv[tid] = gl.dinv[tid];
     __syncthreads();
 
-    // ---- X L_JJ^T = S by forward substitution, a row per thread; store L ----
-    if (tid < R) {
-        const int row = r0 + tid;
-        if (row >= row_lo && row <= N) {
-            double* srow = Ss + tid * S_LD;
-            double q = 0.0;
-            {
-                double x[32];
-#pragma unroll
-                for (int c = 0; c < 32; c++) x[c] = srow[c];
-#pragma unroll
-                for (int c = 0; c < 32; c++) {
-                    x[c] *= dinv[c];
-#pragma unroll
-                    for (int c2 = c + 1; c2 < 32; c2++) x[c2] = kfma(-x[c], LT[c * LT_LD + c2], x[c2]);
-                }
-#pragma unroll
-                for (int c = 0; c < 32; c++) {
-                    srow[c] = x[c];
-                    if (c < nbc) {
-                        W[(size_t)(j0 + c) * ld + row] = x[c];
-                        q = kfma(x[c], x[c], q);
-                    }
-                }
+    // ---- S = C - P, generating C here (its only touch) ----
+    {
+        const GpConsts g = gl.c;
+        const int rl = tid & (R - 1);
+        const int row = r0 + rl;
+        const bool row_ok = row >= row_lo && row <= N;
+        const double trow = (row_ok && row < N) ? __ldg(p.t + row) : 0.0;
+        for (int cl = tid >> 7; cl < NB; cl += CTA_THREADS / R) {
+            const int col = j0 + cl;
+            double v = 0.0;
+            if (row_ok && cl < nbc) {
+                if (row == N) v = W[(size_t)col * ld + N];
+                else v = qp_kernel(g, kadd(__ldg(p.t + col), -trow));  // t[i]-t[j], i<j (:193)
+                v -= SsT[cl * A_LD + rl];
             }
-            {
-                double y[32];
-#pragma unroll
-                for (int c = 0; c < 32; c++) y[c] = srow[32 + c];
-                for (int k = 0; k < 32; k++) {
-                    const double xk = srow[k];
-                    const double* lt = LT + k * LT_LD + 32;
-#pragma unroll
-                    for (int c = 0; c < 32; c++) y[c] = kfma(-xk, lt[c], y[c]);
-                }
-#pragma unroll
-                for (int c = 0; c < 32; c++) {
-                    y[c] *= dinv[32 + c];
-#pragma unroll
-                    for (int c2 = c + 1; c2 < 32; c2++)
-                        y[c2] = kfma(-y[c], LT[(32 + c) * LT_LD + 32 + c2], y[c2]);
-                }
-#pragma unroll
-                for (int c = 0; c < 32; c++)
-                    if (32 + c < nbc) {
-                        W[(size_t)(j0 + 32 + c) * ld + row] = y[c];
-                        q = kfma(y[c], y[c], q);
-                    }
-            }
-            if (row == N) gl.quad += q;  // |z|^2 of this block column
+            SsT[cl * A_LD + rl] = v;
         }
+    }
+    __syncthreads();
+
+    // ---- X L_JJ^T = S: each warp owns 16 rows.  Blocked forward substitution over four
+    //      16-column blocks: the off-diagonal part on the tensor cores, the 16x16 diagonal
+    //      blocks by plain substitution (a row per lane).  Only warp-level syncs. ----
+    {
+        const int rb = warp * 16;
+        for (int jb = 0; jb < 4; jb++) {
+            if (jb > 0) {
+                double u[2][2][2];
+#pragma unroll
+                for (int m = 0; m < 2; m++)
+#pragma unroll
+                    for (int n = 0; n < 2; n++) u[m][n][0] = u[m][n][1] = 0.0;
+                for (int kb = 0; kb < jb * 16; kb += 4) {
+                    const int kk = kb + (lane & 3);
+                    double af[2], bf[2];
+#pragma unroll
+                    for (int m = 0; m < 2; m++) af[m] = SsT[kk * A_LD + rb + m * 8 + (lane >> 2)];
+#pragma unroll
+                    for (int n = 0; n < 2; n++) bf[n] = LT[kk * B_LD + jb * 16 + n * 8 + (lane >> 2)];
+#pragma unroll
+                    for (int m = 0; m < 2; m++)
+#pragma unroll
+                        for (int n = 0; n < 2; n++) dmma(u[m][n][0], u[m][n][1], af[m], bf[n]);
+                }
+#pragma unroll
+                for (int m = 0; m < 2; m++)
+#pragma unroll
+                    for (int n = 0; n < 2; n++)
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            double* q = SsT + (jb * 16 + n * 8 + 2 * (lane & 3) + h) * A_LD + rb + m * 8 + (lane >> 2);
+                            *q -= u[m][n][h];
+                        }
+                __syncwarp();
+            }
+            if (lane < 16) {
+                double x[16];
+                double* col0 = SsT + (jb * 16) * A_LD + rb + lane;
+                const double* l0 = LT + (jb * 16) * B_LD + jb * 16;
+#pragma unroll
+                for (int c = 0; c < 16; c++) x[c] = col0[c * A_LD];
+#pragma unroll
+                for (int c = 0; c < 16; c++) {
+                    x[c] *= dinv[jb * 16 + c];
+#pragma unroll
+                    for (int c2 = c + 1; c2 < 16; c2++) x[c2] = kfma(-x[c], l0[c * B_LD + c2], x[c2]);
+                }
+#pragma unroll
+                for (int c = 0; c < 16; c++) col0[c * A_LD] = x[c];
+            }
+            __syncwarp();
+        }
+        // store the warp's 16 rows: lanes 0-15 an even column, lanes 16-31 the odd one
+        const int rl = rb + (lane & 15);
+        const int row = r0 + rl;
+        const bool ok = row >= row_lo && row <= N;
+        double q = 0.0;
+        for (int cp = 0; cp < NB / 2; cp++) {
+            const int c = 2 * cp + (lane >> 4);
+            if (ok && c < nbc) {
+                const double x = SsT[c * A_LD + rl];
+                W[(size_t)(j0 + c) * ld + row] = x;
+                q = kfma(x, x, q);
+            }
+        }
+        q += __shfl_xor_sync(0xffffffffu, q, 16);
+        if (row == N && lane < 16) gl.quad += q;  // |z|^2 of this block column
     }
 }
 
@@ -453,7 +552,7 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
         for (int J = 0; J < nblk; J++) {
             const int j0 = J * NB;
             const int nbc = min(NB, N - j0);
-            gpb_diag_kernel<<<n, CTA_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0);
+            gpb_diag_kernel<<<n, D_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0);
             // rows below the diagonal block, up to and including the residual row N
             const int first_row = nbc == NB ? j0 + NB : j0;
             const int ntile = (N + 1 - first_row + R - 1) / R;
