@@ -47,6 +47,7 @@ void hc_misc(int which, int n, const double* x, const double* y, double* r)
         else if (which == 2) r[i] = kc::rcp_nr2(x[i]);
         else if (which == 3) r[i] = kc::div_fast(x[i], y[i]);
         else if (which == 4) r[i] = kc::div_by(x[i], y[i], 1.0 / y[i]);
+        else if (which == 6) r[i] = kc::exp_nonpos(x[i]);
         else r[i] = kc::rcp_nr1(x[i]);
     }
 }

@@ -51,7 +51,7 @@ struct kc_ctx {
     int* d_counter = nullptr;
     // GP
     double* d_resid = nullptr;
-    kc::GpWorkspace gp{nullptr, 0, 0, nullptr, 0};
+    kc::GpWorkspace gp{nullptr, 0, 0, nullptr, 0, nullptr, 100};
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
@@ -79,10 +79,10 @@ void free_model(kc_ctx* c)
     if (c->h_np) cudaFreeHost(c->h_np);
     if (c->h_logL) cudaFreeHost(c->h_logL);
     cudaFree(c->d_params); cudaFree(c->d_np); cudaFree(c->d_logL);
-    cudaFree(c->d_resid); cudaFree(c->gp.ws); cudaFree(c->gp.lanes);
+    cudaFree(c->d_resid); cudaFree(c->gp.ws); cudaFree(c->gp.lanes); cudaFree(c->gp.stagger);
     c->h_params = nullptr; c->h_np = nullptr; c->h_logL = nullptr;
     c->d_params = nullptr; c->d_np = nullptr; c->d_logL = nullptr;
-    c->d_resid = nullptr; c->gp = {nullptr, 0, 0, nullptr, 0};
+    c->d_resid = nullptr; c->gp = {nullptr, 0, 0, nullptr, 0, nullptr, c->gp.stagger_pct};
     c->configured = false;
 }
 void free_data(kc_ctx* c)
@@ -112,7 +112,7 @@ int run_kernels(kc_ctx* c, int B, double* d_logL)
     int n = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
-    if (c->F.GP && c->gp.blocked) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->stream, &n);
+    if (c->F.GP && c->gp.blocked) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else if (c->F.GP) e = kc::launch_gp(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
     if (e != cudaSuccess) return fail_cuda(e, "kernel launch");
@@ -276,7 +276,11 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
         if (slots > max_batch) slots = max_batch;
         c->gp.slots = slots;
         CU(cudaMalloc(&c->gp.ws, sizeof(double) * c->gp.slot_doubles * slots));
-        if (c->gp.blocked) CU(cudaMalloc((void**)&c->gp.lanes, kc::gpb_lane_bytes() * slots));
+        if (c->gp.blocked) {
+            CU(cudaMalloc((void**)&c->gp.lanes, kc::gpb_lane_bytes() * slots));
+            CU(cudaMalloc((void**)&c->gp.stagger, sizeof(int) * 1024));
+            CU(cudaMemset(c->gp.stagger, 0, sizeof(int) * 1024));
+        }
     }
     c->configured = true;
     return KC_OK;
@@ -382,6 +386,9 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
     } else if (k == "gp_path") {
         if (value < 0 || value > 2) return fail(KC_ERR_ARG, "gp_path must be 0 (auto), 1 (cta) or 2 (blocked)");
         c->gp_path_opt = value;  // takes effect at the next kc_configure
+    } else if (k == "gp_stagger") {
+        if (value < 0 || value > 400) return fail(KC_ERR_ARG, "gp_stagger is a percentage in [0, 400]");
+        c->gp.stagger_pct = value;
     } else if (k == "gp_slots") {
         if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
         c->gp_slots_opt = value;  // takes effect at the next kc_configure

@@ -29,14 +29,14 @@ namespace gpb {
 constexpr int NB = 64;        // block-column width
 constexpr int R = 128;        // rows per update tile
 constexpr int KC = 16;        // k-chunk per pipeline stage
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int A_LD = R + 4;   // 132 = 4 mod 16: conflict-free fragment reads (half-warp = 4 k x 4 rows)
 constexpr int B_LD = NB + 4;  // 68  = 4 mod 16
 constexpr int S_LD = NB + 1;  // diag kernel: row-per-lane access
 constexpr int STAGE_DOUBLES = KC * (A_LD + B_LD);
 constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;
-constexpr int EPI_DOUBLES = NB * A_LD + NB * B_LD;
-static_assert(EPI_DOUBLES <= PIPE_DOUBLES, "epilogue buffers alias the pipeline stages");
+static_assert(NB * A_LD <= PIPE_DOUBLES, "the S tile aliases the pipeline stages");
+constexpr int U_SMEM_DOUBLES = PIPE_DOUBLES + NB * B_LD + NB;  // + L_JJ^T + 1/diag, prefetched
 constexpr int D_THREADS = 128;
 constexpr int D_STAGES = 3;
 constexpr int H_LD = 34;      // 32x32 half-block buffers of the diag kernel
@@ -331,7 +331,8 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
 // ---- update: the panel below the diagonal block ----------------------------------------------
 __global__ void __launch_bounds__(CTA_THREADS, 2)
 gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                  GpLane* __restrict__ lanes, int j0, int first_row)
+                  GpLane* __restrict__ lanes, int j0, int first_row, int* __restrict__ stagger,
+                  int first_wave, long long stagger_clocks)
 {
     using namespace gpb;
     extern __shared__ __align__(16) double usm[];
@@ -339,6 +340,23 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     GpLane& gl = lanes[slot];
     if (gl.fail) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // Phase staggering.  All CTAs of a launch take the same time, so the two CTAs resident
+    // on an SM would march in lock-step: both in the DMMA loop, then both in the (latency-
+    // bound) epilogue with the FP64 pipe idle.  The second CTA to arrive on each SM in the
+    // first wave waits half a tile period once; from then on one CTA's epilogue overlaps the
+    // other's DMMA loop for the rest of the launch.
+    if (stagger_clocks > 0 && (int)(blockIdx.y * gridDim.x + blockIdx.x) < first_wave) {
+        if (tid == 0) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            const int arrival = atomicAdd(stagger + smid, 1);
+            if (arrival & 1) {
+                const long long t0 = clock64();
+                while (clock64() - t0 < stagger_clocks) {}
+            }
+        }
+        __syncthreads();
+    }
     const int N = p.N;
     const size_t ld = ((size_t)N + 1 + 15) & ~(size_t)15;
     double* W = ws_all + (size_t)slot * slot_doubles;
@@ -352,6 +370,17 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     for (int a = 0; a < 4; a++)
 #pragma unroll
         for (int c = 0; c < 4; c++) acc[a][c][0] = acc[a][c][1] = 0.0;
+
+    // L_JJ (as stored: LT[c][c2] = L_JJ(c2, c), only c2 > c is ever read) and 1/diag ride in
+    // as the oldest cp.async group, hidden behind the K loop
+    double* LT = usm + PIPE_DOUBLES;     // [NB][B_LD]
+    double* dinv = LT + NB * B_LD;       // [NB]
+    for (int u = tid; u < nbc * (NB / 2); u += CTA_THREADS) {
+        const int c = u / (NB / 2), c2 = (u % (NB / 2)) * 2;
+        cp_async16(LT + c * B_LD + c2, W + (size_t)(j0 + c) * ld + j0 + c2);
+    }
+    if (tid < NB / 2) cp_async16(dinv + 2 * tid, gl.dinv + 2 * tid);
+    cp_async_commit();
 
     const int nk = j0 / KC;
     auto load_stage = [&](int s, int it) {
@@ -400,8 +429,6 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     __syncthreads();  // every warp is done with the stages: the epilogue buffers alias them
 
     double* SsT = usm;                   // [NB][A_LD]: the tile, column-major (S, then X in place)
-    double* LT = usm + NB * A_LD;        // [NB][B_LD]: LT[c][c2] = L_JJ(c2, c), zero on/above the diagonal
-    __shared__ double dinv[NB];
 
     // P (fragment layout) -> shared memory, so that the rest is rolled loops over the tile
 #pragma unroll
@@ -411,14 +438,6 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
 #pragma unroll
             for (int h = 0; h < 2; h++)
                 SsT[(wc * 32 + c * 8 + 2 * (lane & 3) + h) * A_LD + wr * 32 + a * 8 + (lane >> 2)] = acc[a][c][h];
-    // L_JJ (transposed) and the reciprocal diagonal, identity-padded for a partial block
-    for (int e = tid; e < NB * NB; e += CTA_THREADS) {
-        const int c = e / NB, c2 = e % NB;  // consecutive threads -> consecutive rows of one column
-        double v = 0.0;
-        if (c2 > c && c2 < nbc) v = W[(size_t)(j0 + c) * ld + j0 + c2];
-        LT[c * B_LD + c2] = v;
-    }
-    if (tid < NB) dinv[tid] = gl.dinv[tid];
     __syncthreads();
 
     // ---- S = C - P, generating C here (its only touch) ----
@@ -428,15 +447,25 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         const int row = r0 + rl;
         const bool row_ok = row >= row_lo && row <= N;
         const double trow = (row_ok && row < N) ? __ldg(p.t + row) : 0.0;
-        for (int cl = tid >> 7; cl < NB; cl += CTA_THREADS / R) {
-            const int col = j0 + cl;
-            double v = 0.0;
-            if (row_ok && cl < nbc) {
-                if (row == N) v = W[(size_t)col * ld + N];
-                else v = qp_kernel(g, kadd(__ldg(p.t + col), -trow));  // t[i]-t[j], i<j (:193)
-                v -= SsT[cl * A_LD + rl];
+        // two columns per pass (cl, cl + 2): two independent chains per thread
+        for (int cl = tid >> 7; cl < NB; cl += 2 * CTA_THREADS / R) {
+            const int cl1 = cl + CTA_THREADS / R;
+            const int col = j0 + cl, col1 = j0 + cl1;
+            double v0 = 0.0, v1 = 0.0;
+            if (row_ok) {
+                if (row == N) {
+                    if (cl < nbc) v0 = W[(size_t)col * ld + N];
+                    if (cl1 < nbc) v1 = W[(size_t)col1 * ld + N];
+                } else {
+                    // t[i]-t[j], i<j (:193); columns past a partial block are generated and dropped
+                    const double tc0 = __ldg(p.t + min(col, N - 1)), tc1 = __ldg(p.t + min(col1, N - 1));
+                    qp_kernel2(g, kadd(tc0, -trow), kadd(tc1, -trow), v0, v1);
+                }
+                v0 = cl < nbc ? v0 - SsT[cl * A_LD + rl] : 0.0;
+                v1 = cl1 < nbc ? v1 - SsT[cl1 * A_LD + rl] : 0.0;
             }
-            SsT[cl * A_LD + rl] = v;
+            SsT[cl * A_LD + rl] = v0;
+            SsT[cl1 * A_LD + rl] = v1;
         }
     }
     __syncthreads();
@@ -528,12 +557,12 @@ __global__ void gpb_finish_kernel(const KParams p, const GpLane* __restrict__ la
     p.logL[lane0 + s] = logL;
 }
 
-cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode,
+cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
                               cudaStream_t stream, int* n_launches)
 {
     using namespace gpb;
     if (p.B <= 0) return cudaSuccess;
-    const size_t usmem = sizeof(double) * PIPE_DOUBLES;
+    const size_t usmem = sizeof(double) * U_SMEM_DOUBLES;
     const size_t dsmem = sizeof(double) * D_SMEM_DOUBLES;
     cudaError_t e;
     e = cudaFuncSetAttribute(gpb_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
@@ -557,8 +586,11 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
             const int first_row = nbc == NB ? j0 + NB : j0;
             const int ntile = (N + 1 - first_row + R - 1) / R;
             dim3 grid(ntile, n);
+            // per CTA: nk chunks of 128x64x16 DMMA work shared with one neighbour + the epilogue
+            const long long period = (long long)(j0 / KC) * 4096 + 24000;
+            const long long stag = (long long)ntile * n > 2 * sm_count ? period * w.stagger_pct / 200 : 0;
             gpb_update_kernel<<<grid, CTA_THREADS, usmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0,
-                                                                   first_row);
+                                                                   first_row, w.stagger, 2 * sm_count, stag);
             *n_launches += 2;
         }
         gpb_finish_kernel<<<(n + 127) / 128, 128, 0, stream>>>(p, w.lanes, lane0, n);

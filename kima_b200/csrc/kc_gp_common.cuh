@@ -7,7 +7,15 @@
 namespace kc {
 
 // sin(x) alone, |x| < ~1e5: one polynomial, chosen by quadrant.
+__device__ __forceinline__ double sin_core(double x);
 __device__ __forceinline__ double sin_fast(double x)
+{
+    if (fabs(x) > 1.0e5) return sin(x);
+    return sin_core(x);
+}
+
+// The same without the large-argument guard (callers check |x| <= 1e5 themselves).
+__device__ __forceinline__ double sin_core(double x)
 {
     const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
                  S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
@@ -15,7 +23,6 @@ __device__ __forceinline__ double sin_fast(double x)
     const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
                  C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
                  C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
-    if (fabs(x) > 1.0e5) return sin(x);
     int k;
     double kd = rint_magic_i(x * TWO_OVER_PI, k);
     double r = kfma(-kd, PIO2_HI, x);
@@ -42,13 +49,15 @@ struct GpConsts {
 };
 
 // Per-lane state of the blocked path, living beside the factor storage in HBM.
-struct GpLane {
+struct __align__(16) GpLane {
+    double dinv[64];          // 1 / diag(L_JJ) of the block column in flight (cp.async source)
     GpConsts c;
     double jit2[KC_MAX_INST];
-    double dinv[64];          // 1 / diag(L_JJ) of the block column in flight
     double logdet, quad;
     int fail, pad;
+    double pad2;
 };
+static_assert(sizeof(GpLane) % 16 == 0, "lanes[] elements stay 16-byte aligned");
 
 __device__ __forceinline__ GpConsts gp_consts(const ParticleScalars& sc)
 {
@@ -69,7 +78,26 @@ __device__ __forceinline__ double qp_kernel(const GpConsts& g, double tau)
     double s = sin_fast(div_by(kmul(PI, tau), g.eta3, g.r_eta3));
     double v = div_by(s, g.eta4, g.r_eta4);
     double a2 = 2.0 * kmul(v, v);
-    return kmul(g.eta1sq, exp(kadd(a1, -a2)));
+    return kmul(g.eta1sq, exp_nonpos(kadd(a1, -a2)));
+}
+
+// Two entries at once: two independent, branch-free dependency chains for the FP64 pipe
+// (one chain per thread leaves it half idle at 4 warps per scheduler).
+__device__ __forceinline__ void qp_kernel2(const GpConsts& g, double tau0, double tau1,
+                                           double& c0, double& c1)
+{
+    double u0 = div_by(tau0, g.eta2, g.r_eta2), u1 = div_by(tau1, g.eta2, g.r_eta2);
+    double x0 = div_by(kmul(PI, tau0), g.eta3, g.r_eta3), x1 = div_by(kmul(PI, tau1), g.eta3, g.r_eta3);
+    double s0 = sin_core(x0), s1 = sin_core(x1);
+    if (!(fabs(x0) <= 1.0e5) || !(fabs(x1) <= 1.0e5)) {  // never taken with any sane eta3
+        s0 = sin(x0);
+        s1 = sin(x1);
+    }
+    double v0 = div_by(s0, g.eta4, g.r_eta4), v1 = div_by(s1, g.eta4, g.r_eta4);
+    double e0 = kadd(-0.5 * kmul(u0, u0), -2.0 * kmul(v0, v0));
+    double e1 = kadd(-0.5 * kmul(u1, u1), -2.0 * kmul(v1, v1));
+    c0 = kmul(g.eta1sq, exp_nonpos(e0));
+    c1 = kmul(g.eta1sq, exp_nonpos(e1));
 }
 
 __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)

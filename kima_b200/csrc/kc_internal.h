@@ -49,6 +49,8 @@ struct GpWorkspace {
     int slots;
     GpLane* lanes;       // blocked path: per-slot state
     int blocked;         // 1 = one launch per block column over all lanes (kc_gp_blocked.cu)
+    int* stagger;        // per-SM arrival counters of the update kernel's phase staggering
+    int stagger_pct;     // 100 = half a tile period; 0 = off
 };
 // single-CTA-per-particle path (kc_gp.cu)
 size_t gp_slot_doubles(int N);
@@ -58,7 +60,7 @@ cudaError_t launch_gp(const KParams& p, const GpWorkspace& w, int kepler_mode, i
 // blocked path (kc_gp_blocked.cu)
 size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();
-cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode,
+cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
                               cudaStream_t stream, int* n_launches);
 cudaError_t launch_gp_cov(const KParams& p, int lane, double* C, cudaStream_t s);
 

@@ -199,6 +199,46 @@ KC_HD double mod_two_pi(double M)
     return (r < 0.0) ? kadd(r, TWO_PI) : r;
 }
 
+// ---- exp(x) for x <= 0 (the GP kernel's argument), branch-free ---------------------
+// k = rint(x log2 e), r = x - k ln2 (two-term Cody-Waite, exact for |k| < 2^11 with the
+// 42-bit high part), exp(r) by its Taylor series to r^13 (|r| <= 0.3466: truncation
+// 4e-18), scaled by 2^k in two exact-until-the-last steps so that results below 2^-1022
+// round once into the subnormals.  ~0.6 ulp (measured against long double in tests/); x < -746 gives 0, NaN gives NaN.
+KC_HD double exp_nonpos(double x)
+{
+    const double LOG2E = 1.44269504088896338700e+00;
+    const double LN2_HI = 6.93147180559890330187e-01;   // 42 significant bits
+    const double LN2_LO = 5.49792301870837115524e-14;
+    double xc = x < -746.0 ? -746.0 : x;  // NaN falls through
+    int k;
+    double kd = rint_magic_i(xc * LOG2E, k);
+    double rh = kfma(-kd, LN2_HI, xc);             // exact
+    double rl = -kd * LN2_LO;
+    double r = rh + rl;
+    double p = 1.0 / 6227020800.0;                 // 1/13!
+    p = kfma(p, r, 1.0 / 479001600.0);
+    p = kfma(p, r, 1.0 / 39916800.0);
+    p = kfma(p, r, 1.0 / 3628800.0);
+    p = kfma(p, r, 1.0 / 362880.0);
+    p = kfma(p, r, 1.0 / 40320.0);
+    p = kfma(p, r, 1.0 / 5040.0);
+    p = kfma(p, r, 1.0 / 720.0);
+    p = kfma(p, r, 1.0 / 120.0);
+    p = kfma(p, r, 1.0 / 24.0);
+    p = kfma(p, r, 1.0 / 6.0);
+    p = kfma(p, r, 0.5);
+    double r2 = r * r;
+    // exp(r) = (1 + r) + r^2 (1/2 + ...) with the rounding error of 1 + r carried along,
+    // so the only full-size rounding is the last addition
+    double t1 = kadd(1.0, rh);
+    double lo = kadd(kadd(rh, -kadd(t1, -1.0)), rl);
+    p = kadd(t1, kfma(p, r2, lo));
+    // 2^(k+64) is a normal number for every k >= -1077; the final 2^-64 rounds once
+    double s1 = from_bits((uint64_t)(int64_t)(k + 64 + 1023) << 52);
+    double y = (p * s1) * 5.42101086242752217004e-20;  // 2^-64
+    return x < -746.0 ? 0.0 : y;
+}
+
 // ---- sin and cos together -------------------------------------------------------
 // fdlibm kernel polynomials on [-pi/4, pi/4]; ~1 ulp.
 KC_HD void sincos_kernel(double r, double& s, double& c)

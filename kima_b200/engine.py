@@ -116,6 +116,9 @@ class LikelihoodEngine:
         _lib.check(self.lib.kc_eval(self._ctx, B, _d(out)))
         return out
 
+    def set_option(self, key: str, value: int) -> None:
+        _lib.check(self.lib.kc_set_option(self._ctx, key.encode(), int(value)))
+
     def log_likelihood_async(self, B: int, out: np.ndarray) -> None:
         _lib.check(self.lib.kc_eval_async(self._ctx, B, _d(out)))
 
