@@ -139,8 +139,20 @@ def cpu_arm(kind_pref: str, flags: ModelFlags, data, lanes: int, threads: int, r
     return kind, lanes / best, best
 
 
+# ncu --set full captures of the dominant kernel of each workload (profiles/, per launch):
+# dram__bytes_read.sum + dram__bytes_write.sum, and what the algorithm needs per launch.
+NCU_TRAFFIC = {
+    "kep": {"kernel": "keplerian_warp_kernel<0,0>", "traffic": 3.50e6,
+            "algorithmic_bytes": 8192 * (52 * 8 + 4 + 8) + 4 * 8000,
+            "source": "profiles/ncu_keplerian_r01b.json (8192 lanes: parameters in, logL out, data arrays once)"},
+    "gp": {"kernel": "gpb_update_kernel (block column 8 of 16, j0=512)", "traffic": 2.84e9 + 0.25e9,
+           "algorithmic_bytes": 1184 * (576 * 512 + 512 * 64) * 8,
+           "source": "profiles/ncu_gp_update_r01b.json (1184 lanes: panel rows re-read once, L tile written once)"},
+}
+
+
 def run_workload(eng, lanes: int, steps: int, warmup: int, flops_per_eval: float, peak_tflops: float,
-                 exch, sampler_idx: int):
+                 exch, sampler_idx: int, key: str = "kep"):
     """W warm-up + K timed steps of one workload on this rank's engine."""
     for _ in range(max(warmup, 3)):
         eng.flush_l2()
@@ -191,9 +203,17 @@ def run_workload(eng, lanes: int, steps: int, warmup: int, flops_per_eval: float
         "e2e": {"value": world * lanes / (e2e_s / steps), "unit": "evals/s",
                 "h2d_bytes_per_step": int(n_rows * lanes * 8 + lanes * 4),
                 "d2h_bytes_per_step": int(lanes * 8)},
-        "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
-                     "frac": achieved / peak_tflops, "traffic": None,
+        # "tensor" = compute roofline in TFLOP/s (the contract's two classes are hbm | tensor).
+        # The denominator is the FP64 peak: DMMA (FP64 tensor pipe) for the GP kernels, which
+        # issue mma.sync.m8n8k4.f64; the Keplerian kernel runs on the FP64 vector pipe (DFMA),
+        # whose measured peak is 0.91 of the DMMA figure used here.
+        "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
+                     "frac": achieved / peak_tflops, "traffic": NCU_TRAFFIC[key]["traffic"],
+                     "traffic_detail": NCU_TRAFFIC[key],
+                     "pipe": "FP64 tensor (DMMA.8x8x4)" if key == "gp" else "FP64 vector (DFMA); no tensor-core instructions",
                      "flops_per_eval": flops_per_eval,
+                     "per": "one step = one evaluation of all lanes (GP: 34 launches; the dominant "
+                            "kernel gpb_update_kernel is 85% of the step, profiles/launches_gp_r01b.csv)",
                      "peak_source": "kc_measure_fp64_peak in this run (max of DFMA / DMMA m8n8k4); "
                                     "MEASURED_PEAKS.json has no FP64 entry"},
         "clocks": clocks, "wall_s_timed_region": wall, "finite": bool(np.all(np.isfinite(out))),
@@ -269,7 +289,7 @@ def main():
         P, nps = make_params(flags, data, lanes, "max", seed=43 + rank)
         eng.set_params(P, nps)
         eng.log_likelihood(lanes)  # puts the block on the device
-        r = run_workload(eng, lanes, a.steps, a.warmup, fl, peak, exch, local)
+        r = run_workload(eng, lanes, a.steps, a.warmup, fl, peak, exch, local, key)
         if rank == 0 and world == 1 and not a.skip_cpu_baseline:
             ref_lanes = REF_KEP_LANES * 4 if key == "kep" else REF_GP_LANES * 8
             kind, v, secs = cpu_arm("reference", flags, data, ref_lanes, threads)

@@ -50,12 +50,10 @@ struct kc_ctx {
     double *d_logL = nullptr, *h_logL = nullptr;
     int* d_counter = nullptr;
     // GP
-    double* d_resid = nullptr;
-    kc::GpWorkspace gp{nullptr, 0, 0, nullptr, 0, nullptr, 100};
+    kc::GpWorkspace gp{nullptr, 0, 0, nullptr, 0};
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
-    int gp_path_opt = 0;   // 0 auto, 1 single CTA per particle, 2 blocked
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     float last_ms = 0.f;
@@ -79,10 +77,10 @@ void free_model(kc_ctx* c)
     if (c->h_np) cudaFreeHost(c->h_np);
     if (c->h_logL) cudaFreeHost(c->h_logL);
     cudaFree(c->d_params); cudaFree(c->d_np); cudaFree(c->d_logL);
-    cudaFree(c->d_resid); cudaFree(c->gp.ws); cudaFree(c->gp.lanes); cudaFree(c->gp.stagger);
+    cudaFree(c->gp.ws); cudaFree(c->gp.lanes);
     c->h_params = nullptr; c->h_np = nullptr; c->h_logL = nullptr;
     c->d_params = nullptr; c->d_np = nullptr; c->d_logL = nullptr;
-    c->d_resid = nullptr; c->gp = {nullptr, 0, 0, nullptr, 0, nullptr, c->gp.stagger_pct};
+    c->gp = {nullptr, 0, 0, nullptr, c->gp.fuse_diag};
     c->configured = false;
 }
 void free_data(kc_ctx* c)
@@ -102,7 +100,7 @@ kc::KParams make_params(kc_ctx* c, int B, double* d_logL)
     p.M0_epoch = c->M0_epoch; p.t_middle = c->t_middle;
     p.F = c->F; p.L = c->L;
     p.params = c->d_params; p.np = c->d_np; p.ld = c->ld; p.B = B;
-    p.logL = d_logL; p.resid = c->d_resid; p.counter = c->d_counter;
+    p.logL = d_logL; p.counter = c->d_counter;
     return p;
 }
 
@@ -112,8 +110,7 @@ int run_kernels(kc_ctx* c, int B, double* d_logL)
     int n = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
-    if (c->F.GP && c->gp.blocked) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
-    else if (c->F.GP) e = kc::launch_gp(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
+    if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
     if (e != cudaSuccess) return fail_cuda(e, "kernel launch");
     CU(cudaEventRecord(c->ev1, c->stream));
@@ -260,27 +257,17 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
     CU(cudaMemset(c->d_params, 0, pb));
     CU(cudaMemset(c->d_np, 0, sizeof(int32_t) * c->ld));
     if (f->GP) {
-        // default: one launch per block column over all lanes in flight (faster at every N
-        // measured, profiles/dev_gp_r01b.jsonl); gp_path=1 keeps the CTA-per-particle walk
-        c->gp.blocked = c->gp_path_opt ? (c->gp_path_opt == 2) : 1;
-        int slots;
-        if (c->gp.blocked) {
-            c->gp.slot_doubles = kc::gpb_slot_doubles(c->N);
-            const size_t cap = (size_t)64 << 30;  // factor storage budget out of 180 GB
-            size_t fit = cap / (sizeof(double) * c->gp.slot_doubles);
-            slots = c->gp_slots_opt > 0 ? c->gp_slots_opt : (int)(fit < 1 ? 1 : (fit > (size_t)max_batch ? (size_t)max_batch : fit));
-        } else {
-            c->gp.slot_doubles = kc::gp_slot_doubles(c->N);
-            slots = c->gp_slots_opt > 0 ? c->gp_slots_opt : kc::gp_default_slots(c->N, c->sm_count);
-        }
+        // factor storage for as many lanes in flight as fit the budget; more lanes than
+        // slots run in waves
+        c->gp.slot_doubles = kc::gpb_slot_doubles(c->N);
+        const size_t cap = (size_t)64 << 30;  // out of 180 GB
+        size_t fit = cap / (sizeof(double) * c->gp.slot_doubles);
+        if (fit < 1) fit = 1;
+        int slots = c->gp_slots_opt > 0 ? c->gp_slots_opt : (int)(fit > (size_t)max_batch ? (size_t)max_batch : fit);
         if (slots > max_batch) slots = max_batch;
         c->gp.slots = slots;
         CU(cudaMalloc(&c->gp.ws, sizeof(double) * c->gp.slot_doubles * slots));
-        if (c->gp.blocked) {
-            CU(cudaMalloc((void**)&c->gp.lanes, kc::gpb_lane_bytes() * slots));
-            CU(cudaMalloc((void**)&c->gp.stagger, sizeof(int) * 1024));
-            CU(cudaMemset(c->gp.stagger, 0, sizeof(int) * 1024));
-        }
+        CU(cudaMalloc((void**)&c->gp.lanes, kc::gpb_lane_bytes() * slots));
     }
     c->configured = true;
     return KC_OK;
@@ -383,12 +370,8 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
     if (k == "kepler_mode") {
         if (value != 0 && value != 1) return fail(KC_ERR_ARG, "kepler_mode must be 0 or 1");
         c->kepler_mode = value;
-    } else if (k == "gp_path") {
-        if (value < 0 || value > 2) return fail(KC_ERR_ARG, "gp_path must be 0 (auto), 1 (cta) or 2 (blocked)");
-        c->gp_path_opt = value;  // takes effect at the next kc_configure
-    } else if (k == "gp_stagger") {
-        if (value < 0 || value > 400) return fail(KC_ERR_ARG, "gp_stagger is a percentage in [0, 400]");
-        c->gp.stagger_pct = value;
+    } else if (k == "gp_fuse_diag") {
+        c->gp.fuse_diag = value ? 1 : 0;
     } else if (k == "gp_slots") {
         if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
         c->gp_slots_opt = value;  // takes effect at the next kc_configure

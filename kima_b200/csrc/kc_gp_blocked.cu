@@ -43,6 +43,7 @@ constexpr int H_LD = 34;      // 32x32 half-block buffers of the diag kernel
 constexpr int D_STAGE_DOUBLES = KC * B_LD;
 constexpr int D_SMEM_DOUBLES = D_STAGES * D_STAGE_DOUBLES + NB * S_LD;
 static_assert(2 * 32 * H_LD <= D_STAGES * D_STAGE_DOUBLES, "half-block buffers alias the diag pipeline");
+static_assert(D_SMEM_DOUBLES <= PIPE_DOUBLES, "the fused diagonal block reuses the update pipeline");
 constexpr int PAD_DOUBLES = 256;  // tiles may read (never use) up to R rows past the last column
 }  // namespace gpb
 
@@ -58,6 +59,10 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N_>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+
+// Barrier over the 128 threads (warps 0-3) that factor a diagonal block, whether they are
+// the whole diag CTA or half of an update CTA.
+__device__ __forceinline__ void bar_diag() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 // ---- prep: per-lane constants + the residual row ------------------------------------------
 template <int MODE>
@@ -116,9 +121,13 @@ gpb_prep_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
 __device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, int nvalid,
                                                      double& logdet, double* dinv_out,
                                                      double* __restrict__ Lout, size_t ld,
-                                                     double* LT, int lt_ld)
+                                                     double* LT, int lt_ld, double* colbuf)
 {
+    // colbuf: [2][64] doubles of shared memory; the finished column is broadcast through it
+    // (written twice, 32 apart, so that L(c+k, c) is colbuf[c+k] without wrap-around;
+    // double-buffered by the parity of c: one __syncwarp per column)
     bool ok = true;
+    double lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant
 #pragma unroll 1
     for (int c = 0; c < 32; c++) {
         const double d = __shfl_sync(0xffffffffu, s[0], c);
@@ -134,18 +143,34 @@ __device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, 
         y = kfma(y, e, y);
         l = kfma(kfma(-l, l, d), 0.5 * y, l);
         const double inv = y;
-        if (c < nvalid) logdet += log(l);
+        if (lane == c) lmine = l;
         if (lane == 0) dinv_out[c] = inv;
         const double lrc = s[0] * inv;
+        double* cb = colbuf + (c & 1) * 64;
+        cb[lane] = lrc;
+        cb[lane + 32] = lrc;
         if (lane >= c && lane < nvalid) Lout[(size_t)c * ld + lane] = (lane == c) ? l : lrc;
         if (LT) LT[c * lt_ld + lane] = (lane > c) ? lrc : 0.0;
+        __syncwarp();
+        const double* col = cb + c;
+        // all 31 loads first, then the 31 FMAs: left alone the compiler pairs each load with
+        // its FMA through one register and the step costs 31 shared-memory latencies
+        double cv[32];
 #pragma unroll
-        for (int k = 1; k < 32; k++) {
-            const double lc2 = __shfl_sync(0xffffffffu, lrc, (c + k) & 31);  // L(c+k, c)
-            s[k - 1] = kfma(-lrc, lc2, s[k]);
-        }
+        for (int k = 1; k < 32; k++) cv[k] = col[k];  // col[k] = L(c+k, c)
+#pragma unroll
+        for (int k = 1; k < 32; k += 8)
+            asm volatile("" : "+d"(cv[k]), "+d"(cv[k + 1]), "+d"(cv[k + 2]), "+d"(cv[k + 3]),
+                              "+d"(cv[k + 4]), "+d"(cv[k + 5]), "+d"(cv[k + 6 < 32 ? k + 6 : 31]),
+                              "+d"(cv[k + 7 < 32 ? k + 7 : 31]));
+#pragma unroll
+        for (int k = 1; k < 32; k++) s[k - 1] = kfma(-lrc, cv[k], s[k]);
         s[31] = 0.0;
     }
+    double lg = lane < nvalid ? log(lmine) : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, o);
+    logdet += lg;
     return ok;
 }
 
@@ -180,7 +205,7 @@ __device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t 
     }
     for (int it = 0; it < nk; it++) {
         cp_async_wait<D_STAGES - 2>();
-        __syncthreads();
+        bar_diag();
         if (it + D_STAGES - 1 < nk) load_stage((it + D_STAGES - 1) % D_STAGES, it + D_STAGES - 1);
         cp_async_commit();
         const double* Bs = pipe + (it % D_STAGES) * D_STAGE_DOUBLES;
@@ -211,25 +236,24 @@ __device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t 
     }
 }
 
-__global__ void __launch_bounds__(gpb::D_THREADS, 3)
-gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                GpLane* __restrict__ lanes, int j0)
+// Factor the diagonal block that starts at column j0 (threads 0..127 of the CTA; `dsm` is
+// D_SMEM_DOUBLES of shared memory they own).  Called by the diag kernel for the first block
+// column and by the update kernel's first row tile for every later one: that CTA has just
+// produced the 64 rows of L the block needs, and folding the (latency-bound) factorisation
+// into the update launch lets the other CTA on the SM keep the FP64 pipe busy meanwhile.
+__device__ __forceinline__ void diag_block(const KParams& p, double* __restrict__ W, size_t ld,
+                                           GpLane& gl, int j0, double* dsm, int tid)
 {
     using namespace gpb;
-    extern __shared__ __align__(16) double dsm[];
     double* pipe = dsm;                                // D_STAGES x [KC][B_LD]
     double* Ss = dsm + D_STAGES * D_STAGE_DOUBLES;     // [NB][S_LD]
     double* LTs = pipe;                                // after the K loop: [32][H_LD], LTs[c][c2] = L11(c2,c)
     double* T21 = pipe + 32 * H_LD;                    // [32][H_LD]: L21 row-major
     __shared__ double dinv_s[NB];
+    __shared__ double colbuf_s[2 * 64];
     __shared__ int fail_s;
-    const int slot = blockIdx.x;
-    GpLane& gl = lanes[slot];
-    if (gl.fail) return;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int warp = tid >> 5, lane = tid & 31;
     const int N = p.N;
-    const size_t ld = ((size_t)N + 1 + 15) & ~(size_t)15;
-    double* W = ws_all + (size_t)slot * slot_doubles;
     const int nbc = min(NB, N - j0);
     if (tid == 0) fail_s = 0;
     switch (warp) {
@@ -238,7 +262,7 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
         case 2: diag_kloop<2>(W, ld, j0, pipe, Ss, tid, lane); break;
         default: diag_kloop<3>(W, ld, j0, pipe, Ss, tid, lane); break;
     }
-    __syncthreads();
+    bar_diag();
     {
         const GpConsts g = gl.c;
         const bool multi = p.F.multi_instrument != 0;
@@ -264,7 +288,7 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
             Ss[r * S_LD + cc] = v;
         }
     }
-    __syncthreads();
+    bar_diag();
 
     double logdet = 0.0;
 #pragma unroll 1
@@ -277,10 +301,10 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
             for (int c = 0; c < 32; c++) s[c] = Ss[(h0 + lane) * S_LD + h0 + c];
             if (!chol32_rows_in_lanes(s, lane, nv, logdet, dinv_s + h0,
                                       W + (size_t)(j0 + h0) * ld + j0 + h0, ld,
-                                      half == 0 ? LTs : nullptr, H_LD) && lane == 0)
+                                      half == 0 ? LTs : nullptr, H_LD, colbuf_s) && lane == 0)
                 fail_s = 1;
         }
-        __syncthreads();
+        bar_diag();
         if (half == 0) {
             if (warp == 1) {
                 // L21 = S21 L11^-T: row 32+lane, forward substitution
@@ -299,7 +323,7 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
                     if (32 + lane < nbc) W[(size_t)(j0 + c) * ld + j0 + 32 + lane] = t[c];
                 }
             }
-            __syncthreads();
+            bar_diag();
             {
                 // S22 -= L21 L21^T: warp w takes columns [8w, 8w+8), lane = row
                 double t[32];
@@ -318,21 +342,32 @@ gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
                     Ss[(32 + lane) * S_LD + 32 + c2] -= a0 + a1;
                 }
             }
-            __syncthreads();
+            bar_diag();
         }
     }
-    if (tid < NB) gl.dinv[tid] = dinv_s[tid];
+    if (tid < NB) gl.dinv[(j0 / NB) & 1][tid] = dinv_s[tid];  // double-buffered by block parity
     if (tid == 0) {
         if (fail_s) gl.fail = 1;
         else gl.logdet += logdet;
     }
 }
 
+__global__ void __launch_bounds__(gpb::D_THREADS, 3)
+gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
+                GpLane* __restrict__ lanes, int j0)
+{
+    extern __shared__ __align__(16) double dsm_k[];
+    GpLane& gl = lanes[blockIdx.x];
+    if (gl.fail) return;
+    const size_t ld = ((size_t)p.N + 1 + 15) & ~(size_t)15;
+    diag_block(p, ws_all + (size_t)blockIdx.x * slot_doubles, ld, gl, j0, dsm_k, threadIdx.x);
+}
+
+
 // ---- update: the panel below the diagonal block ----------------------------------------------
 __global__ void __launch_bounds__(CTA_THREADS, 2)
 gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                  GpLane* __restrict__ lanes, int j0, int first_row, int* __restrict__ stagger,
-                  int first_wave, long long stagger_clocks)
+                  GpLane* __restrict__ lanes, int j0, int first_row, int fuse_next)
 {
     using namespace gpb;
     extern __shared__ __align__(16) double usm[];
@@ -340,23 +375,6 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     GpLane& gl = lanes[slot];
     if (gl.fail) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    // Phase staggering.  All CTAs of a launch take the same time, so the two CTAs resident
-    // on an SM would march in lock-step: both in the DMMA loop, then both in the (latency-
-    // bound) epilogue with the FP64 pipe idle.  The second CTA to arrive on each SM in the
-    // first wave waits half a tile period once; from then on one CTA's epilogue overlaps the
-    // other's DMMA loop for the rest of the launch.
-    if (stagger_clocks > 0 && (int)(blockIdx.y * gridDim.x + blockIdx.x) < first_wave) {
-        if (tid == 0) {
-            unsigned smid;
-            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-            const int arrival = atomicAdd(stagger + smid, 1);
-            if (arrival & 1) {
-                const long long t0 = clock64();
-                while (clock64() - t0 < stagger_clocks) {}
-            }
-        }
-        __syncthreads();
-    }
     const int N = p.N;
     const size_t ld = ((size_t)N + 1 + 15) & ~(size_t)15;
     double* W = ws_all + (size_t)slot * slot_doubles;
@@ -379,7 +397,7 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         const int c = u / (NB / 2), c2 = (u % (NB / 2)) * 2;
         cp_async16(LT + c * B_LD + c2, W + (size_t)(j0 + c) * ld + j0 + c2);
     }
-    if (tid < NB / 2) cp_async16(dinv + 2 * tid, gl.dinv + 2 * tid);
+    if (tid < NB / 2) cp_async16(dinv + 2 * tid, &gl.dinv[(j0 / NB) & 1][2 * tid]);
     cp_async_commit();
 
     const int nk = j0 / KC;
@@ -538,6 +556,12 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         q += __shfl_xor_sync(0xffffffffu, q, 16);
         if (row == N && lane < 16) gl.quad += q;  // |z|^2 of this block column
     }
+    // The first row tile holds rows j0+NB .. j0+2NB-1 of L in warps 0-3: everything the next
+    // diagonal block needs.  Factor it here, inside this launch.
+    if (fuse_next && blockIdx.x == 0) {
+        __syncthreads();  // all warps are done with the S tile (the diag buffers alias it)
+        if (warp < 4) diag_block(p, W, ld, gl, j0 + NB, usm, tid);
+    }
 }
 
 __global__ void gpb_finish_kernel(const KParams p, const GpLane* __restrict__ lanes, int lane0, int n)
@@ -581,17 +605,18 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
         for (int J = 0; J < nblk; J++) {
             const int j0 = J * NB;
             const int nbc = min(NB, N - j0);
-            gpb_diag_kernel<<<n, D_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0);
+            if (J == 0 || !w.fuse_diag) {
+                gpb_diag_kernel<<<n, D_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0);
+                *n_launches += 1;
+            }
             // rows below the diagonal block, up to and including the residual row N
             const int first_row = nbc == NB ? j0 + NB : j0;
             const int ntile = (N + 1 - first_row + R - 1) / R;
             dim3 grid(ntile, n);
-            // per CTA: nk chunks of 128x64x16 DMMA work shared with one neighbour + the epilogue
-            const long long period = (long long)(j0 / KC) * 4096 + 24000;
-            const long long stag = (long long)ntile * n > 2 * sm_count ? period * w.stagger_pct / 200 : 0;
+            const int fuse_next = (w.fuse_diag && nbc == NB && j0 + NB < N) ? 1 : 0;
             gpb_update_kernel<<<grid, CTA_THREADS, usmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0,
-                                                                   first_row, w.stagger, 2 * sm_count, stag);
-            *n_launches += 2;
+                                                                   first_row, fuse_next);
+            *n_launches += 1;
         }
         gpb_finish_kernel<<<(n + 127) / 128, 128, 0, stream>>>(p, w.lanes, lane0, n);
         *n_launches += 1;

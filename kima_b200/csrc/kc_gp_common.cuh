@@ -50,7 +50,7 @@ struct GpConsts {
 
 // Per-lane state of the blocked path, living beside the factor storage in HBM.
 struct __align__(16) GpLane {
-    double dinv[64];          // 1 / diag(L_JJ) of the block column in flight (cp.async source)
+    double dinv[2][64];       // 1 / diag(L_JJ), double-buffered by block-column parity (cp.async source)
     GpConsts c;
     double jit2[KC_MAX_INST];
     double logdet, quad;

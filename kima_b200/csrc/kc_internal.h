@@ -30,7 +30,6 @@ struct KParams {
     const int32_t* np;      // [B]
     int ld, B;
     double* logL;           // [B]
-    double* resid;          // [B][N], GP only: y - mu
     int* counter;           // dynamic work counter (zeroed before launch)
 };
 
@@ -44,20 +43,12 @@ cudaError_t launch_model_mu(const KParams& p, int kepler_mode, int lane, double*
 
 struct GpLane;  // kc_gp_common.cuh
 struct GpWorkspace {
-    double* ws;          // per-slot factor storage
+    double* ws;          // per-slot factor storage (lower triangle of L + the residual row)
     size_t slot_doubles; // doubles per slot
-    int slots;
-    GpLane* lanes;       // blocked path: per-slot state
-    int blocked;         // 1 = one launch per block column over all lanes (kc_gp_blocked.cu)
-    int* stagger;        // per-SM arrival counters of the update kernel's phase staggering
-    int stagger_pct;     // 100 = half a tile period; 0 = off
+    int slots;           // lanes in flight per wave
+    GpLane* lanes;       // per-slot state
+    int fuse_diag;       // 1 = the update kernel's first row tile also factors the next diagonal block
 };
-// single-CTA-per-particle path (kc_gp.cu)
-size_t gp_slot_doubles(int N);
-int gp_default_slots(int N, int sm_count);
-cudaError_t launch_gp(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
-                      cudaStream_t stream, int* n_launches);
-// blocked path (kc_gp_blocked.cu)
 size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();
 cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,

@@ -81,6 +81,24 @@ def test_seeded_batches_vs_oracle(gpu, port, case):
     assert relerr(got, ref).max() <= LOGL_RTOL
 
 
+@pytest.mark.parametrize("N", [3, 63, 64, 65, 127, 128, 129, 191, 192, 193, 320])
+def test_gp_block_column_edges(gpu, port, N):
+    """The blocked factorisation at every alignment of N against its 64-wide block columns
+    and 128-row tiles (partial last block, residual row alone in a tile, one block only)."""
+    flags = ModelFlags(GP=True, npmax=2)
+    d = make_data(N, seed=4000 + N)
+    B = 40
+    P, nps = make_params(flags, d, B, "mix", seed=N)
+    port.set_rvdata(d)
+    port.set_flags(flags)
+    ref, _ = port.eval_batch(P, nps, nthreads=8)
+    with LikelihoodEngine(d, flags, B, gp_slots=16) as eng:   # 40 lanes in waves of 16, 16, 8
+        got = eng.evaluate(P, nps)
+        again = eng.evaluate(P, nps)
+    assert relerr(got, ref).max() <= LOGL_RTOL
+    assert np.array_equal(got, again)  # deterministic: no atomics on the data path
+
+
 def test_ragged_batches_and_reuse(gpu, port):
     """B = 1, odd sizes, reuse of one context for shrinking and growing batches."""
     flags = ModelFlags(npmax=3)
@@ -170,7 +188,7 @@ def test_full_size_gp_vs_oracle(gpu, port):
     port.set_rvdata(d)
     port.set_flags(flags)
     ref, _ = port.eval_batch(P, nps, nthreads=os.cpu_count() or 8)
-    with LikelihoodEngine(d, flags, 400) as eng:
+    with LikelihoodEngine(d, flags, 400, gp_slots=48) as eng:  # 400 lanes in waves of 48 (+16)
         got = eng.evaluate(P, nps)
         assert relerr(got, ref).max() <= LOGL_RTOL
         # more lanes than workspace slots: slots are recycled, results unchanged

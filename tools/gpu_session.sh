@@ -13,7 +13,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
    --log-file $OUT/launches.csv python bench.py --steps 2 --warmup 3 --skip-cpu-baseline > $OUT/ncu_list.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:keplerian -c 1 -s 3 \
    -o $OUT/kep_full -f python bench.py --steps 2 --warmup 3 --skip-cpu-baseline --workloads kep > $OUT/ncu_kep.log 2>&1
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:gp_ -c 1 -s 3 \
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:gpb_update -c 1 -s 40 \
    -o $OUT/gp_full -f python bench.py --steps 2 --warmup 3 --skip-cpu-baseline --workloads gp > $OUT/ncu_gp.log 2>&1
 ls -la $OUT
 tail -3 $OUT/pytest_gpu.log; cat $OUT/bench.json
