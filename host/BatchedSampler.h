@@ -1,0 +1,200 @@
+// DNest4::BatchedSampler — the reference's Sampler with its particle loop turned into
+// lock-step lanes, so that every MCMC step scores all lanes' proposals with ONE batched
+// likelihood call instead of one ModelType::log_likelihood() per thread.
+//
+// What is reused unchanged from the reference (it is the base class): the level table,
+// do_bookkeeping / kill_lagging_particles / save_particle / save_levels, the output files,
+// update_level_assignment, log_push, print/read, the Options/CommandLineOptions handling
+// (DNest4/code/Sampler.h, SamplerImpl.h:224-265, 377-637).
+// What is new: initialise() and run(), i.e. the restatement of
+//     Sampler::initialise      SamplerImpl.h:52-79
+//     Sampler::run/run_thread  SamplerImpl.h:82-131, 268-335
+//     Sampler::mcmc_thread     SamplerImpl.h:134-165
+//     Sampler::update_particle SamplerImpl.h:168-221   (split around the likelihood call)
+//
+// A lane is exactly one DNest4 "thread" (-t): its own RNG (seed + lane), its own
+// num_particles particles, its own copy of the level table between barriers.  Since
+// log_likelihood() draws no random numbers, splitting update_particle around it leaves every
+// lane's RNG stream identical to the reference thread with the same seed: `-t 4 -s 43` on
+// the CI OPTIONS reproduces the reference's golden sample.txt (tests/test_host_cpp.py).
+//
+// The Evaluator concept (host/RVmodelDevice.h is the RVmodel instance):
+//     explicit Evaluator(int max_batch);  int max_batch() const;
+//     void stage(int slot, const ModelType&);  void evaluate(int B, double* logL);
+//
+// This header must be included after Sampler.h has been included with its private section
+// opened (host/overlay/kima.h does that).
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <fstream>
+#include <iostream>
+#include <memory>
+#include <vector>
+
+namespace DNest4 {
+
+template <class ModelType, class Evaluator>
+class BatchedSampler : public Sampler<ModelType> {
+    using Base = Sampler<ModelType>;
+
+    // evaluator shared so that the sampler stays copyable (setup() returns it by value)
+    std::shared_ptr<Evaluator> evaluator;
+
+    struct LaneStep {
+        unsigned int which = 0;
+        bool particle_first = true;  // the coin of mcmc_thread (SamplerImpl.h:151)
+        bool scored = false;         // passed the prior-ratio test, proposal staged
+        int slot = -1;
+        ModelType proposal;
+    };
+    std::vector<LaneStep> lane_steps;
+    std::vector<double> logl_buf;
+
+    void ensure_evaluator()
+    {
+        if (evaluator) return;
+        const size_t total = this->particles.size();
+        const int cap = (int)std::max<size_t>(this->num_threads, std::min<size_t>(total, 8192));
+        evaluator = std::make_shared<Evaluator>(cap);
+        logl_buf.resize(cap);
+    }
+
+    // thread_steps lock-step MCMC steps of all lanes (mcmc_thread for every thread at once)
+    void mcmc_lockstep()
+    {
+        const unsigned int T = this->num_threads;
+        const unsigned int P = this->options.num_particles;
+        if (lane_steps.size() != T) lane_steps.resize(T);
+        for (unsigned int i = 0; i < this->options.thread_steps; ++i) {
+            // ---- phase A: up to the likelihood call of update_particle ------------------
+            int nb = 0;
+            for (unsigned int k = 0; k < T; ++k) {
+                RNG& rng = this->rngs[k];
+                LaneStep& st = lane_steps[k];
+                st.which = k * P + rng.rand_int(P);
+                st.particle_first = (rng.rand() <= 0.5);
+                if (!st.particle_first) this->update_level_assignment(k, st.which);
+                st.proposal = this->particles[st.which];
+                double log_H = st.proposal.perturb(rng);
+                if (log_H > 0.0) log_H = 0.0;
+                st.scored = (rng.rand() <= exp(log_H));
+                if (st.scored) {
+                    st.slot = nb++;
+                    evaluator->stage(st.slot, st.proposal);
+                }
+            }
+            // ---- one batched likelihood call for every lane that needs one --------------
+            if (nb > 0) evaluator->evaluate(nb, logl_buf.data());
+            // ---- phase B: the rest of update_particle, then level assignment ------------
+            for (unsigned int k = 0; k < T; ++k) {
+                RNG& rng = this->rngs[k];
+                LaneStep& st = lane_steps[k];
+                std::vector<Level>& lv = this->copies_of_levels[k];
+                Level& level = lv[this->level_assignments[st.which]];
+                if (st.scored) {
+                    LikelihoodType cand(logl_buf[st.slot],
+                                        this->log_likelihoods[st.which].get_tiebreaker());
+                    cand.perturb(rng);  // tiebreaker move: draws from the lane's stream
+                    if (level.get_log_likelihood() < cand) {
+                        this->particles[st.which] = st.proposal;
+                        this->log_likelihoods[st.which] = cand;
+                        level.increment_accepts(1);
+                    }
+                }
+                level.increment_tries(1);
+                for (unsigned int j = this->level_assignments[st.which]; j + 1 < lv.size(); ++j) {
+                    lv[j].increment_visits(1);
+                    if (lv[j + 1].get_log_likelihood() < this->log_likelihoods[st.which])
+                        lv[j].increment_exceeds(1);
+                    else
+                        break;
+                }
+                if (st.particle_first) this->update_level_assignment(k, st.which);
+                if (!this->enough_levels(lv) &&
+                    lv.back().get_log_likelihood() < this->log_likelihoods[st.which])
+                    this->above[k].push_back(this->log_likelihoods[st.which]);
+            }
+        }
+    }
+
+public:
+    BatchedSampler() {}
+    BatchedSampler(unsigned int num_threads, double compression, const Options& options,
+                   bool save_to_disk = true)
+        : Base(num_threads, compression, options, save_to_disk)
+    {
+    }
+
+    // Same console output and RNG consumption as Sampler::initialise; the likelihoods of
+    // the prior draws are scored in batches afterwards.
+    void initialise(unsigned int first_seed)
+    {
+        RNG& rng = this->rngs[0];
+        this->all_above.reserve(2 * this->options.new_level_interval);
+        for (auto& a : this->above) a.reserve(2 * this->options.new_level_interval);
+        std::cout << "# Seeding random number generators. First seed = ";
+        std::cout << first_seed << "." << std::endl;
+        for (RNG& r : this->rngs) r.set_seed(first_seed++);
+        const size_t n = this->particles.size();
+        std::cout << "# Generating " << n;
+        std::cout << " particle" << ((n > 1) ? ("s") : (""));
+        std::cout << " from the prior..." << std::flush;
+        std::vector<double> tiebreakers(n);
+        for (size_t i = 0; i < n; ++i) {
+            this->particles[i].from_prior(rng);
+            tiebreakers[i] = rng.rand();
+        }
+        ensure_evaluator();
+        const size_t cap = (size_t)evaluator->max_batch();
+        for (size_t i0 = 0; i0 < n; i0 += cap) {
+            const int nb = (int)std::min(cap, n - i0);
+            for (int b = 0; b < nb; ++b) evaluator->stage(b, this->particles[i0 + b]);
+            evaluator->evaluate(nb, logl_buf.data());
+            for (int b = 0; b < nb; ++b)
+                this->log_likelihoods[i0 + b] = LikelihoodType(logl_buf[b], tiebreakers[i0 + b]);
+        }
+        std::cout << "done." << std::endl;
+        this->initialise_output_files();
+    }
+
+    // Alternate lock-step MCMC and bookkeeping until max_num_saves is reached
+    // (run_thread with every "thread == 0" duty done by the one host thread).
+    void run(unsigned int thin = 1)
+    {
+        this->thin_print = thin;
+        ensure_evaluator();
+        const unsigned int T = this->num_threads;
+        while (true) {
+            for (unsigned int k = 0; k < T; ++k) this->copies_of_levels[k] = this->levels;
+            if (this->options.max_num_saves != 0 && this->count_saves != 0 &&
+                (this->count_saves % this->options.max_num_saves == 0))
+                break;
+            mcmc_lockstep();
+            const unsigned long long done = (unsigned long long)T * this->options.thread_steps;
+            this->count_mcmc_steps += done;
+            this->count_mcmc_steps_since_save += done;
+            // fold every lane's counter increments back into the master level table
+            const std::vector<Level> before = this->levels;
+            for (const auto& lv : this->copies_of_levels)
+                for (size_t j = 0; j < this->levels.size(); ++j) {
+                    this->levels[j].increment_accepts(lv[j].get_accepts() - before[j].get_accepts());
+                    this->levels[j].increment_tries(lv[j].get_tries() - before[j].get_tries());
+                    this->levels[j].increment_visits(lv[j].get_visits() - before[j].get_visits());
+                    this->levels[j].increment_exceeds(lv[j].get_exceeds() - before[j].get_exceeds());
+                }
+            for (auto& a : this->above) {
+                this->all_above.insert(this->all_above.end(), a.begin(), a.end());
+                a.clear();
+            }
+            this->do_bookkeeping();
+        }
+        std::fstream fout("sampler_state.txt", std::ios::out);
+        this->print(fout);
+        fout.close();
+    }
+
+    long long device_launches() const { return evaluator ? evaluator->launches() : 0; }
+};
+
+}  // namespace DNest4

@@ -1,0 +1,111 @@
+// Device side of RVmodel: what replaces the inline calls to calculate_mu / calculate_C /
+// log_likelihood (/root/reference/src/RVmodel.cpp:286-395, 170-216, 827-943) once the
+// sampler scores its particles in batches.
+//
+// Included from host/overlay/kima.h AFTER the reference's own headers (Data.h, RVmodel.h,
+// RVConditionalPrior.h) have been included with the access keywords opened, so this file can
+// read RVmodel's parameter members (src/RVmodel.h:44-76).  It owns no model state: a particle
+// is still an RVmodel object held by the Sampler; `stage` copies its parameters into one
+// column of libkima_cuda's pinned SoA block (include/kima_cuda.h, kc_layout).
+#pragma once
+#include <cmath>
+#include <cstdlib>
+#include <iostream>
+#include <limits>
+#include <vector>
+#include "kima_cuda.hpp"
+
+// the nine model flags every kima_setup.cpp defines (src/RVmodel.h:16-34)
+extern const bool GP, MA, hyperpriors, trend, multi_instrument, known_object, studentt;
+extern const int degree, n_known_object;
+
+namespace kima_b200 {
+
+class RVmodelEvaluator {
+public:
+    using Model = RVmodel;
+
+    explicit RVmodelEvaluator(int max_batch)
+    {
+        int device = 0;
+        if (const char* e = std::getenv("KIMA_CUDA_DEVICE")) device = std::atoi(e);
+        ctx_.reset(new kimacuda::Context(device));
+        // Data is uploaded once; the reference copies the whole singleton on every call
+        // (src/RVmodel.cpp:173,288,829)
+        const Data& d = Data::get_instance();
+        std::vector<std::vector<double>> act(d.get_actind().begin(),
+                                             d.get_actind().begin() + d.number_indicators);
+        ctx_->upload_data(d.get_t(), d.get_y(), d.get_sig(), d.get_obsi(), d.number_instruments,
+                          act, d.M0_epoch, d.get_t_middle());
+        RVmodel probe;  // the user's constructor: fix, npmax, kernel (kima_setup.cpp)
+        kc_model_flags f{};
+        f.GP = GP; f.MA = MA; f.hyperpriors = hyperpriors; f.trend = trend; f.degree = degree;
+        f.multi_instrument = multi_instrument; f.known_object = known_object;
+        f.n_known_object = n_known_object; f.studentt = studentt;
+        f.npmax = probe.npmax;
+        f.kernel = (probe.kernel == RVmodel::celerite) ? 1 : 0;
+        flags_ = f;
+        ctx_->configure(f, max_batch);
+        if (const char* e = std::getenv("KIMA_CUDA_KEPLER_MODE")) ctx_->set_option("kepler_mode", std::atoi(e));
+    }
+
+    int max_batch() const { return ctx_->max_batch(); }
+
+    // Parameters of particle `m` -> column `lane` of the staging block.
+    void stage(int lane, const RVmodel& m)
+    {
+        const kc_layout& L = ctx_->layout();
+        double* P = ctx_->params();
+        const size_t ld = (size_t)ctx_->ld();
+        auto put = [&](int row, double v) { P[(size_t)row * ld + lane] = v; };
+        const auto& comps = m.planets.get_components();
+        const int np = (int)comps.size();
+        ctx_->np()[lane] = np;
+        for (int j = 0; j < np; j++) {
+            put(L.row_P + j, comps[j][0]);   // P, or log P under hyperpriors (:357-360)
+            put(L.row_K + j, comps[j][1]);
+            put(L.row_phi + j, comps[j][2]);
+            put(L.row_ecc + j, comps[j][3]);
+            put(L.row_w + j, comps[j][4]);
+        }
+        put(L.row_vsys, m.background);
+        if (multi_instrument) {
+            for (int i = 0; i < L.n_jit; i++) put(L.row_jit + i, m.jitters[i]);
+            for (int i = 0; i < L.n_off; i++) put(L.row_off + i, m.offsets[i]);
+        } else {
+            put(L.row_jit, m.extra_sigma);
+        }
+        if (trend) {
+            put(L.row_trend + 0, m.slope);
+            put(L.row_trend + 1, m.quadr);
+            put(L.row_trend + 2, m.cubic);
+        }
+        for (int i = 0; i < L.n_beta; i++) put(L.row_beta + i, m.betas[i]);
+        if (GP) {
+            put(L.row_eta + 0, m.eta1);
+            put(L.row_eta + 1, m.eta2);
+            put(L.row_eta + 2, m.eta3);
+            put(L.row_eta + 3, m.eta4);
+        }
+        if (studentt) put(L.row_nu, m.nu);
+        for (int i = 0; i < L.n_ko; i++) {
+            put(L.row_KO_P + i, m.KO_P[i]);
+            put(L.row_KO_K + i, m.KO_K[i]);
+            put(L.row_KO_e + i, m.KO_e[i]);
+            put(L.row_KO_phi + i, m.KO_phi[i]);
+            put(L.row_KO_w + i, m.KO_w[i]);
+        }
+    }
+
+    // logL[b] for the staged lanes [0,B): exactly what RVmodel::log_likelihood() returns,
+    // +inf for a non-finite value included (src/RVmodel.cpp:938-941)
+    void evaluate(int B, double* logL) { ctx_->eval(B, logL); }
+
+    long long launches() const { return ctx_->launch_count(); }
+
+private:
+    std::unique_ptr<kimacuda::Context> ctx_;
+    kc_model_flags flags_{};
+};
+
+}  // namespace kima_b200

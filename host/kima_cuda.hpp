@@ -1,0 +1,80 @@
+// C++ face of libkima_cuda's C ABI (include/kima_cuda.h): RAII context, exceptions instead
+// of status codes.  Header-only; this is what the RVmodel / Sampler shim talks to.
+//
+// Replaces, for a whole batch of particles per call, the three private methods the reference
+// runs per particle:  RVmodel::calculate_mu / calculate_C / log_likelihood
+// (/root/reference/src/RVmodel.cpp:286-395, 170-216, 827-943).
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "kima_cuda.h"
+
+namespace kimacuda {
+
+struct Error : std::runtime_error {
+    int code;
+    Error(int c, const std::string& what) : std::runtime_error(what), code(c) {}
+};
+
+inline void check(int rc)
+{
+    if (rc != KC_OK) throw Error(rc, std::string("libkima_cuda: ") + kc_last_error());
+}
+
+// One context = one GPU = one data set + one set of model flags.  Not copyable.
+class Context {
+public:
+    explicit Context(int device = 0) { check(kc_create(device, &ctx_)); }
+    ~Context() { if (ctx_) kc_destroy(ctx_); }
+    Context(const Context&) = delete;
+    Context& operator=(const Context&) = delete;
+
+    // Data::get_t/get_y/get_sig/get_obsi/get_actind, M0_epoch, get_t_middle (src/Data.h:52-108)
+    void upload_data(const std::vector<double>& t, const std::vector<double>& y,
+                     const std::vector<double>& sig, const std::vector<int>& obsi, int n_inst,
+                     const std::vector<std::vector<double>>& actind, double M0_epoch,
+                     double t_middle)
+    {
+        const int N = (int)t.size();
+        std::vector<int32_t> ob(obsi.begin(), obsi.end());
+        std::vector<double> act;
+        for (const auto& a : actind) act.insert(act.end(), a.begin(), a.end());
+        check(kc_upload_data(ctx_, N, t.data(), y.data(), sig.data(),
+                             n_inst > 1 ? ob.data() : nullptr, n_inst, (int)actind.size(),
+                             actind.empty() ? nullptr : act.data(), M0_epoch, t_middle));
+    }
+
+    void configure(const kc_model_flags& f, int max_batch)
+    {
+        check(kc_configure(ctx_, &f, max_batch));
+        check(kc_get_layout(ctx_, &layout_));
+        check(kc_host_params(ctx_, &params_, &np_, &ld_));
+        max_batch_ = max_batch;
+    }
+
+    const kc_layout& layout() const { return layout_; }
+    int ld() const { return ld_; }
+    int max_batch() const { return max_batch_; }
+    // pinned staging block: params()[row * ld() + lane], np()[lane]
+    double* params() { return params_; }
+    int32_t* np() { return np_; }
+
+    // H2D of lanes [0,B), kernels, D2H: logL[b] as RVmodel::log_likelihood() returns it
+    void eval(int B, double* logL) { check(kc_eval(ctx_, B, logL)); }
+    void eval_async(int B, double* logL) { check(kc_eval_async(ctx_, B, logL)); }
+    void wait() { check(kc_wait(ctx_)); }
+    void set_option(const char* key, int value) { check(kc_set_option(ctx_, key, value)); }
+    long long launch_count() const { return (long long)kc_launch_count(ctx_); }
+    kc_ctx* raw() { return ctx_; }
+
+private:
+    kc_ctx* ctx_ = nullptr;
+    kc_layout layout_{};
+    double* params_ = nullptr;
+    int32_t* np_ = nullptr;
+    int ld_ = 0, max_batch_ = 0;
+};
+
+}  // namespace kimacuda
