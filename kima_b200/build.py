@@ -15,7 +15,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libkima_cuda.so")
 HOSTCHECK = os.path.join(HERE, "libkc_hostcheck.so")
 
-CU_SOURCES = ["kc_api.cu", "kc_keplerian.cu", "kc_gp.cu", "kc_gp_blocked.cu", "kc_comm.cu", "kc_peak.cu"]
+CU_SOURCES = ["kc_api.cu", "kc_keplerian.cu", "kc_gp.cu", "kc_gp_blocked.cu", "kc_gp_small.cu", "kc_comm.cu", "kc_peak.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v", "-diag-suppress", "550",
@@ -54,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + os.environ.get("KC_NVCC_EXTRA", "").split() + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed on %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -54,6 +54,7 @@ struct kc_ctx {
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
+    int gp_small_opt = 1;   // 1 = shared-memory-resident kernel whenever N fits, 0 = always blocked
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     float last_ms = 0.f;
@@ -110,7 +111,9 @@ int run_kernels(kc_ctx* c, int B, double* d_logL)
     int n = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
-    if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
+    if (c->F.GP && c->gp_small_opt && kc::gps_smem_bytes(c->N))
+        e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n);
+    else if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
     if (e != cudaSuccess) return fail_cuda(e, "kernel launch");
     CU(cudaEventRecord(c->ev1, c->stream));
@@ -372,6 +375,8 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
         c->kepler_mode = value;
     } else if (k == "gp_fuse_diag") {
         c->gp.fuse_diag = value ? 1 : 0;
+    } else if (k == "gp_small") {
+        c->gp_small_opt = value ? 1 : 0;
     } else if (k == "gp_slots") {
         if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
         c->gp_slots_opt = value;  // takes effect at the next kc_configure

@@ -113,67 +113,6 @@ gpb_prep_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
 // of ONE warp (pivot and column broadcast by shuffles, no block-wide barrier per column),
 // a row-per-lane triangular solve for L21 and a 4-warp rank-32 update in between.
 
-// Unblocked Cholesky of a 32x32 block (LLT.h:313-337) by one warp, row `lane` of the block
-// in s[0..lane].  A rolled loop over the columns: every step consumes s[0] and writes the
-// updated row shifted down by one (s[k-1] <- s[k] - L(r,c) L(c+k,c)), so all register
-// indices are static and the body stays in the instruction cache.  The finished column goes
-// to HBM (Lout(c, r) = L(r, c), column-major) and, transposed, to LT (shared) if wanted.
-__device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, int nvalid,
-                                                     double& logdet, double* dinv_out,
-                                                     double* __restrict__ Lout, size_t ld,
-                                                     double* LT, int lt_ld, double* colbuf)
-{
-    // colbuf: [2][64] doubles of shared memory; the finished column is broadcast through it
-    // (written twice, 32 apart, so that L(c+k, c) is colbuf[c+k] without wrap-around;
-    // double-buffered by the parity of c: one __syncwarp per column)
-    bool ok = true;
-    double lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant
-#pragma unroll 1
-    for (int c = 0; c < 32; c++) {
-        const double d = __shfl_sync(0xffffffffu, s[0], c);
-        if (!(d > 0.0)) ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
-        // 1/sqrt(d) from the MUFU seed + two Newton steps, sqrt(d) = d/sqrt(d) + one Heron step
-        double y = rsqrt_seed(d);
-        double hy = 0.5 * y;
-        double e = kfma(-d * y, hy, 0.5);
-        y = kfma(y, e, y);
-        hy = 0.5 * y;
-        double l = d * y;
-        e = kfma(-l, hy, 0.5);
-        y = kfma(y, e, y);
-        l = kfma(kfma(-l, l, d), 0.5 * y, l);
-        const double inv = y;
-        if (lane == c) lmine = l;
-        if (lane == 0) dinv_out[c] = inv;
-        const double lrc = s[0] * inv;
-        double* cb = colbuf + (c & 1) * 64;
-        cb[lane] = lrc;
-        cb[lane + 32] = lrc;
-        if (lane >= c && lane < nvalid) Lout[(size_t)c * ld + lane] = (lane == c) ? l : lrc;
-        if (LT) LT[c * lt_ld + lane] = (lane > c) ? lrc : 0.0;
-        __syncwarp();
-        const double* col = cb + c;
-        // all 31 loads first, then the 31 FMAs: left alone the compiler pairs each load with
-        // its FMA through one register and the step costs 31 shared-memory latencies
-        double cv[32];
-#pragma unroll
-        for (int k = 1; k < 32; k++) cv[k] = col[k];  // col[k] = L(c+k, c)
-#pragma unroll
-        for (int k = 1; k < 32; k += 8)
-            asm volatile("" : "+d"(cv[k]), "+d"(cv[k + 1]), "+d"(cv[k + 2]), "+d"(cv[k + 3]),
-                              "+d"(cv[k + 4]), "+d"(cv[k + 5]), "+d"(cv[k + 6 < 32 ? k + 6 : 31]),
-                              "+d"(cv[k + 7 < 32 ? k + 7 : 31]));
-#pragma unroll
-        for (int k = 1; k < 32; k++) s[k - 1] = kfma(-lrc, cv[k], s[k]);
-        s[31] = 0.0;
-    }
-    double lg = lane < nvalid ? log(lmine) : 0.0;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, o);
-    logdet += lg;
-    return ok;
-}
-
 // K loop of the diag kernel for the warp that owns fragment rows F0 and 7-F0 (all
 // fragment indices compile-time: 9 DMMAs per k-step, no predication), then P -> Ss.
 template <int F0>

@@ -106,4 +106,112 @@ __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// Unblocked Cholesky of a 32x32 block (LLT.h:313-337) by one warp, row `lane` of the block
+// in s[0..lane].  Rolled loops over the columns: every step consumes s[0] and writes the
+// updated row shifted down by one (s[k-1] <- s[k] - L(r,c) L(c+k,c)), so all register
+// indices are static and the body stays in the instruction cache; the window of live
+// entries narrows every 8 columns (31, 23, 15, 7).  The finished column goes to Lout
+// (Lout(c, r) = L(r, c), column-major; HBM or shared) and, transposed, to LT if wanted.
+// `progress` (shared memory, may be null): set to progress_base + c + 1 once column c and
+// 1/L(c,c) are visible, so that other warps can follow the factorisation column by column.
+// CTA-scope release store / acquire load for flags in shared memory (a __threadfence_block()
+// is a sequentially consistent MEMBAR.SC.CTA, far more than a producer/consumer flag needs).
+__device__ __forceinline__ void st_release_cta(int* p, int v)
+{
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_cta(const int* p)
+{
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+
+struct Chol32State {
+    double d, inv, l, lmine;
+    bool ok;
+};
+
+// 1/sqrt(d) from the MUFU seed + two Newton steps, sqrt(d) = d/sqrt(d) + one Heron step
+__device__ __forceinline__ void chol_pivot(double d, double& inv, double& l)
+{
+    double y = rsqrt_seed(d);
+    double hy = 0.5 * y;
+    double e = kfma(-d * y, hy, 0.5);
+    y = kfma(y, e, y);
+    hy = 0.5 * y;
+    l = d * y;
+    e = kfma(-l, hy, 0.5);
+    y = kfma(y, e, y);
+    l = kfma(kfma(-l, l, d), 0.5 * y, l);
+    inv = y;
+}
+
+template <int W>
+__device__ __forceinline__ void chol32_steps(double (&s)[32], Chol32State& st, int c_lo, int c_hi, int lane,
+                                             int nvalid, double* dinv_out, double* __restrict__ Lout,
+                                             size_t ld, double* LT, int lt_ld, double* colbuf,
+                                             int* progress, int progress_base)
+{
+#pragma unroll 1
+    for (int c = c_lo; c < c_hi; c++) {
+        if (!(st.d > 0.0)) st.ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
+        if (lane == c) st.lmine = st.l;
+        if (lane == 0) dinv_out[c] = st.inv;
+        const double lrc = s[0] * st.inv;
+        const double lcc = st.l;
+        // The next pivot is known to lane c+1 before the column is broadcast:
+        // s'[0] = s[1] - L(c+1,c)^2, the same FMA the update below performs.  Its
+        // rsqrt chain (latency-bound) then overlaps the loads + FMAs (issue-bound).
+        st.d = __shfl_sync(0xffffffffu, kfma(-lrc, lrc, s[1]), (c + 1) & 31);
+        chol_pivot(st.d, st.inv, st.l);
+        double* cb = colbuf + (c & 1) * 64;
+        cb[lane] = lrc;
+        cb[lane + 32] = lrc;
+        if (lane >= c && lane < nvalid) Lout[(size_t)c * ld + lane] = (lane == c) ? lcc : lrc;
+        if (LT) LT[c * lt_ld + lane] = (lane > c) ? lrc : 0.0;
+        __syncwarp();
+        if (progress && lane == 0) st_release_cta(progress, progress_base + c + 1);
+        const double* col = cb + c;
+        // all loads first, then the FMAs: left alone the compiler pairs each load with its
+        // FMA through one register and the step costs W shared-memory latencies
+        double cv[W + 1];
+#pragma unroll
+        for (int k = 1; k <= W; k++) cv[k] = col[k];  // col[k] = L(c+k, c)
+#pragma unroll
+        for (int k = 1; k <= W; k += 8)
+            asm volatile("" : "+d"(cv[k]), "+d"(cv[k + 1]), "+d"(cv[k + 2]), "+d"(cv[k + 3]),
+                              "+d"(cv[k + 4]), "+d"(cv[k + 5]), "+d"(cv[k + 6 <= W ? k + 6 : W]),
+                              "+d"(cv[k + 7 <= W ? k + 7 : W]));
+#pragma unroll
+        for (int k = 1; k <= W; k++) s[k - 1] = kfma(-lrc, cv[k], s[k]);
+        s[W] = 0.0;
+    }
+}
+
+__device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, int nvalid,
+                                                     double& logdet, double* dinv_out,
+                                                     double* __restrict__ Lout, size_t ld,
+                                                     double* LT, int lt_ld, double* colbuf,
+                                                     int* progress = nullptr, int progress_base = 0)
+{
+    // colbuf: [2][64] doubles of shared memory; the finished column is broadcast through it
+    // (written twice, 32 apart, so that L(c+k, c) is colbuf[c+k] without wrap-around;
+    // double-buffered by the parity of c: one __syncwarp per column)
+    Chol32State st;
+    st.ok = true;
+    st.lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant
+    st.d = __shfl_sync(0xffffffffu, s[0], 0);
+    chol_pivot(st.d, st.inv, st.l);
+    chol32_steps<31>(s, st, 0, 8, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
+    chol32_steps<23>(s, st, 8, 16, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
+    chol32_steps<15>(s, st, 16, 24, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
+    chol32_steps<7>(s, st, 24, 32, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
+    double lg = lane < nvalid ? log(st.lmine) : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, o);
+    logdet += lg;
+    return st.ok;
+}
+
 }  // namespace kc

@@ -1,0 +1,396 @@
+// Kernel family 2, small-N path: the whole GP likelihood of one particle inside one CTA,
+// the factor resident in shared memory (N <= ~208: CoRoT7-sized data sets).
+//
+// Replaces, per particle,  calculate_mu() -> calculate_C() -> log_likelihood()
+// (GP / standard-kernel branch) of the reference
+// (/root/reference/src/RVmodel.cpp:170-216, 286-375, 841-873; Eigen LLT,
+// eigen/Eigen/src/Cholesky/LLT.h:313-368).  One launch, one CTA per particle, no HBM
+// traffic beyond the particle's parameters and one double out.
+//
+// Storage: the lower triangle of C / L in packed 32-wide block columns; block column J is
+// column-major [32][ld_J] over rows 32J .. N, where row N is the residual r = y - mu (so
+// z = L^-1 r falls out of the factorisation as row N of L and r^T C^-1 r = |z|^2).
+//
+// Warp roles (12 warps in one CTA per SM; 6 or 4 warps in 2 or 3 CTAs per SM when the factor is
+// small enough, so that the serial chains of several particles overlap):
+//   warp 0      "diag": the 32x32 Cholesky of each diagonal block, rows in lanes
+//               (chol32_rows_in_lanes) -- a serial chain of N column steps, the critical path
+//   warps 1..   "workers", left-looking per block column J:
+//       U_J  S[:,J] = C[:,J] - L[:,0:j0] L[J,0:j0]^T   8x32 strips on the FP64 tensor cores
+//       T_J  X = S L_JJ^-T                              a row per lane, forward substitution
+//     and, whenever they would wait for the diag warp, they generate covariance entries of
+//     later block columns from a shared work queue: the generation (the largest consumer of
+//     issue slots at this size) hides under the factorisation chain.
+#include "kc_model.cuh"
+#include "kc_gp_common.cuh"
+#ifdef KC_GPS_PROFILE
+#include <cstdio>
+#endif
+
+namespace kc {
+
+namespace gps {
+constexpr int T = 32;
+constexpr int REGS_PER_THREAD = 168;  // 1 x 12, 2 x 6 or 3 x 4 warps fill the register file
+constexpr int MAXBLK = 8;
+constexpr int GW = 2;              // columns per generation item (one qp_kernel2 call per lane)
+constexpr int GQ = T / GW;         // generation items per 32x32 tile
+constexpr int SLACK = 64;          // doubles past the last block column (strips read, never use, rows > N)
+constexpr size_t SMEM_LIMIT = 227 * 1024;
+
+struct Hdr {
+    PlanetInv inv[MAX_PLANETS];
+    ParticleScalars sc;
+    GpConsts g;
+    double dinv[T];
+    double colbuf[128];
+    double quad;
+    int base[MAXBLK];
+    int ld[MAXBLK];
+    int gen_end[MAXBLK];
+    int gen_next, u_done, d_done, col_done;
+};
+
+__host__ __device__ inline int ld_for(int rows) { return ((rows + 11) & ~15) + 4; }  // >= rows, = 4 mod 16
+__host__ __device__ inline int npad(int N) { return (N + 15) & ~15; }
+__host__ __device__ inline size_t hdr_bytes() { return (sizeof(Hdr) + 15) & ~(size_t)15; }
+}  // namespace gps
+
+// Bytes of dynamic shared memory the small path needs for N epochs (0 = does not fit).
+size_t gps_smem_bytes(int N)
+{
+    using namespace gps;
+    const int nb = (N + T - 1) / T;
+    if (nb > MAXBLK) return 0;
+    size_t d = 2 * (size_t)npad(N) + SLACK;
+    for (int J = 0; J < nb; J++) d += (size_t)T * ld_for(N + 1 - T * J);
+    size_t bytes = hdr_bytes() + d * sizeof(double);
+    return bytes <= SMEM_LIMIT ? bytes : 0;
+}
+
+namespace {
+
+using namespace gps;
+
+template <int NW>
+__device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"((NW - 1) * 32) : "memory"); }
+// warp-uniform read of a flag / counter in shared memory
+__device__ __forceinline__ int ld_uniform(const int* p, int lane)
+{
+    int v = 0;
+    if (lane == 0) v = ld_acquire_cta(p);
+    return __shfl_sync(0xffffffffu, v, 0);
+}
+
+// One generation item: rows 32I .. 32I+31 (a row per lane) x 8 columns of block column J.
+__device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS, double* M,
+                                         int N, int item, int nb, int lane)
+{
+    int J = 0;
+    while (item >= H.gen_end[J]) J++;
+    const int local = item - (J ? H.gen_end[J - 1] : 0);
+    const int I = J + local / GQ, q = local % GQ;
+    const int j0 = T * J;
+    const int row = T * I + lane;
+    const int c0 = j0 + GW * q;
+    const bool row_ok = row < N;
+    const double trow = tS[row_ok ? row : N - 1];
+    double* dst = M + H.base[J] + (size_t)(GW * q) * H.ld[J] + (row - j0);
+    const int ldj = H.ld[J];
+    const GpConsts g = H.g;
+#pragma unroll 1
+    for (int cc = 0; cc < GW; cc += 2) {
+        const int ca = c0 + cc, cb = ca + 1;
+        // t[i]-t[j] with i<j (:193): i is the column (smaller index) of the lower triangle
+        const double ta = tS[ca < N ? ca : N - 1], tb = tS[cb < N ? cb : N - 1];
+        double va, vb;
+        qp_kernel2(g, kadd(ta, -trow), kadd(tb, -trow), va, vb);
+        if (row_ok) {
+            // eta1^2 * exp(-0 - 0) + sig^2 + jit^2 on the diagonal (:199-206)
+            if (ca == row) va = kadd(g.eta1sq, nS[row]);
+            if (cb == row) vb = kadd(g.eta1sq, nS[row]);
+            if (ca <= row && ca < N) dst[(size_t)cc * ldj] = va;
+            if (cb <= row && cb < N) dst[(size_t)(cc + 1) * ldj] = vb;
+        }
+    }
+}
+
+__device__ __forceinline__ int claim(Hdr& H, int lane)
+{
+    int it = 0;
+    if (lane == 0) it = atomicAdd(&H.gen_next, 1);
+    return __shfl_sync(0xffffffffu, it, 0);
+}
+
+// U_J for one 8-row strip: S -= L[strip, 0:j0] L[J, 0:j0]^T, accumulated in registers over
+// all earlier block columns, one read-modify-write of the strip at the end.  8 rows (one
+// fragment row) per item: at these sizes the number of items per step, not the operand
+// reuse, decides how many of the four tensor pipes are busy.
+__device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int J, int strip, int lane)
+{
+    const int j0 = T * J;
+    const int r0 = j0 + 8 * strip;
+    double acc[4][2];
+#pragma unroll
+    for (int n = 0; n < 4; n++) acc[n][0] = acc[n][1] = 0.0;
+    for (int Jk = 0; Jk < J; Jk++) {
+        const int ldk = H.ld[Jk];
+        const double* Acol = M + H.base[Jk] + (r0 - T * Jk) + (lane >> 2) + (size_t)(lane & 3) * ldk;
+        const double* Bcol = M + H.base[Jk] + (j0 - T * Jk) + (lane >> 2) + (size_t)(lane & 3) * ldk;
+#pragma unroll
+        for (int k4 = 0; k4 < T; k4 += 4) {
+            double bf[4];
+            const double af = Acol[(size_t)k4 * ldk];
+#pragma unroll
+            for (int n = 0; n < 4; n++) bf[n] = Bcol[(size_t)k4 * ldk + 8 * n];
+#pragma unroll
+            for (int n = 0; n < 4; n++) dmma(acc[n][0], acc[n][1], af, bf[n]);
+        }
+    }
+    double* S = M + H.base[J];
+    const int ldj = H.ld[J];
+    const int row = r0 + (lane >> 2);
+    if (row <= N) {
+#pragma unroll
+        for (int n = 0; n < 4; n++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                double* q = S + (size_t)(8 * n + 2 * (lane & 3) + h) * ldj + (row - j0);
+                *q -= acc[n][h];
+            }
+    }
+}
+
+// T_J for 32 rows below the diagonal block: row per lane, X L_JJ^T = S in place.  Rolled
+// loops over the columns with a rotating register window (x[k] holds element c+k at step c),
+// so register indices stay static and the body stays in the instruction cache; the window
+// narrows from 31 to 15 for the second half of the columns.
+template <int W>
+__device__ __forceinline__ void trsm_steps(double (&x)[T], const double* S, int ldj, int c_lo, int c_hi,
+                                           const double* dinv, double* mine, bool ok, double& q,
+                                           const int* col_done, int need0, int& seen, int lane)
+{
+#pragma unroll 1
+    for (int c = c_lo; c < c_hi; c++) {
+        // follow the diag warp column by column: column c of L_JJ and 1/L(c,c) are published
+        if (seen < need0 + c + 1) {
+            while ((seen = ld_uniform(col_done, lane)) < need0 + c + 1) __nanosleep(20);
+        }
+        const double x0 = x[0] * dinv[c];
+        if (ok) mine[(size_t)c * ldj] = x0;
+        q = kfma(x0, x0, q);
+        const double* lc = S + (size_t)c * ldj + c;  // lc[k] = L_JJ(c+k, c)
+        double lv[W + 1];
+#pragma unroll
+        for (int k = 1; k <= W; k++) lv[k] = lc[k];
+#pragma unroll
+        for (int k = 1; k <= W; k++) x[k - 1] = kfma(-x0, lv[k], x[k]);
+        x[W] = 0.0;
+    }
+}
+
+__device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int nbc, int tile, int lane)
+{
+    const int j0 = T * J;
+    const int row = j0 + nbc + T * tile + lane;
+    const bool ok = row <= N;
+    const int ldj = H.ld[J];
+    double* S = M + H.base[J];
+    double* mine = S + (ok ? row - j0 : nbc);
+    double x[T];
+#pragma unroll
+    for (int c = 0; c < T; c++) x[c] = mine[(size_t)c * ldj];
+    double q = 0.0;
+    int seen = 0;
+    trsm_steps<31>(x, S, ldj, 0, min(nbc, 8), H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
+    trsm_steps<23>(x, S, ldj, 8, min(nbc, 16), H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
+    trsm_steps<15>(x, S, ldj, 16, min(nbc, 24), H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
+    trsm_steps<7>(x, S, ldj, 24, nbc, H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
+    if (ok && row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
+}
+
+// NW warps per CTA (1 diag + NW-1 workers); 12 / NW CTAs share an SM when the factor is small
+// enough, so that the serial chains of several particles overlap.
+template <int MODE, int NW>
+__global__ void __launch_bounds__(NW * 32, 12 / NW) gps_kernel(const KParams p)
+{
+    constexpr int THREADS = NW * 32;
+    constexpr int WORKERS = NW - 1;
+    extern __shared__ __align__(16) unsigned char gps_smem[];
+    Hdr& H = *reinterpret_cast<Hdr*>(gps_smem);
+    const int N = p.N;
+    const int NP = npad(N);
+    double* tS = reinterpret_cast<double*>(gps_smem + hdr_bytes());
+    double* nS = tS + NP;
+    double* M = nS + NP;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int b = blockIdx.x;
+    const int nb = (N + T - 1) / T;
+
+    if (warp == 0) {
+        particle_setup(p, b, H.inv, &H.sc, lane);
+        if (lane == 0) {
+            H.g = gp_consts(H.sc);
+            int off = 0, ge = 0;
+            for (int J = 0; J < nb; J++) {
+                H.base[J] = off;
+                H.ld[J] = ld_for(N + 1 - T * J);
+                off += T * H.ld[J];
+                ge += (nb - J) * GQ;
+                H.gen_end[J] = ge;
+            }
+            H.gen_next = 0; H.u_done = 0; H.d_done = 0; H.col_done = 0;
+            H.quad = 0.0;
+        }
+    }
+    __syncthreads();
+    {
+        const bool multi = p.F.multi_instrument != 0;
+        for (int i = tid; i < N; i += THREADS) {
+            tS[i] = __ldg(p.t + i);
+            const int in = multi ? __ldg(p.obsi + i) - 1 : 0;
+            nS[i] = kadd(__ldg(p.sig2 + i), H.sc.jit2[in]);
+        }
+        // residual = y - mu (:845-847) into row N of the block column that owns epoch i
+        for (int i0 = tid; i0 < N; i0 += 2 * THREADS) {
+            int i1 = i0 + THREADS;
+            const bool has1 = i1 < N;
+            if (!has1) i1 = i0;
+            const double t0 = __ldg(p.t + i0), t1 = __ldg(p.t + i1);
+            const int in0 = multi ? __ldg(p.obsi + i0) - 1 : 0;
+            const int in1 = multi ? __ldg(p.obsi + i1) - 1 : 0;
+            double mu0, mu1;
+            model_mu2<MODE>(p, &H.sc, H.inv, i0, i1, t0, t1, in0, in1, mu0, mu1);
+            {
+                const int J = i0 / T;
+                M[H.base[J] + (size_t)(i0 % T) * H.ld[J] + (N - T * J)] = __ldg(p.y + i0) - mu0;
+            }
+            if (has1) {
+                const int J = i1 / T;
+                M[H.base[J] + (size_t)(i1 % T) * H.ld[J] + (N - T * J)] = __ldg(p.y + i1) - mu1;
+            }
+        }
+    }
+    __syncthreads();
+
+    const int total_items = H.gen_end[nb - 1];
+#ifdef KC_GPS_PROFILE
+    __shared__ long long prof_t[2][MAXBLK][4];
+    const bool prof = (b == 0) && lane == 0 && warp < 2;
+    long long tp = clock64();
+#define PROF(tag)                                                                          \
+    if (prof) { long long tn = clock64(); prof_t[warp][J][tag] = tn - tp; tp = tn; }
+#else
+#define PROF(tag)
+#endif
+    double logdet = 0.0;
+    bool ok = true;
+
+    if (warp == 0) {
+        // ---- diag role ----
+        for (int J = 0; J < nb; J++) {
+            const int j0 = T * J;
+            while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(40);
+            PROF(0);
+            const int nv = min(T, N - j0);
+            const int ldj = H.ld[J];
+            double* S = M + H.base[J];
+            double s[T];
+#pragma unroll
+            for (int c = 0; c < T; c++) {
+                double v = (c == lane) ? 1.0 : 0.0;  // identity padding of a partial block
+                if (lane < nv && c <= lane) v = S[(size_t)c * ldj + lane];
+                s[c] = v;
+            }
+            if (!chol32_rows_in_lanes(s, lane, nv, logdet, H.dinv, S, (size_t)ldj, nullptr, 0, H.colbuf,
+                                      &H.col_done, T * J))
+                ok = false;
+            __syncwarp();
+            if (lane == 0) st_release_cta(&H.d_done, J + 1);
+            PROF(1);
+        }
+    } else {
+        // ---- worker role ----
+        const int wid = warp - 1;
+        for (int J = 0; J < nb; J++) {
+            const int j0 = T * J;
+            const int nbc = min(T, N - j0);
+            // every entry of block column J exists before it is updated
+            while (ld_uniform(&H.gen_next, lane) < H.gen_end[J]) {
+                const int it = claim(H, lane);
+                if (it < total_items) gen_item(H, tS, nS, M, N, it, nb, lane);
+            }
+            worker_bar<NW>();
+            PROF(0);
+            if (J > 0) {
+                const int nstrips = (N + 1 - j0 + 7) / 8;
+                for (int s = wid; s < nstrips; s += WORKERS) update_strip(H, M, N, J, s, lane);
+                worker_bar<NW>();
+            }
+            PROF(1);
+            if (wid == 0 && lane == 0) st_release_cta(&H.u_done, J + 1);
+            // T_J follows the diag warp column by column (one 32-row tile per warp); the
+            // other workers generate ahead until the block is factored
+            const int first = j0 + nbc;
+            const int ntiles = (N + 1 - first + T - 1) / T;
+            if (wid < ntiles) {
+                for (int tl = wid; tl < ntiles; tl += WORKERS) trsm_tile(H, M, N, J, nbc, tl, lane);
+            } else {
+                while (ld_uniform(&H.d_done, lane) < J + 1) {
+                    if (ld_uniform(&H.gen_next, lane) < total_items) {
+                        const int it = claim(H, lane);
+                        if (it < total_items) gen_item(H, tS, nS, M, N, it, nb, lane);
+                    } else {
+                        __nanosleep(40);
+                    }
+                }
+            }
+            PROF(2);
+            worker_bar<NW>();
+            PROF(3);
+        }
+    }
+    __syncthreads();
+#ifdef KC_GPS_PROFILE
+    if (b == 0 && tid == 0)
+        for (int J = 0; J < nb; J++)
+            printf("J%d diag: wait_u %lld chol %lld | worker: gen_pre %lld U %lld fill %lld T %lld\n", J,
+                   prof_t[0][J][0], prof_t[0][J][1], prof_t[1][J][0], prof_t[1][J][1], prof_t[1][J][2], prof_t[1][J][3]);
+#endif
+    if (tid == 0) {
+        const double pinf = __longlong_as_double(0x7ff0000000000000ll);
+        // -0.5 N log(2 pi) - 0.5 * (2 sum log L_ii) - 0.5 r^T C^-1 r   (:858-870)
+        double logL = -0.5 * N * 1.8378770664093453 - logdet - 0.5 * H.quad;
+        if (!ok || isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
+        p.logL[b] = logL;
+    }
+}
+
+}  // namespace
+
+template <int MODE, int NW>
+static cudaError_t launch_one(const KParams& p, size_t smem, cudaStream_t stream)
+{
+    cudaError_t e = cudaFuncSetAttribute(gps_kernel<MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    gps_kernel<MODE, NW><<<p.B, NW * 32, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches)
+{
+    if (p.B <= 0) return cudaSuccess;
+    const size_t smem = gps_smem_bytes(p.N);
+    if (!smem) return cudaErrorInvalidValue;
+    // CTAs per SM by shared-memory footprint (228 KB per SM, 1 KB reserved per CTA)
+    const size_t per_sm = 228 * 1024;
+    const int fit = (int)(per_sm / (smem + 1024));
+    cudaError_t e;
+    if (fit >= 3) e = kepler_mode == 0 ? launch_one<0, 4>(p, smem, stream) : launch_one<1, 4>(p, smem, stream);
+    else if (fit == 2) e = kepler_mode == 0 ? launch_one<0, 6>(p, smem, stream) : launch_one<1, 6>(p, smem, stream);
+    else e = kepler_mode == 0 ? launch_one<0, 12>(p, smem, stream) : launch_one<1, 12>(p, smem, stream);
+    *n_launches += 1;
+    return e;
+}
+
+}  // namespace kc

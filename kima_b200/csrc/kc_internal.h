@@ -53,6 +53,9 @@ size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();
 cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
                               cudaStream_t stream, int* n_launches);
+// small-N path (kc_gp_small.cu): shared-memory-resident, one CTA per particle
+size_t gps_smem_bytes(int N);  // 0 = N does not fit
+cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches);
 cudaError_t launch_gp_cov(const KParams& p, int lane, double* C, cudaStream_t s);
 
 // The communicator state of a context, as kc_comm.cu sees it.

@@ -93,10 +93,37 @@ def test_gp_block_column_edges(gpu, port, N):
     port.set_flags(flags)
     ref, _ = port.eval_batch(P, nps, nthreads=8)
     with LikelihoodEngine(d, flags, B, gp_slots=16) as eng:   # 40 lanes in waves of 16, 16, 8
+        eng.set_option("gp_small", 0)                         # the blocked path at every N
         got = eng.evaluate(P, nps)
         again = eng.evaluate(P, nps)
     assert relerr(got, ref).max() <= LOGL_RTOL
     assert np.array_equal(got, again)  # deterministic: no atomics on the data path
+
+
+@pytest.mark.parametrize("N", [2, 3, 31, 32, 33, 64, 65, 95, 96, 97, 160, 161, 177, 192, 208, 211, 212])
+def test_gp_small_path_edges(gpu, port, N):
+    """The shared-memory-resident kernel (one CTA per particle, N <= 211) at every alignment of
+    N against its 32-wide block columns, 16-row update strips and 32-row substitution tiles;
+    N = 212 is the first size that no longer fits and must take the blocked path.  Both paths
+    against the oracle and against each other."""
+    flags = ModelFlags(GP=True, npmax=2, multi_instrument=(N % 2 == 0 and N > 8))
+    d = make_data(N, 3 if flags.multi_instrument else 1, seed=7000 + N)
+    B = 200  # more CTAs than SMs
+    P, nps = make_params(flags, d, B, "mix", seed=N)
+    port.set_rvdata(d)
+    port.set_flags(flags)
+    ref, _ = port.eval_batch(P, nps, nthreads=8)
+    with LikelihoodEngine(d, flags, B) as eng:
+        n0 = eng.launch_count()
+        got = eng.evaluate(P, nps)
+        launches = eng.launch_count() - n0
+        again = eng.evaluate(P, nps)
+        eng.set_option("gp_small", 0)
+        blocked = eng.evaluate(P, nps)
+    assert (launches == 1) == (N <= 211)   # one launch for the whole likelihood
+    assert relerr(got, ref).max() <= LOGL_RTOL
+    assert np.array_equal(got, again)
+    assert relerr(got, blocked).max() <= LOGL_RTOL
 
 
 def test_ragged_batches_and_reuse(gpu, port):
