@@ -20,17 +20,23 @@
 //
 // The Evaluator concept (host/RVmodelDevice.h is the RVmodel instance):
 //     explicit Evaluator(int max_batch);  int max_batch() const;
-//     void stage(int slot, const ModelType&);  void evaluate(int B, double* logL);
+//     void stage(int slot, const ModelType&);  void evaluate(int B, double* logL);   (group 0, blocking)
+//     void strip(ModelType&);   (drop per-particle host state only the CPU likelihood needs)
+//     void stage(int g, int slot, const ModelType&);  void submit(int g, int B, double* logL);  void wait(int g);
 //
 // This header must be included after Sampler.h has been included with its private section
 // opened (host/overlay/kima.h does that).
 #pragma once
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <fstream>
 #include <iostream>
 #include <memory>
+#include <thread>
 #include <vector>
+#include "LanePool.h"
 
 namespace DNest4 {
 
@@ -49,7 +55,15 @@ class BatchedSampler : public Sampler<ModelType> {
         ModelType proposal;
     };
     std::vector<LaneStep> lane_steps;
-    std::vector<double> logl_buf;
+    std::vector<double> logl_buf;            // initialise(): one batch
+    std::vector<double> logl_grp[2];         // run(): one buffer per lane group
+    std::shared_ptr<kima_b200::LanePool> pool;
+    // wall-clock split of run(), printed at the end when KIMA_PROFILE is set
+    double prof[6] = {0, 0, 0, 0, 0, 0};  // perturb, stage, submit, wait, phase B, bookkeeping
+    static double now()
+    {
+        return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    }
 
     void ensure_evaluator()
     {
@@ -58,18 +72,21 @@ class BatchedSampler : public Sampler<ModelType> {
         const int cap = (int)std::max<size_t>(this->num_threads, std::min<size_t>(total, 8192));
         evaluator = std::make_shared<Evaluator>(cap);
         logl_buf.resize(cap);
+        for (auto& v : logl_grp) v.resize(cap);
+        int nt = (int)std::thread::hardware_concurrency();
+        if (const char* e = std::getenv("KIMA_HOST_THREADS")) nt = std::atoi(e);
+        pool = std::make_shared<kima_b200::LanePool>(std::max(1, std::min(nt, 64)));
     }
 
-    // thread_steps lock-step MCMC steps of all lanes (mcmc_thread for every thread at once)
-    void mcmc_lockstep()
+    // update_particle up to its likelihood call, for the lanes [k0, k1) of group g:
+    // choose the particle, the coin, perturb, prior-ratio test; then stage the survivors
+    // in lane order (so the batch does not depend on the number of host threads).
+    int phase_a(int g, unsigned int k0, unsigned int k1)
     {
-        const unsigned int T = this->num_threads;
         const unsigned int P = this->options.num_particles;
-        if (lane_steps.size() != T) lane_steps.resize(T);
-        for (unsigned int i = 0; i < this->options.thread_steps; ++i) {
-            // ---- phase A: up to the likelihood call of update_particle ------------------
-            int nb = 0;
-            for (unsigned int k = 0; k < T; ++k) {
+        double t0 = now();
+        pool->run((int)k0, (int)k1, [&](int a, int b) {
+            for (int k = a; k < b; ++k) {
                 RNG& rng = this->rngs[k];
                 LaneStep& st = lane_steps[k];
                 st.which = k * P + rng.rand_int(P);
@@ -79,22 +96,33 @@ class BatchedSampler : public Sampler<ModelType> {
                 double log_H = st.proposal.perturb(rng);
                 if (log_H > 0.0) log_H = 0.0;
                 st.scored = (rng.rand() <= exp(log_H));
-                if (st.scored) {
-                    st.slot = nb++;
-                    evaluator->stage(st.slot, st.proposal);
-                }
             }
-            // ---- one batched likelihood call for every lane that needs one --------------
-            if (nb > 0) evaluator->evaluate(nb, logl_buf.data());
-            // ---- phase B: the rest of update_particle, then level assignment ------------
-            for (unsigned int k = 0; k < T; ++k) {
+        });
+        double t1 = now();
+        prof[0] += t1 - t0;
+        int nb = 0;
+        for (unsigned int k = k0; k < k1; ++k) lane_steps[k].slot = lane_steps[k].scored ? nb++ : -1;
+        pool->run((int)k0, (int)k1, [&](int a, int b) {
+            for (int k = a; k < b; ++k)
+                if (lane_steps[k].scored) evaluator->stage(g, lane_steps[k].slot, lane_steps[k].proposal);
+        });
+        prof[1] += now() - t1;
+        return nb;
+    }
+
+    // the rest of update_particle, then the level assignment and the `above` list
+    void phase_b(int g, unsigned int k0, unsigned int k1)
+    {
+        const double* logl = logl_grp[g].data();
+        const double t0 = now();
+        pool->run((int)k0, (int)k1, [&](int a, int b) {
+            for (int k = a; k < b; ++k) {
                 RNG& rng = this->rngs[k];
                 LaneStep& st = lane_steps[k];
                 std::vector<Level>& lv = this->copies_of_levels[k];
                 Level& level = lv[this->level_assignments[st.which]];
                 if (st.scored) {
-                    LikelihoodType cand(logl_buf[st.slot],
-                                        this->log_likelihoods[st.which].get_tiebreaker());
+                    LikelihoodType cand(logl[st.slot], this->log_likelihoods[st.which].get_tiebreaker());
                     cand.perturb(rng);  // tiebreaker move: draws from the lane's stream
                     if (level.get_log_likelihood() < cand) {
                         this->particles[st.which] = st.proposal;
@@ -115,6 +143,43 @@ class BatchedSampler : public Sampler<ModelType> {
                     lv.back().get_log_likelihood() < this->log_likelihoods[st.which])
                     this->above[k].push_back(this->log_likelihoods[st.which]);
             }
+        });
+        prof[4] += now() - t0;
+    }
+
+    void timed_wait(int g)
+    {
+        const double t0 = now();
+        evaluator->wait(g);
+        prof[3] += now() - t0;
+    }
+
+    // thread_steps lock-step MCMC steps of all lanes (mcmc_thread for every thread at once).
+    // The lanes form two groups; while the GPU scores one group's proposals the host finishes
+    // the previous step of the other group and prepares its next one.  Within a lane the
+    // order of operations, and therefore its RNG stream, is that of the reference thread.
+    void mcmc_lockstep()
+    {
+        const unsigned int T = this->num_threads;
+        if (lane_steps.size() != T) lane_steps.resize(T);
+        const unsigned int split[3] = {0, T < 2 ? T : (T + 1) / 2, T};
+        const int ngroups = T < 2 ? 1 : 2;
+        int nb[2] = {0, 0};
+        for (unsigned int i = 0; i < this->options.thread_steps; ++i) {
+            for (int g = 0; g < ngroups; ++g) {
+                if (i > 0) {
+                    if (nb[g] > 0) timed_wait(g);
+                    phase_b(g, split[g], split[g + 1]);
+                }
+                nb[g] = phase_a(g, split[g], split[g + 1]);
+                const double t0 = now();
+                if (nb[g] > 0) evaluator->submit(g, nb[g], logl_grp[g].data());
+                prof[2] += now() - t0;
+            }
+        }
+        for (int g = 0; g < ngroups; ++g) {
+            if (nb[g] > 0) timed_wait(g);
+            phase_b(g, split[g], split[g + 1]);
         }
     }
 
@@ -141,11 +206,12 @@ public:
         std::cout << " particle" << ((n > 1) ? ("s") : (""));
         std::cout << " from the prior..." << std::flush;
         std::vector<double> tiebreakers(n);
+        ensure_evaluator();
         for (size_t i = 0; i < n; ++i) {
             this->particles[i].from_prior(rng);
             tiebreakers[i] = rng.rand();
+            evaluator->strip(this->particles[i]);  // host-side state the GPU path never reads
         }
-        ensure_evaluator();
         const size_t cap = (size_t)evaluator->max_batch();
         for (size_t i0 = 0; i0 < n; i0 += cap) {
             const int nb = (int)std::min(cap, n - i0);
@@ -187,8 +253,14 @@ public:
                 this->all_above.insert(this->all_above.end(), a.begin(), a.end());
                 a.clear();
             }
+            const double tb = now();
             this->do_bookkeeping();
+            prof[5] += now() - tb;
         }
+        if (std::getenv("KIMA_PROFILE"))
+            std::cerr << "# host threads " << pool->threads() << "  perturb " << prof[0] << " s, stage " << prof[1]
+                      << " s, submit " << prof[2] << " s, wait " << prof[3] << " s, phase B " << prof[4]
+                      << " s, bookkeeping " << prof[5] << " s" << std::endl;
         std::fstream fout("sampler_state.txt", std::ios::out);
         this->print(fout);
         fout.close();

@@ -25,18 +25,17 @@ class RVmodelEvaluator {
 public:
     using Model = RVmodel;
 
+    // Two contexts on the same GPU (own stream, own pinned staging block each): while one
+    // group of lanes is being scored, the host perturbs the other (BatchedSampler.h).
+    static constexpr int GROUPS = 2;
+
     explicit RVmodelEvaluator(int max_batch)
     {
         int device = 0;
         if (const char* e = std::getenv("KIMA_CUDA_DEVICE")) device = std::atoi(e);
-        ctx_.reset(new kimacuda::Context(device));
-        // Data is uploaded once; the reference copies the whole singleton on every call
-        // (src/RVmodel.cpp:173,288,829)
         const Data& d = Data::get_instance();
         std::vector<std::vector<double>> act(d.get_actind().begin(),
                                              d.get_actind().begin() + d.number_indicators);
-        ctx_->upload_data(d.get_t(), d.get_y(), d.get_sig(), d.get_obsi(), d.number_instruments,
-                          act, d.M0_epoch, d.get_t_middle());
         RVmodel probe;  // the user's constructor: fix, npmax, kernel (kima_setup.cpp)
         kc_model_flags f{};
         f.GP = GP; f.MA = MA; f.hyperpriors = hyperpriors; f.trend = trend; f.degree = degree;
@@ -45,15 +44,38 @@ public:
         f.npmax = probe.npmax;
         f.kernel = (probe.kernel == RVmodel::celerite) ? 1 : 0;
         flags_ = f;
-        ctx_->configure(f, max_batch);
-        if (const char* e = std::getenv("KIMA_CUDA_KEPLER_MODE")) ctx_->set_option("kepler_mode", std::atoi(e));
+        for (int g = 0; g < GROUPS; g++) {
+            ctx_[g].reset(new kimacuda::Context(device));
+            // Data is uploaded once; the reference copies the whole singleton on every call
+            // (src/RVmodel.cpp:173,288,829)
+            ctx_[g]->upload_data(d.get_t(), d.get_y(), d.get_sig(), d.get_obsi(), d.number_instruments,
+                                 act, d.M0_epoch, d.get_t_middle());
+            if (const char* e = std::getenv("KIMA_CUDA_KEPLER_MODE"))
+                ctx_[g]->set_option("kepler_mode", std::atoi(e));
+            // group 0 also scores the prior draws of initialise(), so it gets the full batch
+            ctx_[g]->configure(f, g == 0 ? max_batch : (max_batch + 1) / 2);
+        }
     }
 
-    int max_batch() const { return ctx_->max_batch(); }
+    int max_batch() const { return ctx_[0]->max_batch(); }
+    int max_batch(int g) const { return ctx_[g]->max_batch(); }
+
+    // The host copies of a particle no longer need the model vector or the covariance
+    // matrix (src/RVmodel.h:84,95: N long doubles and an N x N MatrixXd, both copied with
+    // every proposal, SamplerImpl.h:184): nothing on the host reads them once calculate_mu /
+    // calculate_C / log_likelihood run on the GPU, and perturb()'s incremental updates of mu
+    // (src/RVmodel.cpp:548-804) loop over mu.size().
+    void strip(RVmodel& m) const
+    {
+        std::vector<long double>().swap(m.mu);
+        m.C.resize(0, 0);
+    }
 
     // Parameters of particle `m` -> column `lane` of the staging block.
-    void stage(int lane, const RVmodel& m)
+    void stage(int lane, const RVmodel& m) { stage(0, lane, m); }
+    void stage(int g, int lane, const RVmodel& m)
     {
+        kimacuda::Context* ctx_ = this->ctx_[g].get();
         const kc_layout& L = ctx_->layout();
         double* P = ctx_->params();
         const size_t ld = (size_t)ctx_->ld();
@@ -99,12 +121,15 @@ public:
 
     // logL[b] for the staged lanes [0,B): exactly what RVmodel::log_likelihood() returns,
     // +inf for a non-finite value included (src/RVmodel.cpp:938-941)
-    void evaluate(int B, double* logL) { ctx_->eval(B, logL); }
+    void evaluate(int B, double* logL) { ctx_[0]->eval(B, logL); }
+    // the same, split: submit returns at once, wait blocks until logL[0..B) is there
+    void submit(int g, int B, double* logL) { ctx_[g]->eval_async(B, logL); }
+    void wait(int g) { ctx_[g]->wait(); }
 
-    long long launches() const { return ctx_->launch_count(); }
+    long long launches() const { return ctx_[0]->launch_count() + ctx_[1]->launch_count(); }
 
 private:
-    std::unique_ptr<kimacuda::Context> ctx_;
+    std::unique_ptr<kimacuda::Context> ctx_[GROUPS];
     kc_model_flags flags_{};
 };
 

@@ -1,0 +1,78 @@
+"""End to end through the C++ host side: the reference's own example binaries, CPU sampler vs
+batched GPU sampler, MCMC steps per second.
+
+    steps/s = count_mcmc_steps (last field of sampler_state.txt, SamplerImpl.h:610-611) / wall time
+
+Both run the same unmodified examples/<name>/kima_setup.cpp with the same OPTIONS; the CPU
+binary with one DNest4 thread per host core, the GPU binary with `lanes` DNest4 threads (= lanes).
+"""
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+E2E = os.path.join(ROOT, "tests", "golden", "e2e")
+BUILD = os.path.join(ROOT, "host", "_build")
+DATA = {"51Peg": ["51Peg.rv"], "BL2009": ["BL2009_dataset2.kms.rv"], "CoRoT7": ["corot7.txt"],
+        "studentT": ["d1.txt"],
+        "multi_instrument": ["HD106252_ELODIE.txt", "HD106252_HET.txt", "HD106252_HJS.txt", "HD106252_Lick.txt"]}
+
+OPTIONS = """# DNest4 options for the throughput run
+2	# Number of particles
+{nli}	# new level interval
+1	# save interval
+{ts}	# threadSteps
+0	# maximum number of levels
+10	# lambda
+100	# beta
+{saves}	# Maximum number of saves
+"""
+
+
+def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=1200):
+    exe = os.path.join(BUILD, "kima_%s_%s" % (kind, name))
+    if not os.path.exists(exe):
+        return None
+    d = tempfile.mkdtemp(prefix="kima_%s_%s_" % (kind, name))
+    try:
+        for f in DATA[name]:
+            shutil.copy(os.path.join(E2E, f), d)
+        with open(os.path.join(d, "OPTIONS"), "w") as fh:
+            fh.write(OPTIONS.format(nli=max(2000, threads * thread_steps // 4), ts=thread_steps, saves=saves))
+        e = dict(os.environ)
+        e.update(env or {})
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, "-t", str(threads), "-s", str(seed)], cwd=d, capture_output=True, text=True,
+                           timeout=timeout, env=e)
+        wall = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"error": (r.stdout[-500:] + r.stderr[-500:])}
+        with open(os.path.join(d, "sampler_state.txt")) as fh:
+            steps = int(fh.read().split()[-1])
+        prof = [l for l in r.stderr.splitlines() if l.startswith("# host threads")]
+        return {"kind": kind, "example": name, "profile": prof[-1] if prof else None, "threads": threads, "thread_steps": thread_steps, "saves": saves,
+                "mcmc_steps": steps, "wall_s": wall, "steps_per_s": steps / wall}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
+def compare(name, lanes, cores, gpu_saves=20, cpu_saves=20, thread_steps=100, env=None):
+    cpu = run("cpu", name, cores, thread_steps, cpu_saves)
+    gpu = run("gpu", name, lanes, thread_steps, gpu_saves, env=env)
+    out = {"example": name, "cpu": cpu, "gpu": gpu}
+    if cpu and gpu and "steps_per_s" in cpu and "steps_per_s" in gpu:
+        out["speedup"] = gpu["steps_per_s"] / cpu["steps_per_s"]
+    return out
+
+
+if __name__ == "__main__":
+    names = sys.argv[1].split(",") if len(sys.argv) > 1 else ["CoRoT7", "51Peg"]
+    lanes = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+    cores = os.cpu_count() or 8
+    os.environ["KIMA_PROFILE"] = "1"
+    for n in names:
+        print(json.dumps(compare(n, lanes, cores, gpu_saves=40, cpu_saves=100)), flush=True)
