@@ -232,6 +232,7 @@ def main():
     ap.add_argument("--kepler-mode", type=int, default=0)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--workloads", default="kep,gp")
+    ap.add_argument("--skip-sampler", action="store_true")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -309,6 +310,15 @@ def main():
                      "kepler_mode": a.kepler_mode, "parallelism": "lanes sharded over %d GPU(s), no data-path collective" % world,
                      "l2": "flushed between timed iterations (256 MiB memset on the kernel stream)",
                      "fp64_peak_tflops_measured": peak}
+    if rank == 0 and world == 1 and not a.skip_sampler:
+        # the reference's unmodified examples end to end, MCMC steps/s of
+        # the batched GPU sampler (host/BatchedSampler.h) next to the reference's CPU sampler
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import sampler_bench
+        os.environ.setdefault("KIMA_CUDA_DEVICE", str(local))
+        out["sampler"] = {"unit": "MCMC steps/s", "lanes": 4096, "cpu_threads": threads,
+                          "runs": [sampler_bench.compare(n, 4096, threads, gpu_saves=40, cpu_saves=100)
+                                   for n in ("CoRoT7", "51Peg")]}
     if exch:
         import torch.distributed as dist
         dist.barrier()

@@ -110,6 +110,10 @@ public:
             put(L.row_eta + 3, m.eta4);
         }
         if (studentt) put(L.row_nu, m.nu);
+        if (MA) {
+            put(L.row_MA + 0, m.sigmaMA);
+            put(L.row_MA + 1, m.tauMA);
+        }
         for (int i = 0; i < L.n_ko; i++) {
             put(L.row_KO_P + i, m.KO_P[i]);
             put(L.row_KO_K + i, m.KO_K[i]);

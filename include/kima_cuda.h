@@ -28,7 +28,7 @@ extern "C" {
 #define KC_OK 0
 #define KC_ERR_ARG 1      /* bad argument / call order                        */
 #define KC_ERR_CUDA 2     /* CUDA runtime failure (see kc_last_error)         */
-#define KC_ERR_UNSUPPORTED 3 /* MA=true or kernel=celerite: out of scope      */
+#define KC_ERR_UNSUPPORTED 3 /* a flag combination the library does not implement */
 #define KC_ERR_COMM 4     /* NCCL failure                                     */
 
 #define KC_MAX_NPMAX 32   /* planets per particle held in shared memory       */
@@ -44,7 +44,7 @@ typedef struct kc_ctx kc_ctx;
  * here. */
 typedef struct kc_model_flags {
     int32_t GP;               /* extern const bool GP                         */
-    int32_t MA;               /* must be 0 (out of scope)          */
+    int32_t MA;               /* MA(1) term of calculate_mu (:378-386)        */
     int32_t hyperpriors;      /* P row holds log(P): P = exp(c[0]) (:357-360) */
     int32_t trend;
     int32_t degree;           /* 0..3                                         */
@@ -78,6 +78,7 @@ typedef struct kc_layout {
     int32_t row_nu;    /* 1 row if studentt else -1                          */
     int32_t n_ko;
     int32_t row_KO_P, row_KO_K, row_KO_e, row_KO_phi, row_KO_w; /* n_ko rows each */
+    int32_t row_MA;    /* 2 rows sigmaMA, tauMA if MA else -1                */
 } kc_layout;
 
 /* Pure function of the flags and the data shape; shared by the library, the
@@ -108,6 +109,7 @@ static inline void kc_layout_from_flags(const kc_model_flags* f, int n_inst,
     L->row_KO_e = L->n_ko ? r : -1;   r += L->n_ko;
     L->row_KO_phi = L->n_ko ? r : -1; r += L->n_ko;
     L->row_KO_w = L->n_ko ? r : -1;   r += L->n_ko;
+    L->row_MA = f->MA ? r : -1; r += f->MA ? 2 : 0;
     L->n_rows = r;
 }
 

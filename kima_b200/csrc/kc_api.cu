@@ -233,7 +233,6 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
     if (!c || !f) return fail(KC_ERR_ARG, "null argument");
     if (!c->have_data) return fail(KC_ERR_ARG, "kc_upload_data must come before kc_configure");
     if (max_batch < 1) return fail(KC_ERR_ARG, "max_batch < 1");
-    if (f->MA) return fail(KC_ERR_UNSUPPORTED, "MA=true is outside the accelerated path (SURVEY 8f3)");
     if (f->kernel != 0) return fail(KC_ERR_UNSUPPORTED, "kernel=celerite is outside the accelerated path (SURVEY 8f2)");
     if (f->npmax < 0 || f->npmax > KC_MAX_NPMAX) return fail(KC_ERR_ARG, "npmax outside [0, KC_MAX_NPMAX]");
     if (f->known_object && (f->n_known_object < 0 || f->n_known_object > KC_MAX_KO))

@@ -90,6 +90,13 @@ gpb_prep_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
         if (tid < KC_MAX_INST) lanes[slot].jit2[tid] = sc.jit2[tid];
     }
     __syncthreads();
+    if (p.F.MA) {
+        // residual with the MA(1) term (:378-386): recurrence in shared memory, then row N
+        extern __shared__ __align__(16) double ma_buf[];
+        ma_residuals<MODE>(p, &sc, inv, ma_buf, ma_buf + N, tid, CTA_THREADS);
+        for (int i = tid; i < N; i += CTA_THREADS) W[(size_t)i * ld + N] = ma_buf[i];
+        return;
+    }
     const bool multi = p.F.multi_instrument != 0;
     for (int i0 = tid; i0 < N; i0 += 2 * CTA_THREADS) {
         int i1 = i0 + CTA_THREADS;
@@ -533,13 +540,21 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
     e = cudaFuncSetAttribute(gpb_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem);
     if (e != cudaSuccess) return e;
     const int N = p.N;
+    const size_t ma_smem = p.F.MA ? 2 * sizeof(double) * (size_t)N : 0;
+    if (ma_smem > 160 * 1024) return cudaErrorInvalidValue;
+    if (ma_smem > 48 * 1024) {
+        e = cudaFuncSetAttribute(gpb_prep_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ma_smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(gpb_prep_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ma_smem);
+        if (e != cudaSuccess) return e;
+    }
     const int nblk = (N + NB - 1) / NB;
     for (int lane0 = 0; lane0 < p.B; lane0 += w.slots) {
         const int n = min(w.slots, p.B - lane0);
         if (kepler_mode == 0)
-            gpb_prep_kernel<0><<<n, CTA_THREADS, 0, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
+            gpb_prep_kernel<0><<<n, CTA_THREADS, ma_smem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
         else
-            gpb_prep_kernel<1><<<n, CTA_THREADS, 0, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
+            gpb_prep_kernel<1><<<n, CTA_THREADS, ma_smem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
         *n_launches += 1;
         for (int J = 0; J < nblk; J++) {
             const int j0 = J * NB;

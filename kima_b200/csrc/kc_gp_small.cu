@@ -252,6 +252,21 @@ __global__ void __launch_bounds__(NW * 32, 12 / NW) gps_kernel(const KParams p)
             nS[i] = kadd(__ldg(p.sig2 + i), H.sc.jit2[in]);
         }
         // residual = y - mu (:845-847) into row N of the block column that owns epoch i
+        if (p.F.MA) {
+            // with the MA(1) term (:378-386): recurrence in the (still unused) factor storage
+            __syncthreads();
+            double* rbuf = M;  // nothing of the factor storage is live yet
+            ma_residuals<MODE>(p, &H.sc, H.inv, rbuf, rbuf + NP, tid, THREADS);
+            double rv[(MAXBLK * T + THREADS - 1) / THREADS];
+            int k = 0;
+            for (int i = tid; i < N; i += THREADS) rv[k++] = rbuf[i];
+            __syncthreads();
+            k = 0;
+            for (int i = tid; i < N; i += THREADS) {
+                const int J = i / T;
+                M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = rv[k++];
+            }
+        } else
         for (int i0 = tid; i0 < N; i0 += 2 * THREADS) {
             int i1 = i0 + THREADS;
             const bool has1 = i1 < N;

@@ -29,6 +29,14 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
+// One epoch's log-likelihood term from its residual and variance.
+template <int LIK>
+__device__ __forceinline__ double loglik_term(double r, double var, double hnu1, double inv_nu)
+{
+    if (LIK == 0) return -HALF_LOG_2PI - 0.5 * log(var) - 0.5 * div_fast(r * r, var);
+    return -0.5 * log(var) - hnu1 * log1p(div_fast(r * r, var) * inv_nu);
+}
+
 // Sum of the per-epoch log-likelihood terms of this lane's epochs.
 // LIK: 0 Gaussian (:912-929), 1 Student-t (:891-910).
 template <int MODE, int LIK>
@@ -54,16 +62,8 @@ __device__ __forceinline__ double lane_loglik(const KParams& p, const ParticleSl
         double r0 = __ldg(p.y + i0) - mu0, r1 = __ldg(p.y + i1) - mu1;
         double var0 = kadd(__ldg(p.sig2 + i0), sc->jit2[in0]);
         double var1 = kadd(__ldg(p.sig2 + i1), sc->jit2[in1]);
-        double term0, term1;
-        if (LIK == 0) {
-            term0 = -HALF_LOG_2PI - 0.5 * log(var0) - 0.5 * div_fast(r0 * r0, var0);
-            term1 = -HALF_LOG_2PI - 0.5 * log(var1) - 0.5 * div_fast(r1 * r1, var1);
-        } else {
-            term0 = -0.5 * log(var0) - hnu1 * log1p(div_fast(r0 * r0, var0) * inv_nu);
-            term1 = -0.5 * log(var1) - hnu1 * log1p(div_fast(r1 * r1, var1) * inv_nu);
-        }
-        acc += term0;
-        if (has1) acc += term1;
+        acc += loglik_term<LIK>(r0, var0, hnu1, inv_nu);
+        if (has1) acc += loglik_term<LIK>(r1, var1, hnu1, inv_nu);
     }
     return acc;
 }
@@ -133,6 +133,51 @@ keplerian_cta_kernel(const KParams p)
     }
 }
 
+// ---- MA = true: a CTA per particle, the residual recurrence in shared memory ------------------
+// (:378-386).  The model without the MA term goes to shared memory as b = y - mu0 together
+// with the recurrence coefficients, one warp runs the scan (kc_model.cuh), then every thread
+// turns its epochs' residuals into likelihood terms.
+template <int MODE, int LIK>
+__global__ void __launch_bounds__(CTA_THREADS)
+keplerian_ma_kernel(const KParams p)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ParticleSlot* slot = reinterpret_cast<ParticleSlot*>(smem_raw);
+    double* rbuf = reinterpret_cast<double*>(smem_raw + ((sizeof(ParticleSlot) + 15) & ~(size_t)15));
+    double* cbuf = rbuf + p.N;
+    __shared__ double partial[CTA_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool multi = p.F.multi_instrument != 0;
+    for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
+        if (warp == 0) particle_setup(p, b, slot->inv, &slot->sc, lane);
+        __syncthreads();
+        ma_residuals<MODE>(p, &slot->sc, slot->inv, rbuf, cbuf, threadIdx.x, CTA_THREADS);
+        const double nu = slot->sc.nu;
+        const double hnu1 = 0.5 * (nu + 1.0), inv_nu = LIK == 1 ? 1.0 / nu : 0.0;
+        double acc = 0.0;
+        for (int i = threadIdx.x; i < p.N; i += CTA_THREADS) {
+            const int in = multi ? __ldg(p.obsi + i) - 1 : 0;
+            acc += loglik_term<LIK>(rbuf[i], kadd(__ldg(p.sig2 + i), slot->sc.jit2[in]), hnu1, inv_nu);
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) partial[warp] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < CTA_WARPS; w++) s += partial[w];
+            if (LIK == 1) s += studentt_const(slot->sc.nu, p.N);
+            p.logL[b] = finish(s);
+        }
+        __syncthreads();
+    }
+}
+
+static size_t ma_smem_bytes(int N)
+{
+    return ((sizeof(ParticleSlot) + 15) & ~(size_t)15) + 2 * sizeof(double) * (size_t)N;
+}
+
 template <int MODE, int LIK>
 static cudaError_t launch_variant(const KParams& p, int sm_count, cudaStream_t stream,
                                   int* n_launches)
@@ -140,7 +185,20 @@ static cudaError_t launch_variant(const KParams& p, int sm_count, cudaStream_t s
     // One warp per particle once that alone gives every SM >= 16 warps.
     const bool per_warp = p.B >= sm_count * 16;
     cudaError_t e;
-    if (per_warp) {
+    if (p.F.MA) {
+        const size_t smem = ma_smem_bytes(p.N);
+        if (smem > 227 * 1024) return cudaErrorInvalidValue;  // N > ~14000 epochs
+        auto k = keplerian_ma_kernel<MODE, LIK>;
+        e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        int per_sm = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, CTA_THREADS, smem);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) per_sm = 1;
+        int grid = sm_count * per_sm;
+        if (grid > p.B) grid = p.B;
+        k<<<grid, CTA_THREADS, smem, stream>>>(p);
+    } else if (per_warp) {
         size_t smem = sizeof(ParticleSlot) * CTA_WARPS;
         auto k = keplerian_warp_kernel<MODE, LIK>;
         e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -198,9 +256,16 @@ __global__ void true_anomaly_kernel(int n, const double* t, const double* P, con
 template <int MODE>
 __global__ void __launch_bounds__(CTA_THREADS) model_mu_kernel(const KParams p, int b, double* mu)
 {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ ParticleSlot slot;
     if (threadIdx.x < 32) particle_setup(p, b, slot.inv, &slot.sc, threadIdx.x);
     __syncthreads();
+    if (p.F.MA) {
+        double* rbuf = reinterpret_cast<double*>(smem_raw);
+        ma_residuals<MODE>(p, &slot.sc, slot.inv, rbuf, rbuf + p.N, threadIdx.x, CTA_THREADS);
+        for (int i = threadIdx.x; i < p.N; i += blockDim.x) mu[i] = p.y[i] - rbuf[i];
+        return;
+    }
     const bool multi = p.F.multi_instrument != 0;
     for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
         double t0 = p.t[i];
@@ -226,8 +291,18 @@ cudaError_t launch_true_anomaly(int n, const double* t, const double* P, const d
 }
 cudaError_t launch_model_mu(const KParams& p, int kepler_mode, int lane, double* mu, cudaStream_t s)
 {
-    if (kepler_mode == 0) model_mu_kernel<0><<<1, CTA_THREADS, 0, s>>>(p, lane, mu);
-    else model_mu_kernel<1><<<1, CTA_THREADS, 0, s>>>(p, lane, mu);
+    const size_t smem = p.F.MA ? 2 * sizeof(double) * (size_t)p.N : 0;
+    if (smem > 160 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e;
+    if (kepler_mode == 0) {
+        e = cudaFuncSetAttribute(model_mu_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        model_mu_kernel<0><<<1, CTA_THREADS, smem, s>>>(p, lane, mu);
+    } else {
+        e = cudaFuncSetAttribute(model_mu_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        model_mu_kernel<1><<<1, CTA_THREADS, smem, s>>>(p, lane, mu);
+    }
     return cudaGetLastError();
 }
 

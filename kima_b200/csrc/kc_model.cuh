@@ -13,6 +13,7 @@ namespace kc {
 struct ParticleScalars {
     double vsys, slope, quadr, cubic, nu;
     double eta1, eta2, eta3, eta4;
+    double sigmaMA, tauMA;
     double jit2[KC_MAX_INST];  // jitter^2 per instrument (index 0 = extra_sigma^2)
     double off[KC_MAX_INST];   // offsets, 0 for the last instrument
     double beta[KC_MAX_IND];
@@ -61,6 +62,10 @@ __device__ __forceinline__ void particle_setup(const KParams& p, int b, PlanetIn
         sc->quadr = p.F.trend ? ldp(p, L.row_trend + 1, b) : 0.0;
         sc->cubic = p.F.trend ? ldp(p, L.row_trend + 2, b) : 0.0;
         sc->nu = p.F.studentt ? ldp(p, L.row_nu, b) : 0.0;
+        if (p.F.MA) {
+            sc->sigmaMA = ldp(p, L.row_MA, b);
+            sc->tauMA = ldp(p, L.row_MA + 1, b);
+        }
         if (p.F.GP) {
             sc->eta1 = ldp(p, L.row_eta, b);
             sc->eta2 = ldp(p, L.row_eta + 1, b);
@@ -117,6 +122,78 @@ __device__ __forceinline__ void model_mu2(const KParams& p, const ParticleScalar
         mu0 += kepler_term<MODE>(pl, t0);
         mu1 += kepler_term<MODE>(pl, t1);
     }
+}
+
+// ---- MA(1) term of calculate_mu (:378-386) --------------------------------------------------
+// The reference walks the epochs in order:  mu[i] += sigmaMA exp(-|t[i-1]-t[i]|/tauMA) (y[i-1] - mu[i-1]),
+// mu[i-1] already updated.  In terms of the residual r = y - mu this is the first-order linear
+// recurrence  r[i] = b[i] + c[i] r[i-1]  with  b = y - mu0  (mu0: the model without the MA
+// term),  c[i] = -sigmaMA exp(-|t[i-1]-t[i]|/tauMA),  c[0] = 0.
+
+// c[i] for one epoch.
+__device__ __forceinline__ double ma_coeff(const KParams& p, const ParticleScalars* sc, int i)
+{
+    if (i == 0) return 0.0;
+    const double dt = fabs(kadd(__ldg(p.t + i - 1), -__ldg(p.t + i)));
+    return -kmul(sc->sigmaMA, exp(-kdiv(dt, sc->tauMA)));
+}
+
+// One warp turns b[0..N) into r[0..N) in place (shared memory): each lane composes the affine
+// maps of a contiguous chunk, the 32 chunk maps are combined with a shuffle scan
+// ((C2,B2) o (C1,B1) = (C2 C1, B2 + C2 B1)), then each lane replays its chunk from the
+// residual that enters it.
+__device__ __forceinline__ void ma_scan_warp(double* b, const double* c, int N, int lane)
+{
+    const int chunk = (N + 31) / 32;
+    const int lo = min(N, lane * chunk), hi = min(N, lo + chunk);
+    double C = 1.0, Bc = 0.0;
+    for (int i = lo; i < hi; i++) {
+        Bc = kfma(c[i], Bc, b[i]);
+        C = c[i] * C;
+    }
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const double Cp = __shfl_up_sync(0xffffffffu, C, o);
+        const double Bp = __shfl_up_sync(0xffffffffu, Bc, o);
+        if (lane >= o) {
+            Bc = kfma(C, Bp, Bc);
+            C = C * Cp;
+        }
+    }
+    double r = __shfl_up_sync(0xffffffffu, Bc, 1);
+    if (lane == 0) r = 0.0;
+    for (int i = lo; i < hi; i++) {
+        r = kfma(c[i], r, b[i]);
+        b[i] = r;
+    }
+}
+
+// All threads of a CTA: b = y - mu0 and c into shared memory, the scan, r left in rbuf.
+template <int MODE>
+__device__ __forceinline__ void ma_residuals(const KParams& p, const ParticleScalars* sc, const PlanetInv* inv,
+                                             double* rbuf, double* cbuf, int tid, int nthreads)
+{
+    const int N = p.N;
+    const bool multi = p.F.multi_instrument != 0;
+    for (int i0 = tid; i0 < N; i0 += 2 * nthreads) {
+        int i1 = i0 + nthreads;
+        const bool has1 = i1 < N;
+        if (!has1) i1 = i0;
+        double t0 = __ldg(p.t + i0), t1 = __ldg(p.t + i1);
+        int in0 = multi ? __ldg(p.obsi + i0) - 1 : 0;
+        int in1 = multi ? __ldg(p.obsi + i1) - 1 : 0;
+        double mu0, mu1;
+        model_mu2<MODE>(p, sc, inv, i0, i1, t0, t1, in0, in1, mu0, mu1);
+        rbuf[i0] = __ldg(p.y + i0) - mu0;
+        cbuf[i0] = ma_coeff(p, sc, i0);
+        if (has1) {
+            rbuf[i1] = __ldg(p.y + i1) - mu1;
+            cbuf[i1] = ma_coeff(p, sc, i1);
+        }
+    }
+    __syncthreads();
+    if (tid < 32) ma_scan_warp(rbuf, cbuf, N, tid);
+    __syncthreads();
 }
 
 }  // namespace kc

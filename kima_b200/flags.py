@@ -25,7 +25,7 @@ class CLayout(ctypes.Structure):
         "n_rows", "npmax", "row_P", "row_K", "row_phi", "row_ecc", "row_w",
         "row_vsys", "n_jit", "row_jit", "n_off", "row_off", "row_trend",
         "n_beta", "row_beta", "row_eta", "row_nu", "n_ko", "row_KO_P",
-        "row_KO_K", "row_KO_e", "row_KO_phi", "row_KO_w")]
+        "row_KO_K", "row_KO_e", "row_KO_phi", "row_KO_w", "row_MA")]
 
     def as_dict(self) -> dict:
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -95,5 +95,7 @@ def layout_from_flags(flags: ModelFlags, n_inst: int, n_ind: int) -> dict:
     for name in ("row_KO_P", "row_KO_K", "row_KO_e", "row_KO_phi", "row_KO_w"):
         L[name] = r if L["n_ko"] else -1
         r += L["n_ko"]
+    L["row_MA"] = r if flags.MA else -1
+    r += 2 if flags.MA else 0
     L["n_rows"] = r
     return L

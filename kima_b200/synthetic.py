@@ -93,4 +93,9 @@ def make_params(flags: ModelFlags, data: RVData, B: int, np_mode: str = "max",
     if L["n_ko"]:
         planets(L["row_KO_P"], L["row_KO_K"], L["row_KO_phi"], L["row_KO_e"],
                 L["row_KO_w"], L["n_ko"], False)
+    if flags.MA:
+        # sigmaMA ~ U(-1, 1), tauMA ~ LogUniform(1, 100)  (src/RVmodel.cpp:31-32); drawn last so
+        # that the other rows of a seeded batch do not depend on the MA flag
+        P[L["row_MA"]] = rng.uniform(-1, 1, B)
+        P[L["row_MA"] + 1] = np.exp(rng.uniform(np.log(1.0), np.log(100.0), B))
     return np.ascontiguousarray(P), nps

@@ -165,7 +165,7 @@ int ko_set_flags(const kc_model_flags* f)
 
 /* ------------------------------------------------------------------------ */
 /* RVmodel::calculate_mu, src/RVmodel.cpp:286-395 (from-scratch branch),      */
-/* add_known_object :416-432.  MA (:378-386) is out of scope.                */
+/* add_known_object :416-432, MA(1) term :378-386.                           */
 /* ------------------------------------------------------------------------ */
 #define AT(row) (params[(size_t)(row) * ld + b])
 
@@ -222,6 +222,12 @@ void ko_calculate_mu(const double* params, int ld, int b, int np, long double* m
             double v = K * (cos(f + omega) + ecc * cos(omega));
             mu[i] += v;
         }
+    }
+    if (g_flags.MA) { /* :378-386: the loop starts at the 2nd point */
+        double sigmaMA = AT(L->row_MA), tauMA = AT(L->row_MA + 1);
+        const double* y = D->y;
+        for (int i = 1; i < N; i++)
+            mu[i] += sigmaMA * exp(-fabs(t[i - 1] - t[i]) / tauMA) * (y[i - 1] - mu[i - 1]);
     }
 }
 

@@ -109,6 +109,10 @@ void set_lane(RVmodel& m, const double* params, int ld, int b, int np)
         m.eta4 = at(L.row_eta + 3);
     }
     if (g_flags.studentt) m.nu = at(L.row_nu);
+    if (g_flags.MA) {
+        m.sigmaMA = at(L.row_MA);
+        m.tauMA = at(L.row_MA + 1);
+    }
     if (L.n_ko) {
         m.KO_P.resize(L.n_ko); m.KO_K.resize(L.n_ko); m.KO_e.resize(L.n_ko);
         m.KO_phi.resize(L.n_ko); m.KO_w.resize(L.n_ko);

@@ -136,6 +136,13 @@ def main():
                                                  n_known_object=2, hyperpriors=True),
               make_data(200, 3, 2), 32, "mix", 56)
 
+    # ---- MA(1) term (src/RVmodel.cpp:378-386) ---------------------------------------------
+    save_case(ref, "synth_ma_N200", ModelFlags(npmax=3, MA=True), make_data(200), 16, "mix", 58)
+    save_case(ref, "synth_ma_studentt_multi", ModelFlags(npmax=2, MA=True, studentt=True, multi_instrument=True,
+                                                         trend=True, degree=2),
+              make_data(150, 3, 1), 16, "mix", 59)
+    save_case(ref, "synth_gp_ma_N100", ModelFlags(GP=True, npmax=2, MA=True), make_data(100), 8, "mix", 60)
+
     # ---- edge cases: extreme eccentricities / periods, non-finite outputs ----------------
     def edge(P, nps, L):
         B = P.shape[1]

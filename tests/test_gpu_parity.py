@@ -64,6 +64,12 @@ FLAG_CASES = [
     ("gp_multi_trend_ind", ModelFlags(GP=True, npmax=2, multi_instrument=True, trend=True, degree=2), 161, 3, 1),
     ("gp_ko_hyper", ModelFlags(GP=True, npmax=5, hyperpriors=True, known_object=True, n_known_object=1), 177, 1, 0),
     ("gp_257", ModelFlags(GP=True, npmax=1), 257, 1, 0),
+    ("ma", ModelFlags(npmax=3, MA=True), 300, 1, 0),
+    ("ma_1000", ModelFlags(npmax=2, MA=True), 1000, 1, 0),
+    ("ma_studentt_multi_trend_ind", ModelFlags(npmax=2, MA=True, studentt=True, multi_instrument=True,
+                                               trend=True, degree=3), 97, 3, 2),
+    ("gp_ma_small", ModelFlags(GP=True, npmax=2, MA=True), 177, 1, 0),
+    ("gp_ma_blocked", ModelFlags(GP=True, npmax=2, MA=True, multi_instrument=True), 300, 2, 0),
 ]
 
 
@@ -279,10 +285,8 @@ def test_async_and_device_resident_paths(gpu):
 def test_error_behaviour(gpu):
     d = make_data(32)
     with pytest.raises(KimaCudaError) as e:
-        LikelihoodEngine(d, ModelFlags(MA=True), 4)
-    assert e.value.code == 3  # KC_ERR_UNSUPPORTED
-    with pytest.raises(KimaCudaError):
         LikelihoodEngine(d, ModelFlags(kernel=1, GP=True), 4)
+    assert e.value.code == 3  # KC_ERR_UNSUPPORTED
     with pytest.raises(KimaCudaError):
         LikelihoodEngine(d, ModelFlags(npmax=33), 4)
     with LikelihoodEngine(d, ModelFlags(), 4) as eng:

@@ -33,11 +33,14 @@ FLAG_GRID = [
     ModelFlags(npmax=3, studentt=True, multi_instrument=True, hyperpriors=True),
     ModelFlags(GP=True, npmax=2),
     ModelFlags(GP=True, npmax=2, multi_instrument=True, trend=True, degree=2),
+    ModelFlags(npmax=2, MA=True),
+    ModelFlags(npmax=2, MA=True, studentt=True, multi_instrument=True, trend=True, degree=1),
+    ModelFlags(GP=True, npmax=2, MA=True),
 ]
 
 
 @pytest.mark.parametrize("flags", FLAG_GRID, ids=lambda f: "-".join(
-    k for k in ("GP", "hyperpriors", "trend", "multi_instrument", "known_object", "studentt") if getattr(f, k)) or "plain")
+    k for k in ("GP", "MA", "hyperpriors", "trend", "multi_instrument", "known_object", "studentt") if getattr(f, k)) or "plain")
 @pytest.mark.parametrize("shape", [(40, 1, 0), (75, 3, 2)])
 def test_port_matches_reference(port, reference, flags, shape):
     N, n_inst, n_ind = shape
