@@ -51,6 +51,7 @@ struct kc_ctx {
     int* d_counter = nullptr;
     // GP
     kc::GpWorkspace gp{nullptr, 0, 0, nullptr, 0};
+    double* d_resid = nullptr;   // kernel = celerite: residuals, [N][ld]
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
@@ -78,7 +79,8 @@ void free_model(kc_ctx* c)
     if (c->h_np) cudaFreeHost(c->h_np);
     if (c->h_logL) cudaFreeHost(c->h_logL);
     cudaFree(c->d_params); cudaFree(c->d_np); cudaFree(c->d_logL);
-    cudaFree(c->gp.ws); cudaFree(c->gp.lanes);
+    cudaFree(c->gp.ws); cudaFree(c->gp.lanes); cudaFree(c->d_resid);
+    c->d_resid = nullptr;
     c->h_params = nullptr; c->h_np = nullptr; c->h_logL = nullptr;
     c->d_params = nullptr; c->d_np = nullptr; c->d_logL = nullptr;
     c->gp = {nullptr, 0, 0, nullptr, c->gp.fuse_diag};
@@ -111,7 +113,9 @@ int run_kernels(kc_ctx* c, int B, double* d_logL)
     int n = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
-    if (c->F.GP && c->gp_small_opt && kc::gps_smem_bytes(c->N))
+    if (c->F.GP && c->F.kernel == 1)
+        e = kc::launch_gp_celerite(p, c->d_resid, c->ld, c->kepler_mode, c->stream, &n);
+    else if (c->F.GP && c->gp_small_opt && kc::gps_smem_bytes(c->N))
         e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n);
     else if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
@@ -233,7 +237,11 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
     if (!c || !f) return fail(KC_ERR_ARG, "null argument");
     if (!c->have_data) return fail(KC_ERR_ARG, "kc_upload_data must come before kc_configure");
     if (max_batch < 1) return fail(KC_ERR_ARG, "max_batch < 1");
-    if (f->kernel != 0) return fail(KC_ERR_UNSUPPORTED, "kernel=celerite is outside the accelerated path (SURVEY 8f2)");
+    if (f->kernel != 0 && f->kernel != 1) return fail(KC_ERR_ARG, "kernel must be 0 (standard) or 1 (celerite)");
+    // the reference's celerite branch reads extra_sigma, which multi_instrument leaves unset
+    // (src/RVmodel.cpp:258 against :124-127)
+    if (f->GP && f->kernel == 1 && f->multi_instrument)
+        return fail(KC_ERR_UNSUPPORTED, "kernel=celerite with multi_instrument: the reference reads an unset jitter");
     if (f->npmax < 0 || f->npmax > KC_MAX_NPMAX) return fail(KC_ERR_ARG, "npmax outside [0, KC_MAX_NPMAX]");
     if (f->known_object && (f->n_known_object < 0 || f->n_known_object > KC_MAX_KO))
         return fail(KC_ERR_ARG, "n_known_object outside [0, KC_MAX_KO]");
@@ -258,7 +266,9 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
     CU(cudaMalloc(&c->d_logL, sizeof(double) * c->ld));
     CU(cudaMemset(c->d_params, 0, pb));
     CU(cudaMemset(c->d_np, 0, sizeof(int32_t) * c->ld));
-    if (f->GP) {
+    if (f->GP && f->kernel == 1) {
+        CU(cudaMalloc(&c->d_resid, sizeof(double) * (size_t)c->N * c->ld));
+    } else if (f->GP) {
         // factor storage for as many lanes in flight as fit the budget; more lanes than
         // slots run in waves
         c->gp.slot_doubles = kc::gpb_slot_doubles(c->N);
@@ -489,7 +499,7 @@ int kc_gp_cov(kc_ctx* c, int lane, double* C)
     int rc = stage_lane(c, lane);
     if (rc) return rc;
     if (!C) return fail(KC_ERR_ARG, "C is null");
-    if (!c->F.GP) return fail(KC_ERR_ARG, "kc_gp_cov needs GP=true");
+    if (!c->F.GP || c->F.kernel != 0) return fail(KC_ERR_ARG, "kc_gp_cov needs GP=true and the standard kernel");
     double* d = nullptr;
     size_t nb = sizeof(double) * (size_t)c->N * c->N;
     CU(cudaMalloc(&d, nb));

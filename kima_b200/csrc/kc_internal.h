@@ -56,6 +56,9 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
 // small-N path (kc_gp_small.cu): shared-memory-resident, one CTA per particle
 size_t gps_smem_bytes(int N);  // 0 = N does not fit
 cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches);
+// kernel = celerite (kc_celerite.cu): resid is [N][ldr] doubles of scratch
+cudaError_t launch_gp_celerite(const KParams& p, double* resid, int ldr, int kepler_mode,
+                               cudaStream_t stream, int* n_launches);
 cudaError_t launch_gp_cov(const KParams& p, int lane, double* C, cudaStream_t s);
 
 // The communicator state of a context, as kc_comm.cu sees it.

@@ -343,6 +343,90 @@ static void ko_llt_solve(const double* A, int n, double* x)
 }
 
 /* ------------------------------------------------------------------------ */
+/* kernel = celerite: RVmodel::calculate_C :218-266 (the three complex terms of    */
+/* the quasi-periodic approximation) + celerite::solver::CholeskySolver::compute,  */
+/* dot_solve, log_determinant (celerite/cpp/include/celerite/solver/cholesky.h     */
+/* :41-209, :326-400), J = 6.  Returns dot_solve + log_det; *fail = 1 where the    */
+/* reference would throw linalg_exception (Dn < 0).                               */
+/* ------------------------------------------------------------------------ */
+#define KO_J 6
+static double ko_celerite(const double* params, int ld, int b, const double* residual, int* fail)
+{
+    const ko_data* D = &g_data;
+    const kc_layout* L = &g_layout;
+    const int N = D->N, J = KO_J;
+    const double *x = D->t, *sig = D->sig;
+    double eta1 = AT(L->row_eta), eta2 = AT(L->row_eta + 1), eta3 = AT(L->row_eta + 2);
+    double extra_sigma = AT(L->row_jit);
+    /* :231-237 */
+    double wbeat = 1 / eta2, wrot = 2 * M_PI / eta3, amp = eta1 * eta1;
+    double c = wbeat, d = wrot, xx = c / d;
+    double a = amp / 2, bb = amp * xx / 2, e = amp / 8, f = amp * xx / 4, g = amp * (3. / 8. + 0.001);
+    double a_comp[3] = {a, e, g}, b_comp[3] = {bb, f, 0.0}, c_comp[3] = {c, c, c}, d_comp[3] = {d, 2 * d, 0.0};
+    double jitter = extra_sigma * extra_sigma;
+    double asum = (a_comp[0] + a_comp[1]) + a_comp[2];
+    double S[KO_J][KO_J], W0[KO_J], W1[KO_J], phi[KO_J], u[KO_J], fv[KO_J];
+    memset(S, 0, sizeof S);
+    *fail = 0;
+    /* D_ = diag + a_real.sum() + a_comp.sum() + jitter, diag = sig^2 (:254-262, cholesky.h:95) */
+    double Dn = ((sig[0] * sig[0] + 0.0) + asum) + jitter;
+    {
+        double value = 1.0 / Dn, t = x[0];
+        for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+            double dd = d_comp[j] * t;
+            W0[k] = cos(dd) * value;
+            W0[k + 1] = sin(dd) * value;
+        }
+    }
+    for (int j = 0; j < J; j++) fv[j] = 0.0;
+    double xm1 = residual[0];
+    double result = xm1 * (xm1 / Dn); /* cholesky.h:347 */
+    double log_det = log(Dn);
+    for (int n = 1; n < N; ++n) {
+        double t = x[n], dx = t - x[n - 1];
+        for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+            double aa = a_comp[j], bq = b_comp[j], dd = d_comp[j] * t, cd = cos(dd), sd = sin(dd);
+            double value = exp(-c_comp[j] * dx);
+            phi[k] = value; phi[k + 1] = value;
+            u[k] = aa * cd + bq * sd;
+            u[k + 1] = aa * sd - bq * cd;
+            W1[k] = cd; W1[k + 1] = sd;
+        }
+        for (int j = 0; j < J; ++j) {
+            double phij = phi[j], xj = Dn * W0[j];
+            for (int k = 0; k <= j; ++k) S[k][j] = phij * (phi[k] * (S[k][j] + xj * W0[k]));
+        }
+        Dn = ((sig[n] * sig[n] + 0.0) + asum) + jitter;
+        for (int j = 0; j < J; ++j) {
+            double uj = u[j], xj = W1[j];
+            for (int k = 0; k < j; ++k) {
+                double tmp = u[k] * S[k][j];
+                Dn -= 2.0 * (uj * tmp);
+                xj -= tmp;
+                W1[k] -= uj * S[k][j];
+            }
+            double tmp = uj * S[j][j];
+            Dn -= uj * tmp;
+            W1[j] = xj - tmp;
+        }
+        if (Dn < 0) *fail = 1;
+        for (int j = 0; j < J; ++j) W1[j] /= Dn;
+        /* dot_solve, forward recursion (cholesky.h:348-357) */
+        double xv = residual[n];
+        for (int j = 0; j < J; ++j) {
+            double value = phi[j] * (fv[j] + W0[j] * xm1);
+            fv[j] = value;
+            xv -= u[j] * value;
+        }
+        xm1 = xv;
+        result += xv * xv / Dn;
+        log_det += log(Dn);
+        for (int j = 0; j < J; ++j) W0[j] = W1[j];
+    }
+    return result + log_det;
+}
+
+/* ------------------------------------------------------------------------ */
 /* RVmodel::log_likelihood, src/RVmodel.cpp:827-943                           */
 /* ------------------------------------------------------------------------ */
 typedef struct {
@@ -373,7 +457,14 @@ static double ko_log_likelihood(const double* params, int ld, int b, ko_work* w)
     const double halflog2pi = 0.5 * log(2. * M_PI); /* :20 */
     double logL = 0.;
 
-    if (g_flags.GP) { /* :841-873 */
+    if (g_flags.GP && g_flags.kernel == 1) { /* :875-882 */
+        double* residual = w->res;
+        for (int i = 0; i < N; i++) residual[i] = (double)(y[i] - mu[i]);
+        int fail = 0;
+        double s = ko_celerite(params, ld, b, residual, &fail);
+        logL = -0.5 * (s + N * log(2 * M_PI));
+        if (fail) logL = INFINITY; /* the reference throws linalg_exception out of calculate_C */
+    } else if (g_flags.GP) { /* :841-873 */
         double* residual = w->res;
         for (int i = 0; i < N; i++) residual[i] = (double)(y[i] - mu[i]);
         ko_llt_blocked(w->C, N); /* info() is never checked in the reference (:854) */
@@ -414,7 +505,7 @@ static double ko_log_likelihood(const double* params, int ld, int b, ko_work* w)
 static double ko_eval_lane(const double* params, int ld, int b, int np, ko_work* w)
 {
     ko_calculate_mu(params, ld, b, np, w->mu);
-    if (g_flags.GP) ko_calculate_C(params, ld, b, w->C);
+    if (g_flags.GP && g_flags.kernel == 0) ko_calculate_C(params, ld, b, w->C);
     return ko_log_likelihood(params, ld, b, w);
 }
 

@@ -65,7 +65,10 @@ static kc_layout g_layout;
 // The user-supplied constructor of every kima_setup.cpp
 // (e.g. examples/51Peg/kima_setup.cpp:13).  Default priors are left alone: the
 // harness never draws from them.
-RVmodel::RVmodel() : fix(g_fix), npmax(g_npmax) {}
+RVmodel::RVmodel() : fix(g_fix), npmax(g_npmax)
+{
+    kernel = g_flags.kernel ? celerite : standard;  // examples/*/kima_setup.cpp set it here
+}
 
 namespace {
 

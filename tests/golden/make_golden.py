@@ -143,6 +143,13 @@ def main():
               make_data(150, 3, 1), 16, "mix", 59)
     save_case(ref, "synth_gp_ma_N100", ModelFlags(GP=True, npmax=2, MA=True), make_data(100), 8, "mix", 60)
 
+    # ---- kernel = celerite (src/RVmodel.cpp:218-266, 875-882) --------------------------------
+    save_case(ref, "synth_celerite_N300", ModelFlags(GP=True, kernel=1, npmax=3), make_data(300), 16, "mix", 61)
+    save_case(ref, "CoRoT7_celerite", ModelFlags(GP=True, kernel=1, npmax=5, hyperpriors=True), dco, 16, "mix", 62,
+              load_info=dict(file="examples/CoRoT7/corot7.txt", units="ms", skip=2))
+    save_case(ref, "synth_celerite_ma_trend", ModelFlags(GP=True, kernel=1, npmax=2, MA=True, trend=True, degree=2),
+              make_data(120, 1, 1), 8, "mix", 63)
+
     # ---- edge cases: extreme eccentricities / periods, non-finite outputs ----------------
     def edge(P, nps, L):
         B = P.shape[1]

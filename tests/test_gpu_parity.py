@@ -69,6 +69,9 @@ FLAG_CASES = [
     ("ma_studentt_multi_trend_ind", ModelFlags(npmax=2, MA=True, studentt=True, multi_instrument=True,
                                                trend=True, degree=3), 97, 3, 2),
     ("gp_ma_small", ModelFlags(GP=True, npmax=2, MA=True), 177, 1, 0),
+    ("celerite_1000", ModelFlags(GP=True, kernel=1, npmax=3), 1000, 1, 0),
+    ("celerite_ma_trend_ind", ModelFlags(GP=True, kernel=1, npmax=2, MA=True, trend=True, degree=1, hyperpriors=True), 177, 1, 1),
+    ("celerite_tiny", ModelFlags(GP=True, kernel=1, npmax=0), 2, 1, 0),
     ("gp_ma_blocked", ModelFlags(GP=True, npmax=2, MA=True, multi_instrument=True), 300, 2, 0),
 ]
 
@@ -285,8 +288,10 @@ def test_async_and_device_resident_paths(gpu):
 def test_error_behaviour(gpu):
     d = make_data(32)
     with pytest.raises(KimaCudaError) as e:
-        LikelihoodEngine(d, ModelFlags(kernel=1, GP=True), 4)
-    assert e.value.code == 3  # KC_ERR_UNSUPPORTED
+        LikelihoodEngine(make_data(32, 2), ModelFlags(kernel=1, GP=True, multi_instrument=True), 4)
+    assert e.value.code == 3  # KC_ERR_UNSUPPORTED: the reference reads an unset jitter there
+    with pytest.raises(KimaCudaError):
+        LikelihoodEngine(d, ModelFlags(kernel=2, GP=True), 4)
     with pytest.raises(KimaCudaError):
         LikelihoodEngine(d, ModelFlags(npmax=33), 4)
     with LikelihoodEngine(d, ModelFlags(), 4) as eng:
