@@ -347,6 +347,7 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     cp_async_commit();
 
     const int nk = j0 / KC;
+    const bool warp_rows_live = r0 + wr * 32 <= N;
     auto load_stage = [&](int s, int it) {
         double* As = usm + s * STAGE_DOUBLES;
         double* Bs = As + KC * A_LD;
@@ -375,8 +376,9 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         cp_async_commit();
         const double* As = usm + (it % STAGES) * STAGE_DOUBLES;
         const double* Bs = As + KC * A_LD;
+        // a warp whose 32 rows are all past row N (partial last tile): loads and barriers only
 #pragma unroll
-        for (int k4 = 0; k4 < KC; k4 += 4) {
+        for (int k4 = 0; k4 < (warp_rows_live ? KC : 0); k4 += 4) {
             const int kk = k4 + (lane & 3);
             double af[4], bf[4];
 #pragma unroll
