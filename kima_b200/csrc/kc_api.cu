@@ -50,7 +50,7 @@ struct kc_ctx {
     double *d_logL = nullptr, *h_logL = nullptr;
     int* d_counter = nullptr;
     // GP
-    kc::GpWorkspace gp{nullptr, 0, 0, nullptr, 0};
+    kc::GpWorkspace gp{nullptr, 0, 0, nullptr};
     double* d_resid = nullptr;   // kernel = celerite: residuals, [N][ld]
     // options / instrumentation
     int kepler_mode = 0;
@@ -83,7 +83,7 @@ void free_model(kc_ctx* c)
     c->d_resid = nullptr;
     c->h_params = nullptr; c->h_np = nullptr; c->h_logL = nullptr;
     c->d_params = nullptr; c->d_np = nullptr; c->d_logL = nullptr;
-    c->gp = {nullptr, 0, 0, nullptr, c->gp.fuse_diag};
+    c->gp = {nullptr, 0, 0, nullptr};
     c->configured = false;
 }
 void free_data(kc_ctx* c)
@@ -382,8 +382,7 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
     if (k == "kepler_mode") {
         if (value != 0 && value != 1) return fail(KC_ERR_ARG, "kepler_mode must be 0 or 1");
         c->kepler_mode = value;
-    } else if (k == "gp_fuse_diag") {
-        c->gp.fuse_diag = value ? 1 : 0;
+
     } else if (k == "gp_small") {
         c->gp_small_opt = value ? 1 : 0;
     } else if (k == "gp_slots") {

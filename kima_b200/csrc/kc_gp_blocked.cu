@@ -43,9 +43,16 @@ constexpr int H_LD = 34;      // 32x32 half-block buffers of the diag kernel
 constexpr int D_STAGE_DOUBLES = KC * B_LD;
 constexpr int D_SMEM_DOUBLES = D_STAGES * D_STAGE_DOUBLES + NB * S_LD;
 static_assert(2 * 32 * H_LD <= D_STAGES * D_STAGE_DOUBLES, "half-block buffers alias the diag pipeline");
-static_assert(D_SMEM_DOUBLES <= PIPE_DOUBLES, "the fused diagonal block reuses the update pipeline");
 constexpr int PAD_DOUBLES = 256;  // tiles may read (never use) up to R rows past the last column
 }  // namespace gpb
+
+// What one block-column launch works on.
+struct GpbStep {
+    int j0;         // first column of the block column
+    int n;          // lanes (= slots) in flight
+    int first_row;  // update kernel: first row of the first tile
+    int ntile;      // update kernel: row tiles per lane
+};
 
 static size_t gpb_ld(int N) { return ((size_t)N + 1 + 15) & ~(size_t)15; }
 size_t gpb_slot_doubles(int N) { return gpb_ld(N) * (size_t)N + gpb::PAD_DOUBLES; }
@@ -300,24 +307,27 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
 
 __global__ void __launch_bounds__(gpb::D_THREADS, 3)
 gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                GpLane* __restrict__ lanes, int j0)
+                GpLane* __restrict__ lanes, const GpbStep w)
 {
     extern __shared__ __align__(16) double dsm_k[];
-    GpLane& gl = lanes[blockIdx.x];
+    const int slot = blockIdx.x;
+    GpLane& gl = lanes[slot];
     if (gl.fail) return;
     const size_t ld = ((size_t)p.N + 1 + 15) & ~(size_t)15;
-    diag_block(p, ws_all + (size_t)blockIdx.x * slot_doubles, ld, gl, j0, dsm_k, threadIdx.x);
+    diag_block(p, ws_all + (size_t)slot * slot_doubles, ld, gl, w.j0, dsm_k, threadIdx.x);
 }
 
 
 // ---- update: the panel below the diagonal block ----------------------------------------------
 __global__ void __launch_bounds__(CTA_THREADS, 2)
 gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                  GpLane* __restrict__ lanes, int j0, int first_row, int fuse_next)
+                  GpLane* __restrict__ lanes, const GpbStep w)
 {
     using namespace gpb;
     extern __shared__ __align__(16) double usm[];
+    const int j0 = w.j0, first_row = w.first_row;
     const int slot = blockIdx.y;
+    const int tile = blockIdx.x;
     GpLane& gl = lanes[slot];
     if (gl.fail) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -325,7 +335,7 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     const size_t ld = ((size_t)N + 1 + 15) & ~(size_t)15;
     double* W = ws_all + (size_t)slot * slot_doubles;
     const int nbc = min(NB, N - j0);
-    const int r0 = first_row + blockIdx.x * R;
+    const int r0 = first_row + tile * R;
     const int row_lo = j0 + nbc;  // rows below the diagonal block; row N is the residual
     const int wr = warp >> 1, wc = warp & 1;
 
@@ -504,12 +514,6 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         q += __shfl_xor_sync(0xffffffffu, q, 16);
         if (row == N && lane < 16) gl.quad += q;  // |z|^2 of this block column
     }
-    // The first row tile holds rows j0+NB .. j0+2NB-1 of L in warps 0-3: everything the next
-    // diagonal block needs.  Factor it here, inside this launch.
-    if (fuse_next && blockIdx.x == 0) {
-        __syncthreads();  // all warps are done with the S tile (the diag buffers alias it)
-        if (warp < 4) diag_block(p, W, ld, gl, j0 + NB, usm, tid);
-    }
 }
 
 __global__ void gpb_finish_kernel(const KParams p, const GpLane* __restrict__ lanes, int lane0, int n)
@@ -559,20 +563,16 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
             gpb_prep_kernel<1><<<n, CTA_THREADS, ma_smem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
         *n_launches += 1;
         for (int J = 0; J < nblk; J++) {
-            const int j0 = J * NB;
-            const int nbc = min(NB, N - j0);
-            if (J == 0 || !w.fuse_diag) {
-                gpb_diag_kernel<<<n, D_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0);
-                *n_launches += 1;
-            }
+            GpbStep st;
+            st.j0 = J * NB;
+            st.n = n;
+            const int nbc = min(NB, N - st.j0);
             // rows below the diagonal block, up to and including the residual row N
-            const int first_row = nbc == NB ? j0 + NB : j0;
-            const int ntile = (N + 1 - first_row + R - 1) / R;
-            dim3 grid(ntile, n);
-            const int fuse_next = (w.fuse_diag && nbc == NB && j0 + NB < N) ? 1 : 0;
-            gpb_update_kernel<<<grid, CTA_THREADS, usmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, j0,
-                                                                   first_row, fuse_next);
-            *n_launches += 1;
+            st.first_row = nbc == NB ? st.j0 + NB : st.j0;
+            st.ntile = (N + 1 - st.first_row + R - 1) / R;
+            gpb_diag_kernel<<<n, D_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, st);
+            gpb_update_kernel<<<dim3(st.ntile, n), CTA_THREADS, usmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, st);
+            *n_launches += 2;
         }
         gpb_finish_kernel<<<(n + 127) / 128, 128, 0, stream>>>(p, w.lanes, lane0, n);
         *n_launches += 1;

@@ -47,7 +47,6 @@ struct GpWorkspace {
     size_t slot_doubles; // doubles per slot
     int slots;           // lanes in flight per wave
     GpLane* lanes;       // per-slot state
-    int fuse_diag;       // 1 = the update kernel's first row tile also factors the next diagonal block
 };
 size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();

@@ -23,20 +23,18 @@ def parity(N, B, flags, path, ninst=1, seed=7):
     print(json.dumps(dict(kind="parity", N=N, B=B, path=path, ninst=ninst, max=float(r.max()) if r.size else 0.0,
                           med=float(np.median(r)) if r.size else 0.0, inf_match=ok_inf)), flush=True)
 
-def timing(N, B, path, slots=0, reps=5, stagger=None):
+def timing(N, B, path, slots=0, reps=5):
     flags = ModelFlags(GP=True, npmax=10)
     d = make_data(N)
     P, nps = make_params(flags, d, B, "max")
     with LikelihoodEngine(d, flags, B, gp_slots=slots) as eng:
-        if stagger is not None:
-            eng.set_option("gp_fuse_diag", stagger)
         eng.evaluate(P, nps)
         ms = []
         for _ in range(reps):
             eng.flush_l2(); eng.log_likelihood_device(B); eng.sync(); ms.append(eng.last_kernel_ms())
     F = N ** 3 / 3 + 37.0 * N * N + N * (330.0 * 10 + 45)
     best = min(ms)
-    print(json.dumps(dict(kind="timing", N=N, B=B, path=path, stagger=stagger, ms=best, evals_s=B / best * 1e3,
+    print(json.dumps(dict(kind="timing", N=N, B=B, path=path, ms=best, evals_s=B / best * 1e3,
                           tflops=B / best * 1e3 * F * 1e-12)), flush=True)
 
 if __name__ == "__main__":
@@ -51,9 +49,3 @@ if __name__ == "__main__":
         timing(1000, 1184, 2)
         timing(384, 2048, 2)
         timing(4096, 148, 2, reps=2)
-    if which == "stagger":
-        for st in (0, 1):
-            timing(1000, 1184, 2, stagger=st)
-        for st in (0, 1):
-            timing(4096, 148, 2, reps=2, stagger=st)
-            timing(384, 2048, 2, stagger=st)
