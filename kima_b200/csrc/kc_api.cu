@@ -50,7 +50,8 @@ struct kc_ctx {
     double *d_logL = nullptr, *h_logL = nullptr;
     int* d_counter = nullptr;
     // GP
-    kc::GpWorkspace gp{nullptr, 0, 0, nullptr};
+    kc::GpWorkspace gp{};
+    int gp_streams_opt = 2;
     double* d_resid = nullptr;   // kernel = celerite: residuals, [N][ld]
     // options / instrumentation
     int kepler_mode = 0;
@@ -81,9 +82,14 @@ void free_model(kc_ctx* c)
     cudaFree(c->d_params); cudaFree(c->d_np); cudaFree(c->d_logL);
     cudaFree(c->gp.ws); cudaFree(c->gp.lanes); cudaFree(c->d_resid);
     c->d_resid = nullptr;
+    for (int i = 0; i < 3; i++) {
+        if (c->gp.aux[i]) cudaStreamDestroy(c->gp.aux[i]);
+        if (c->gp.join[i]) cudaEventDestroy(c->gp.join[i]);
+    }
+    if (c->gp.fork) cudaEventDestroy(c->gp.fork);
     c->h_params = nullptr; c->h_np = nullptr; c->h_logL = nullptr;
     c->d_params = nullptr; c->d_np = nullptr; c->d_logL = nullptr;
-    c->gp = {nullptr, 0, 0, nullptr};
+    c->gp = kc::GpWorkspace{};
     c->configured = false;
 }
 void free_data(kc_ctx* c)
@@ -280,6 +286,12 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
         c->gp.slots = slots;
         CU(cudaMalloc(&c->gp.ws, sizeof(double) * c->gp.slot_doubles * slots));
         CU(cudaMalloc((void**)&c->gp.lanes, kc::gpb_lane_bytes() * slots));
+        c->gp.nstreams = c->gp_streams_opt;
+        CU(cudaEventCreateWithFlags(&c->gp.fork, cudaEventDisableTiming));
+        for (int i = 0; i + 1 < c->gp.nstreams; i++) {
+            CU(cudaStreamCreateWithFlags(&c->gp.aux[i], cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&c->gp.join[i], cudaEventDisableTiming));
+        }
     }
     c->configured = true;
     return KC_OK;
@@ -385,6 +397,9 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
 
     } else if (k == "gp_small") {
         c->gp_small_opt = value ? 1 : 0;
+    } else if (k == "gp_streams") {
+        if (value < 1 || value > 4) return fail(KC_ERR_ARG, "gp_streams must be 1..4");
+        c->gp_streams_opt = value;  // takes effect at the next kc_configure
     } else if (k == "gp_slots") {
         if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
         c->gp_slots_opt = value;  // takes effect at the next kc_configure

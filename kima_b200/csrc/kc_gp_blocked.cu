@@ -555,29 +555,56 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
         if (e != cudaSuccess) return e;
     }
     const int nblk = (N + NB - 1) / NB;
-    for (int lane0 = 0; lane0 < p.B; lane0 += w.slots) {
-        const int n = min(w.slots, p.B - lane0);
-        if (kepler_mode == 0)
-            gpb_prep_kernel<0><<<n, CTA_THREADS, ma_smem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
-        else
-            gpb_prep_kernel<1><<<n, CTA_THREADS, ma_smem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, lane0);
-        *n_launches += 1;
-        for (int J = 0; J < nblk; J++) {
-            GpbStep st;
-            st.j0 = J * NB;
-            st.n = n;
-            const int nbc = min(NB, N - st.j0);
-            // rows below the diagonal block, up to and including the residual row N
-            st.first_row = nbc == NB ? st.j0 + NB : st.j0;
-            st.ntile = (N + 1 - st.first_row + R - 1) / R;
-            gpb_diag_kernel<<<n, D_THREADS, dsmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, st);
-            gpb_update_kernel<<<dim3(st.ntile, n), CTA_THREADS, usmem, stream>>>(p, w.ws, w.slot_doubles, w.lanes, st);
-            *n_launches += 2;
-        }
-        gpb_finish_kernel<<<(n + 127) / 128, 128, 0, stream>>>(p, w.lanes, lane0, n);
-        *n_launches += 1;
-        e = cudaGetLastError();
+    // The lanes of a wave are cut into up to nstreams groups, each factorised on its own
+    // stream with its own share of the slots: the groups drift apart, and one group's
+    // latency-bound diagonal blocks (and launch tails) run beside another's update tiles.
+    int ng = w.nstreams < 1 ? 1 : w.nstreams;
+    while (ng > 1 && (p.B < ng * sm_count || w.slots < ng)) ng--;  // small batches: one group
+    const int gslots = w.slots / ng;
+    const int per_group = (p.B + ng - 1) / ng;
+    if (ng > 1) {
+        e = cudaEventRecord(w.fork, stream);
         if (e != cudaSuccess) return e;
+    }
+    for (int g = 0; g < ng; g++) {
+        cudaStream_t st_g = g == 0 ? stream : w.aux[g - 1];
+        if (g > 0) {
+            e = cudaStreamWaitEvent(st_g, w.fork, 0);
+            if (e != cudaSuccess) return e;
+        }
+        double* ws_g = w.ws + (size_t)g * gslots * w.slot_doubles;
+        GpLane* lanes_g = w.lanes + (size_t)g * gslots;
+        const int lane_end = min(p.B, (g + 1) * per_group);
+        for (int lane0 = g * per_group; lane0 < lane_end; lane0 += gslots) {
+            const int n = min(gslots, lane_end - lane0);
+            if (kepler_mode == 0)
+                gpb_prep_kernel<0><<<n, CTA_THREADS, ma_smem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, lane0);
+            else
+                gpb_prep_kernel<1><<<n, CTA_THREADS, ma_smem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, lane0);
+            *n_launches += 1;
+            for (int J = 0; J < nblk; J++) {
+                GpbStep st;
+                st.j0 = J * NB;
+                st.n = n;
+                const int nbc = min(NB, N - st.j0);
+                // rows below the diagonal block, up to and including the residual row N
+                st.first_row = nbc == NB ? st.j0 + NB : st.j0;
+                st.ntile = (N + 1 - st.first_row + R - 1) / R;
+                gpb_diag_kernel<<<n, D_THREADS, dsmem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, st);
+                gpb_update_kernel<<<dim3(st.ntile, n), CTA_THREADS, usmem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, st);
+                *n_launches += 2;
+            }
+            gpb_finish_kernel<<<(n + 127) / 128, 128, 0, st_g>>>(p, lanes_g, lane0, n);
+            *n_launches += 1;
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
+        }
+        if (g > 0) {
+            e = cudaEventRecord(w.join[g - 1], st_g);
+            if (e != cudaSuccess) return e;
+            e = cudaStreamWaitEvent(stream, w.join[g - 1], 0);
+            if (e != cudaSuccess) return e;
+        }
     }
     return cudaGetLastError();
 }

@@ -47,6 +47,11 @@ struct GpWorkspace {
     size_t slot_doubles; // doubles per slot
     int slots;           // lanes in flight per wave
     GpLane* lanes;       // per-slot state
+    // lane groups factorised concurrently: group 0 on the context stream, the others on aux
+    // streams, so that one group's latency-bound diagonal blocks overlap another's updates
+    int nstreams;               // groups (1..4)
+    cudaStream_t aux[3];
+    cudaEvent_t fork, join[3];
 };
 size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();

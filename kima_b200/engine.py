@@ -30,7 +30,7 @@ def _d(a: np.ndarray):
 
 class LikelihoodEngine:
     def __init__(self, data: RVData, flags: ModelFlags, max_batch: int, device: int = 0,
-                 kepler_mode: int = 0, gp_slots: int = 0):
+                 kepler_mode: int = 0, gp_slots: int = 0, gp_streams: int = 0):
         self.lib = _lib.load_library()
         self.data = data
         self.flags = flags
@@ -42,6 +42,8 @@ class LikelihoodEngine:
             _lib.check(self.lib.kc_set_option(self._ctx, b"kepler_mode", kepler_mode))
             if gp_slots:
                 _lib.check(self.lib.kc_set_option(self._ctx, b"gp_slots", gp_slots))
+            if gp_streams:
+                _lib.check(self.lib.kc_set_option(self._ctx, b"gp_streams", gp_streams))
             cf = flags.to_c()
             _lib.check(self.lib.kc_configure(self._ctx, ctypes.byref(cf), self.max_batch))
             L = CLayout()

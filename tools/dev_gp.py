@@ -49,3 +49,15 @@ if __name__ == "__main__":
         timing(1000, 1184, 2)
         timing(384, 2048, 2)
         timing(4096, 148, 2, reps=2)
+    if which == "streams":
+        for N, B in ((1000, 1184), (4096, 148), (384, 2048)):
+            for ns in (1, 2, 3, 4):
+                flags = ModelFlags(GP=True, npmax=10)
+                d = make_data(N)
+                P, nps = make_params(flags, d, B, "max")
+                with LikelihoodEngine(d, flags, B, gp_streams=ns) as eng:
+                    res = eng.evaluate(P, nps)
+                    ms = []
+                    for _ in range(4):
+                        eng.flush_l2(); eng.log_likelihood_device(B); eng.sync(); ms.append(eng.last_kernel_ms())
+                print(json.dumps(dict(N=N, B=B, streams=ns, ms=min(ms), evals_s=B / min(ms) * 1e3, chk=float(np.sum(res)))), flush=True)
