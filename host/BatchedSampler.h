@@ -33,7 +33,11 @@
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
+#include <cstring>
 #include <memory>
+#include <sstream>
+#include <stdexcept>
+#include <string>
 #include <thread>
 #include <vector>
 #include "LanePool.h"
@@ -154,6 +158,102 @@ class BatchedSampler : public Sampler<ModelType> {
         prof[3] += now() - t0;
     }
 
+    // ---- one process per GPU -----------------------------------------------------------------
+    // Rank r owns the lanes [r T/R, (r+1) T/R) and is the only one to step them, but every rank
+    // keeps the whole sampler state (all particles, likelihoods, level assignments, levels), so
+    // that after the exchange below each rank runs the same do_bookkeeping() on the same data
+    // and no decision has to be broadcast.  With R ranks the run is, lane for lane and draw for
+    // draw, the single-process run with the same -t and -s.
+    int rank() const { return evaluator ? evaluator->rank() : 0; }
+    int world() const { return evaluator ? evaluator->world() : 1; }
+    unsigned int lane_lo() const { return (unsigned int)((unsigned long long)this->num_threads * rank() / world()); }
+    unsigned int lane_hi() const { return (unsigned int)((unsigned long long)this->num_threads * (rank() + 1) / world()); }
+
+    // The barrier of run_thread (SamplerImpl.h:306-329) between processes: the owners' lanes
+    // (particles, likelihoods, level assignments) go to everybody, rank 0's RNG 0 (the one
+    // do_bookkeeping draws from) too; `above` lists are concatenated in lane order and the
+    // level counters summed.
+    void exchange(const std::vector<Level>& before)
+    {
+        const int R = world();
+        const unsigned int T = this->num_threads, P = this->options.num_particles;
+        const size_t S = evaluator->state_doubles(), per = S + 3;
+        const unsigned int lanes_per_rank = T / R;
+        constexpr size_t RNG_BYTES = 16384;
+        const size_t blob = sizeof(double) * per * P * lanes_per_rank + RNG_BYTES;
+        std::vector<char> send(blob, 0), recv(blob * R);
+        double* sd = reinterpret_cast<double*>(send.data());
+        for (unsigned int k = lane_lo(); k < lane_hi(); ++k)
+            for (unsigned int q = 0; q < P; ++q) {
+                const size_t i = (size_t)k * P + q;
+                double* o = sd + ((size_t)(k - lane_lo()) * P + q) * per;
+                evaluator->pack(this->particles[i], o);
+                o[S] = this->log_likelihoods[i].get_value();
+                o[S + 1] = this->log_likelihoods[i].get_tiebreaker();
+                o[S + 2] = (double)this->level_assignments[i];
+            }
+        if (rank() == 0) {
+            std::ostringstream os;
+            os << this->rngs[0].twister << ' ' << this->rngs[0].uniform << ' ' << this->rngs[0].normal;
+            const std::string st = os.str();
+            if (st.size() + 1 > RNG_BYTES) throw std::runtime_error("RNG state larger than its slot");
+            std::memcpy(send.data() + blob - RNG_BYTES, st.c_str(), st.size() + 1);
+        }
+        evaluator->allgather_bytes(send.data(), blob, recv.data());
+        for (int r = 0; r < R; ++r) {
+            if (r == rank()) continue;
+            const double* rd = reinterpret_cast<const double*>(recv.data() + blob * r);
+            const unsigned int lo = (unsigned int)((unsigned long long)T * r / R);
+            for (unsigned int k = 0; k < lanes_per_rank; ++k)
+                for (unsigned int q = 0; q < P; ++q) {
+                    const size_t i = (size_t)(lo + k) * P + q;
+                    const double* o = rd + ((size_t)k * P + q) * per;
+                    evaluator->unpack(this->particles[i], o);
+                    this->log_likelihoods[i] = LikelihoodType(o[S], o[S + 1]);
+                    this->level_assignments[i] = (unsigned int)o[S + 2];
+                }
+        }
+        if (rank() != 0) {
+            std::istringstream is(std::string(recv.data() + blob - RNG_BYTES));
+            is >> this->rngs[0].twister >> this->rngs[0].uniform >> this->rngs[0].normal;
+        }
+        // level counters: this rank's lanes' increments, summed over ranks
+        const size_t L = this->levels.size();
+        std::vector<uint64_t> cnt(4 * L, 0);
+        for (unsigned int k = lane_lo(); k < lane_hi(); ++k) {
+            const std::vector<Level>& lv = this->copies_of_levels[k];
+            for (size_t j = 0; j < L; ++j) {
+                cnt[4 * j + 0] += lv[j].get_accepts() - before[j].get_accepts();
+                cnt[4 * j + 1] += lv[j].get_tries() - before[j].get_tries();
+                cnt[4 * j + 2] += lv[j].get_visits() - before[j].get_visits();
+                cnt[4 * j + 3] += lv[j].get_exceeds() - before[j].get_exceeds();
+            }
+        }
+        evaluator->allreduce_levels(cnt.data(), (int)cnt.size());
+        for (size_t j = 0; j < L; ++j) {
+            this->levels[j].increment_accepts(cnt[4 * j + 0]);
+            this->levels[j].increment_tries(cnt[4 * j + 1]);
+            this->levels[j].increment_visits(cnt[4 * j + 2]);
+            this->levels[j].increment_exceeds(cnt[4 * j + 3]);
+        }
+        // `above`: this rank's lists in lane order, then all ranks' in rank (= lane) order
+        std::vector<double> mine;
+        for (unsigned int k = lane_lo(); k < lane_hi(); ++k) {
+            for (const LikelihoodType& a : this->above[k]) {
+                mine.push_back(a.get_value());
+                mine.push_back(a.get_tiebreaker());
+            }
+            this->above[k].clear();
+        }
+        const int max_total = (int)(T * this->options.thread_steps) + 16;
+        std::vector<double> all(2 * (size_t)max_total);
+        std::vector<int> counts(R);
+        evaluator->allgather_above(mine.data(), (int)(mine.size() / 2), all.data(), max_total, counts.data());
+        size_t tot = 0;
+        for (int c : counts) tot += (size_t)c;
+        for (size_t i = 0; i < tot; ++i) this->all_above.push_back(LikelihoodType(all[2 * i], all[2 * i + 1]));
+    }
+
     // thread_steps lock-step MCMC steps of all lanes (mcmc_thread for every thread at once).
     // The lanes form two groups; while the GPU scores one group's proposals the host finishes
     // the previous step of the other group and prepares its next one.  Within a lane the
@@ -162,8 +262,10 @@ class BatchedSampler : public Sampler<ModelType> {
     {
         const unsigned int T = this->num_threads;
         if (lane_steps.size() != T) lane_steps.resize(T);
-        const unsigned int split[3] = {0, T < 2 ? T : (T + 1) / 2, T};
-        const int ngroups = T < 2 ? 1 : 2;
+        // this rank's lanes [k0, k1), in two groups
+        const unsigned int k0 = lane_lo(), k1 = lane_hi(), n = k1 - k0;
+        const unsigned int split[3] = {k0, n < 2 ? k1 : k0 + (n + 1) / 2, k1};
+        const int ngroups = n < 2 ? 1 : 2;
         int nb[2] = {0, 0};
         for (unsigned int i = 0; i < this->options.thread_steps; ++i) {
             for (int g = 0; g < ngroups; ++g) {
@@ -231,6 +333,8 @@ public:
         this->thin_print = thin;
         ensure_evaluator();
         const unsigned int T = this->num_threads;
+        if (T % (unsigned int)world() != 0)
+            throw std::invalid_argument("the number of lanes (-t) must be a multiple of the number of ranks");
         while (true) {
             for (unsigned int k = 0; k < T; ++k) this->copies_of_levels[k] = this->levels;
             if (this->options.max_num_saves != 0 && this->count_saves != 0 &&
@@ -242,16 +346,20 @@ public:
             this->count_mcmc_steps_since_save += done;
             // fold every lane's counter increments back into the master level table
             const std::vector<Level> before = this->levels;
-            for (const auto& lv : this->copies_of_levels)
-                for (size_t j = 0; j < this->levels.size(); ++j) {
-                    this->levels[j].increment_accepts(lv[j].get_accepts() - before[j].get_accepts());
-                    this->levels[j].increment_tries(lv[j].get_tries() - before[j].get_tries());
-                    this->levels[j].increment_visits(lv[j].get_visits() - before[j].get_visits());
-                    this->levels[j].increment_exceeds(lv[j].get_exceeds() - before[j].get_exceeds());
+            if (world() > 1) {
+                exchange(before);
+            } else {
+                for (const auto& lv : this->copies_of_levels)
+                    for (size_t j = 0; j < this->levels.size(); ++j) {
+                        this->levels[j].increment_accepts(lv[j].get_accepts() - before[j].get_accepts());
+                        this->levels[j].increment_tries(lv[j].get_tries() - before[j].get_tries());
+                        this->levels[j].increment_visits(lv[j].get_visits() - before[j].get_visits());
+                        this->levels[j].increment_exceeds(lv[j].get_exceeds() - before[j].get_exceeds());
+                    }
+                for (auto& a : this->above) {
+                    this->all_above.insert(this->all_above.end(), a.begin(), a.end());
+                    a.clear();
                 }
-            for (auto& a : this->above) {
-                this->all_above.insert(this->all_above.end(), a.begin(), a.end());
-                a.clear();
             }
             const double tb = now();
             this->do_bookkeeping();
@@ -261,9 +369,11 @@ public:
             std::cerr << "# host threads " << pool->threads() << "  perturb " << prof[0] << " s, stage " << prof[1]
                       << " s, submit " << prof[2] << " s, wait " << prof[3] << " s, phase B " << prof[4]
                       << " s, bookkeeping " << prof[5] << " s" << std::endl;
-        std::fstream fout("sampler_state.txt", std::ios::out);
-        this->print(fout);
-        fout.close();
+        if (rank() == 0) {
+            std::fstream fout("sampler_state.txt", std::ios::out);
+            this->print(fout);
+            fout.close();
+        }
     }
 
     long long device_launches() const { return evaluator ? evaluator->launches() : 0; }

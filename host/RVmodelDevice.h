@@ -8,8 +8,13 @@
 // is still an RVmodel object held by the Sampler; `stage` copies its parameters into one
 // column of libkima_cuda's pinned SoA block (include/kima_cuda.h, kc_layout).
 #pragma once
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <thread>
 #include <iostream>
 #include <limits>
 #include <vector>
@@ -31,7 +36,12 @@ public:
 
     explicit RVmodelEvaluator(int max_batch)
     {
+        // one process per GPU: RANK / WORLD_SIZE / LOCAL_RANK as torchrun and mpirun-style
+        // launchers export them; a single process is rank 0 of 1
+        if (const char* e = std::getenv("WORLD_SIZE")) world_ = std::max(1, std::atoi(e));
+        if (const char* e = std::getenv("RANK")) rank_ = std::atoi(e);
         int device = 0;
+        if (const char* e = std::getenv("LOCAL_RANK")) device = std::atoi(e);
         if (const char* e = std::getenv("KIMA_CUDA_DEVICE")) device = std::atoi(e);
         const Data& d = Data::get_instance();
         std::vector<std::vector<double>> act(d.get_actind().begin(),
@@ -54,6 +64,93 @@ public:
                 ctx_[g]->set_option("kepler_mode", std::atoi(e));
             // group 0 also scores the prior draws of initialise(), so it gets the full batch
             ctx_[g]->configure(f, g == 0 ? max_batch : (max_batch + 1) / 2);
+        }
+        if (world_ > 1) comm_bootstrap();
+    }
+
+    int rank() const { return rank_; }
+    int world() const { return world_; }
+
+    // ---- the barrier exchange between ranks (DNest4/code/SamplerImpl.h:306-329) ----------
+    void allgather_bytes(const void* send, size_t nbytes, void* recv) { ctx_[0]->allgather_bytes(send, nbytes, recv); }
+    void allgather_above(const double* pairs, int n, double* out, int max_total, int* counts)
+    {
+        ctx_[0]->allgather_above(pairs, n, out, max_total, counts);
+    }
+    void allreduce_levels(uint64_t* counters, int n) { ctx_[0]->allreduce_levels(counters, n); }
+
+    // ---- a particle as a flat array of doubles, for the exchange between ranks -----------
+    // Everything of an RVmodel that a later perturb(), print() or stage() reads
+    // (src/RVmodel.h:44-76, RJObject.h:34-58, RVConditionalPrior.h:17-20).
+    size_t state_doubles() const
+    {
+        const Data& d = Data::get_instance();
+        RVmodel probe;
+        return 8 + 20 * (size_t)probe.npmax + 3 + 24 + 2 * (size_t)d.number_instruments + d.number_indicators +
+               5 * (size_t)n_known_object;
+    }
+    void pack(const RVmodel& m, double* out) const
+    {
+        size_t o = 0;
+        const auto& pl = m.planets;
+        auto put_vv = [&](const std::vector<std::vector<double>>& vv) {
+            out[o++] = (double)vv.size();
+            for (const auto& v : vv)
+                for (double x : v) out[o++] = x;
+        };
+        out[o++] = (double)pl.num_components;
+        out[o++] = pl.components_changed_flag ? 1.0 : 0.0;
+        put_vv(pl.components);
+        put_vv(pl.u_components);
+        put_vv(pl.added);
+        put_vv(pl.removed);
+        out[o++] = pl.conditional_prior.center;
+        out[o++] = pl.conditional_prior.width;
+        out[o++] = pl.conditional_prior.muK;
+        const double sc[] = {m.background, m.slope, m.quadr, m.cubic, m.sigmaMA, m.tauMA, m.extra_sigma, m.nu,
+                             m.eta1, m.eta2, m.eta3, m.eta4, m.eta5, m.log_eta1, m.log_eta2, m.log_eta3,
+                             m.log_eta4, m.log_eta5, m.a, m.b, m.c, m.P, (double)m.staleness, 0.0};
+        for (double x : sc) out[o++] = x;
+        for (double x : m.offsets) out[o++] = x;
+        for (double x : m.jitters) out[o++] = x;
+        for (double x : m.betas) out[o++] = x;
+        for (const auto* v : {&m.KO_P, &m.KO_K, &m.KO_e, &m.KO_phi, &m.KO_w})
+            for (int i = 0; i < n_known_object; i++) out[o++] = i < (int)v->size() ? (*v)[i] : 0.0;
+    }
+    void unpack(RVmodel& m, const double* in) const
+    {
+        size_t o = 0;
+        auto& pl = m.planets;
+        auto get_vv = [&](std::vector<std::vector<double>>& vv) {
+            const size_t n = (size_t)in[o++];
+            vv.assign(n, std::vector<double>(5));
+            for (auto& v : vv)
+                for (double& x : v) x = in[o++];
+        };
+        pl.num_components = (int)in[o++];
+        pl.components_changed_flag = in[o++] != 0.0;
+        get_vv(pl.components);
+        get_vv(pl.u_components);
+        get_vv(pl.added);
+        get_vv(pl.removed);
+        pl.conditional_prior.center = in[o++];
+        pl.conditional_prior.width = in[o++];
+        pl.conditional_prior.muK = in[o++];
+        double* sc[] = {&m.background, &m.slope, &m.quadr, &m.cubic, &m.sigmaMA, &m.tauMA, &m.extra_sigma, &m.nu,
+                        &m.eta1, &m.eta2, &m.eta3, &m.eta4, &m.eta5, &m.log_eta1, &m.log_eta2, &m.log_eta3,
+                        &m.log_eta4, &m.log_eta5, &m.a, &m.b, &m.c, &m.P};
+        for (double* x : sc) *x = in[o++];
+        m.staleness = (unsigned int)in[o++];
+        o++;
+        for (double& x : m.offsets) x = in[o++];
+        for (double& x : m.jitters) x = in[o++];
+        for (double& x : m.betas) x = in[o++];
+        for (auto* v : {&m.KO_P, &m.KO_K, &m.KO_e, &m.KO_phi, &m.KO_w}) {
+            if (known_object) v->resize(n_known_object);
+            for (int i = 0; i < n_known_object; i++) {
+                if (i < (int)v->size()) (*v)[i] = in[o];
+                o++;
+            }
         }
     }
 
@@ -133,6 +230,39 @@ public:
     long long launches() const { return ctx_[0]->launch_count() + ctx_[1]->launch_count(); }
 
 private:
+    // NCCL's unique id travels through a file in the run directory (all ranks of one node
+    // share it): rank 0 writes it atomically, the others wait for it.
+    void comm_bootstrap()
+    {
+        const char* tag = std::getenv("KIMA_COMM_ID_FILE");
+        std::string path = tag ? tag : ".kima_nccl_id";
+        if (!tag)
+            if (const char* port = std::getenv("MASTER_PORT")) path += std::string(".") + port;
+        unsigned char id[128];
+        if (rank_ == 0) {
+            kimacuda::Context::unique_id(id);
+            const std::string tmp = path + ".tmp";
+            {
+                std::ofstream f(tmp, std::ios::binary | std::ios::trunc);
+                f.write((const char*)id, 128);
+            }
+            std::rename(tmp.c_str(), path.c_str());
+        } else {
+            for (int tries = 0;; tries++) {
+                std::ifstream f(path, std::ios::binary);
+                if (f && f.read((char*)id, 128)) break;
+                if (tries > 6000) throw std::runtime_error("timed out waiting for " + path);
+                std::this_thread::sleep_for(std::chrono::milliseconds(10));
+            }
+        }
+        ctx_[0]->comm_init(rank_, world_, id);
+        // everybody has read the id once this completes: rank 0 can remove the file
+        unsigned char token = 1, all[1024];
+        ctx_[0]->allgather_bytes(&token, 1, all);
+        if (rank_ == 0) std::remove(path.c_str());
+    }
+
+    int rank_ = 0, world_ = 1;
     std::unique_ptr<kimacuda::Context> ctx_[GROUPS];
     kc_model_flags flags_{};
 };

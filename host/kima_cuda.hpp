@@ -67,6 +67,16 @@ public:
     void wait() { check(kc_wait(ctx_)); }
     void set_option(const char* key, int value) { check(kc_set_option(ctx_, key, value)); }
     long long launch_count() const { return (long long)kc_launch_count(ctx_); }
+
+    // one process per GPU: the level-creation barrier (DNest4/code/SamplerImpl.h:306-329)
+    static void unique_id(void* id128) { check(kc_comm_unique_id(id128)); }
+    void comm_init(int rank, int nranks, const void* id128) { check(kc_comm_init(ctx_, rank, nranks, id128)); }
+    void allgather_bytes(const void* send, size_t nbytes, void* recv) { check(kc_allgather_bytes(ctx_, send, nbytes, recv)); }
+    void allgather_above(const double* pairs, int n, double* out, int max_total, int* counts)
+    {
+        check(kc_allgather_above(ctx_, pairs, n, out, max_total, counts));
+    }
+    void allreduce_levels(uint64_t* counters, int n) { check(kc_allreduce_levels(ctx_, counters, n)); }
     kc_ctx* raw() { return ctx_; }
 
 private:

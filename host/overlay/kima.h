@@ -87,8 +87,12 @@ GpuSampler<ModelType> gpu_setup(int argc, char** argv)
     std::cout << "# Target compression factor between levels = ";
     std::cout << options.get_compression() << std::endl;
     DNest4::Options sampler_options(options.get_options_file().c_str());
+    // one process per GPU (RANK / WORLD_SIZE in the environment): every rank keeps the whole
+    // sampler state, rank 0 alone writes the output files
+    const char* rk = std::getenv("RANK");
+    const bool root = !rk || std::atoi(rk) == 0;
     GpuSampler<ModelType> sampler(options.get_num_threads(), options.get_compression_double(),
-                                  sampler_options, true);
+                                  sampler_options, root);
     sampler.initialise(options.get_seed_uint());
     return sampler;
 }

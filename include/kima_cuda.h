@@ -19,6 +19,7 @@
 #ifndef KIMA_CUDA_H
 #define KIMA_CUDA_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -203,6 +204,10 @@ int kc_comm_init(kc_ctx* ctx, int rank, int nranks, const void* id128);
  * rank-major; counts[nranks] receives each rank's n. */
 int kc_allgather_above(kc_ctx* ctx, const double* pairs, int n, double* out,
                        int max_total, int* counts);
+/* Gather nbytes from every rank (the same nbytes on all): recv is nranks * nbytes, rank-major.
+ * Used for the lanes' particle states, which kill_lagging_particles (SamplerImpl.h:534-587)
+ * may copy between lanes of different ranks, and for the RNG that do_bookkeeping draws from. */
+int kc_allgather_bytes(kc_ctx* ctx, const void* send, size_t nbytes, void* recv);
 /* Sum the per-level accepts/tries/visits/exceeds deltas over ranks. */
 int kc_allreduce_levels(kc_ctx* ctx, uint64_t* counters, int n);
 int kc_comm_destroy(kc_ctx* ctx);

@@ -58,6 +58,7 @@ SIGNATURES = {
     "kc_comm_init": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _vp]),
     "kc_allgather_above": (ctypes.c_int, [_vp, _dp, ctypes.c_int, _dp, ctypes.c_int,
                                           ctypes.POINTER(ctypes.c_int)]),
+    "kc_allgather_bytes": (ctypes.c_int, [_vp, _vp, ctypes.c_size_t, _vp]),
     "kc_allreduce_levels": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     "kc_comm_destroy": (ctypes.c_int, [_vp]),
 }

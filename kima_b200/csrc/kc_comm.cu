@@ -174,6 +174,29 @@ int kc_allgather_above(kc_ctx* c, const double* pairs, int n, double* out, int m
     return KC_OK;
 }
 
+int kc_allgather_bytes(kc_ctx* c, const void* send, size_t nbytes, void* recv)
+{
+    if (!c || (nbytes > 0 && (!send || !recv))) return kc::comm_fail(KC_ERR_ARG, "bad argument");
+    kc::CommView v = kc::comm_view(c);
+    const int R = *v.nranks;
+    if (!*v.nccl_comm) {  // single rank without a communicator: identity
+        if (R != 1) return kc::comm_fail(KC_ERR_ARG, "kc_comm_init has not been called");
+        if (nbytes && recv != send) std::memcpy(recv, send, nbytes);
+        return KC_OK;
+    }
+    if (nbytes == 0) return KC_OK;
+    CUC(cudaSetDevice(v.device));
+    int rc = ensure_buf(v, nbytes * (size_t)(R + 1));
+    if (rc) return rc;
+    char* d = (char*)*v.d_buf;
+    char* d_send = d + nbytes * (size_t)R;
+    CUC(cudaMemcpyAsync(d_send, send, nbytes, cudaMemcpyHostToDevice, v.stream));
+    NC(g_nccl.AllGather(d_send, d, nbytes, ncclChar, (ncclComm_t)*v.nccl_comm, v.stream));
+    CUC(cudaMemcpyAsync(recv, d, nbytes * (size_t)R, cudaMemcpyDeviceToHost, v.stream));
+    CUC(cudaStreamSynchronize(v.stream));
+    return KC_OK;
+}
+
 int kc_allreduce_levels(kc_ctx* c, uint64_t* counters, int n)
 {
     if (!c || n < 0 || (n > 0 && !counters)) return kc::comm_fail(KC_ERR_ARG, "bad argument");

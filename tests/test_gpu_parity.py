@@ -109,6 +109,29 @@ def test_gp_block_column_edges(gpu, port, N):
     assert np.array_equal(got, again)  # deterministic: no atomics on the data path
 
 
+@pytest.mark.parametrize("streams", [1, 2, 3, 4])
+def test_gp_blocked_lane_groups_and_waves(gpu, port, streams):
+    """The blocked path cuts a batch into concurrent lane groups (one stream each) and every
+    group into waves of its share of the slots: 700 lanes, 4 groups x 3 waves of 60 slots at
+    most, ragged last wave; results do not depend on the grouping."""
+    flags = ModelFlags(GP=True, npmax=1)
+    N = 70
+    d = make_data(N, seed=4100)
+    B = 700
+    P, nps = make_params(flags, d, B, "mix", seed=N)
+    port.set_rvdata(d)
+    port.set_flags(flags)
+    ref, _ = port.eval_batch(P, nps, nthreads=8)
+    with LikelihoodEngine(d, flags, B, gp_slots=240, gp_streams=streams) as eng:
+        eng.set_option("gp_small", 0)
+        got = eng.evaluate(P, nps)
+    assert relerr(got, ref).max() <= LOGL_RTOL
+    with LikelihoodEngine(d, flags, B, gp_streams=1) as eng:
+        eng.set_option("gp_small", 0)
+        one = eng.evaluate(P, nps)
+    assert np.array_equal(got, one)
+
+
 @pytest.mark.parametrize("N", [2, 3, 31, 32, 33, 64, 65, 95, 96, 97, 160, 161, 177, 192, 208, 211, 212])
 def test_gp_small_path_edges(gpu, port, N):
     """The shared-memory-resident kernel (one CTA per particle, N <= 211) at every alignment of

@@ -119,3 +119,44 @@ def test_ma_setup_runs_through_the_host_side(gpu, tmp_path):
     assert ha == hb and ra.shape == rb.shape
     ib = np.loadtxt(b / "sample_info.txt", ndmin=2)
     assert np.all(np.isfinite(ib[:, 1])) and np.all(ib[:, 1] > -1e299)
+
+
+def _gpu_count():
+    try:
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=30).stdout
+        return sum(1 for l in out.splitlines() if l.startswith("GPU "))
+    except Exception:
+        return 0
+
+
+def run_ranks(name, tmp_path, world, lanes, seed=43, port=29541):
+    """`world` processes, one per GPU, in ONE run directory (RANK / WORLD_SIZE / LOCAL_RANK as a
+    torchrun-style launcher exports them)."""
+    exe = os.path.join(BUILD, "kima_gpu_%s" % name)
+    d = tmp_path / ("ranks%d_%s" % (world, name))
+    d.mkdir()
+    for f in (CASES[name][0] if name in CASES else OWN_SETUPS[name]) + ["OPTIONS"]:
+        shutil.copy(os.path.join(E2E, f), d)
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK=str(r), MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=600) for p in procs]
+    for p, (so, se) in zip(procs, outs):
+        assert p.returncode == 0, so[-1500:] + se[-1500:]
+    return d
+
+
+@pytest.mark.parametrize("name", ["BL2009", "CoRoT7", "multi_instrument"])
+def test_two_ranks_reproduce_the_single_process_chain(gpu, tmp_path, name):
+    """One process per GPU, lanes sharded, the level-creation barrier over NCCL
+    (SamplerImpl.h:306-329 -> kc_allgather_bytes / kc_allgather_above / kc_allreduce_levels):
+    2 ranks x 4 lanes produce, byte for byte, the files of 1 process x 8 lanes (which in turn is
+    the reference's `-t 8` chain)."""
+    if _gpu_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    one = run_example("gpu", name, tmp_path, lanes=8)
+    two = run_ranks(name, tmp_path, 2, 8)
+    for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
+        assert (one / f).read_bytes() == (two / f).read_bytes(), f
