@@ -317,8 +317,37 @@ def main():
         import sampler_bench
         os.environ.setdefault("KIMA_CUDA_DEVICE", str(local))
         out["sampler"] = {"unit": "MCMC steps/s", "lanes": 4096, "cpu_threads": threads,
-                          "runs": [sampler_bench.compare(n, 4096, threads, gpu_saves=40, cpu_saves=100)
+                          "runs": [sampler_bench.compare(n, 4096, threads, gpu_saves=80, cpu_saves=100)
                                    for n in ("CoRoT7", "51Peg")]}
+    if world > 1 and not a.skip_sampler and os.path.exists(os.path.join(ROOT, "host", "_build", "kima_gpu_CoRoT7")):
+        # the same end to end at N GPUs: one C++ process per GPU (host/BatchedSampler.h), lanes
+        # sharded, the level-creation barrier over NCCL; 4096 lanes per GPU (weak scaling)
+        import shutil
+        import torch.distributed as dist
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import sampler_bench
+        runs = []
+        for i, name in enumerate(("CoRoT7", "51Peg")):
+            box = [sampler_bench.prepare_dir(name, 4096 * world, 100, 80) if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0)
+            dist.barrier()
+            r = sampler_bench.run_rank(name, box[0], 4096 * world, rank, world, local,
+                                       int(os.environ.get("MASTER_PORT", "29500")) + 11 + i,
+                                       max(1, threads // world))
+            wall = exch.max_float(float(r.get("wall_s", 0.0)))
+            bad = exch.max_float(1.0 if "error" in r else 0.0)
+            if rank == 0:
+                if bad or not r.get("mcmc_steps"):
+                    runs.append({"example": name, "error": r.get("error", "a rank failed")})
+                else:
+                    runs.append({"example": name, "lanes": 4096 * world, "mcmc_steps": r["mcmc_steps"],
+                                 "wall_s": wall, "steps_per_s": r["mcmc_steps"] / wall,
+                                 "run_s": r.get("run_s"),
+                                 "steps_per_s_run": r["mcmc_steps"] / r["run_s"] if r.get("run_s") else None})
+                shutil.rmtree(box[0], ignore_errors=True)
+        if rank == 0:
+            out["sampler"] = {"unit": "MCMC steps/s", "lanes_per_gpu": 4096, "ranks": world,
+                              "host_threads_per_rank": max(1, threads // world), "runs": runs}
     if exch:
         import torch.distributed as dist
         dist.barrier()

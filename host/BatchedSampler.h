@@ -62,8 +62,9 @@ class BatchedSampler : public Sampler<ModelType> {
     std::vector<double> logl_buf;            // initialise(): one batch
     std::vector<double> logl_grp[2];         // run(): one buffer per lane group
     std::shared_ptr<kima_b200::LanePool> pool;
+    std::vector<char> xbuf_send, xbuf_recv;  // exchange() buffers, kept between rounds
     // wall-clock split of run(), printed at the end when KIMA_PROFILE is set
-    double prof[6] = {0, 0, 0, 0, 0, 0};  // perturb, stage, submit, wait, phase B, bookkeeping
+    double prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // perturb, stage, submit, wait, phase B, bookkeeping, exchange, level copies
     static double now()
     {
         return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -181,17 +182,23 @@ class BatchedSampler : public Sampler<ModelType> {
         const unsigned int lanes_per_rank = T / R;
         constexpr size_t RNG_BYTES = 16384;
         const size_t blob = sizeof(double) * per * P * lanes_per_rank + RNG_BYTES;
-        std::vector<char> send(blob, 0), recv(blob * R);
+        std::vector<char>& send = xbuf_send;
+        std::vector<char>& recv = xbuf_recv;
+        if (send.size() != blob) send.assign(blob, 0);
+        if (recv.size() != blob * R) recv.assign(blob * R, 0);
         double* sd = reinterpret_cast<double*>(send.data());
-        for (unsigned int k = lane_lo(); k < lane_hi(); ++k)
-            for (unsigned int q = 0; q < P; ++q) {
-                const size_t i = (size_t)k * P + q;
-                double* o = sd + ((size_t)(k - lane_lo()) * P + q) * per;
-                evaluator->pack(this->particles[i], o);
-                o[S] = this->log_likelihoods[i].get_value();
-                o[S + 1] = this->log_likelihoods[i].get_tiebreaker();
-                o[S + 2] = (double)this->level_assignments[i];
-            }
+        const unsigned int my_lo = lane_lo();
+        pool->run((int)lane_lo(), (int)lane_hi(), [&](int a, int b) {
+            for (int k = a; k < b; ++k)
+                for (unsigned int q = 0; q < P; ++q) {
+                    const size_t i = (size_t)k * P + q;
+                    double* o = sd + ((size_t)(k - my_lo) * P + q) * per;
+                    evaluator->pack(this->particles[i], o);
+                    o[S] = this->log_likelihoods[i].get_value();
+                    o[S + 1] = this->log_likelihoods[i].get_tiebreaker();
+                    o[S + 2] = (double)this->level_assignments[i];
+                }
+        });
         if (rank() == 0) {
             std::ostringstream os;
             os << this->rngs[0].twister << ' ' << this->rngs[0].uniform << ' ' << this->rngs[0].normal;
@@ -204,14 +211,16 @@ class BatchedSampler : public Sampler<ModelType> {
             if (r == rank()) continue;
             const double* rd = reinterpret_cast<const double*>(recv.data() + blob * r);
             const unsigned int lo = (unsigned int)((unsigned long long)T * r / R);
-            for (unsigned int k = 0; k < lanes_per_rank; ++k)
-                for (unsigned int q = 0; q < P; ++q) {
-                    const size_t i = (size_t)(lo + k) * P + q;
-                    const double* o = rd + ((size_t)k * P + q) * per;
-                    evaluator->unpack(this->particles[i], o);
-                    this->log_likelihoods[i] = LikelihoodType(o[S], o[S + 1]);
-                    this->level_assignments[i] = (unsigned int)o[S + 2];
-                }
+            pool->run(0, (int)lanes_per_rank, [&](int a, int b) {
+                for (int k = a; k < b; ++k)
+                    for (unsigned int q = 0; q < P; ++q) {
+                        const size_t i = (size_t)(lo + k) * P + q;
+                        const double* o = rd + ((size_t)k * P + q) * per;
+                        evaluator->unpack(this->particles[i], o);
+                        this->log_likelihoods[i] = LikelihoodType(o[S], o[S + 1]);
+                        this->level_assignments[i] = (unsigned int)o[S + 2];
+                    }
+            });
         }
         if (rank() != 0) {
             std::istringstream is(std::string(recv.data() + blob - RNG_BYTES));
@@ -308,7 +317,9 @@ public:
         std::cout << " particle" << ((n > 1) ? ("s") : (""));
         std::cout << " from the prior..." << std::flush;
         std::vector<double> tiebreakers(n);
+        const double ti0 = now();
         ensure_evaluator();
+        const double ti1 = now();
         for (size_t i = 0; i < n; ++i) {
             this->particles[i].from_prior(rng);
             tiebreakers[i] = rng.rand();
@@ -323,6 +334,9 @@ public:
                 this->log_likelihoods[i0 + b] = LikelihoodType(logl_buf[b], tiebreakers[i0 + b]);
         }
         std::cout << "done." << std::endl;
+        if (std::getenv("KIMA_PROFILE"))
+            std::cerr << "# initialise: evaluator " << ti1 - ti0 << " s, prior draws + first likelihoods "
+                      << now() - ti1 << " s" << std::endl;
         this->initialise_output_files();
     }
 
@@ -331,12 +345,21 @@ public:
     void run(unsigned int thin = 1)
     {
         this->thin_print = thin;
+        const double t_run0 = now();
         ensure_evaluator();
         const unsigned int T = this->num_threads;
         if (T % (unsigned int)world() != 0)
             throw std::invalid_argument("the number of lanes (-t) must be a multiple of the number of ranks");
         while (true) {
-            for (unsigned int k = 0; k < T; ++k) this->copies_of_levels[k] = this->levels;
+            {
+                // each lane's own copy of the levels (SamplerImpl.h:283-284); only the lanes this
+                // rank steps need one
+                const double tc = now();
+                pool->run((int)lane_lo(), (int)lane_hi(), [&](int a, int b) {
+                    for (int k = a; k < b; ++k) this->copies_of_levels[k] = this->levels;
+                });
+                prof[7] += now() - tc;
+            }
             if (this->options.max_num_saves != 0 && this->count_saves != 0 &&
                 (this->count_saves % this->options.max_num_saves == 0))
                 break;
@@ -347,7 +370,9 @@ public:
             // fold every lane's counter increments back into the master level table
             const std::vector<Level> before = this->levels;
             if (world() > 1) {
+                const double te = now();
                 exchange(before);
+                prof[6] += now() - te;
             } else {
                 for (const auto& lv : this->copies_of_levels)
                     for (size_t j = 0; j < this->levels.size(); ++j) {
@@ -366,9 +391,12 @@ public:
             prof[5] += now() - tb;
         }
         if (std::getenv("KIMA_PROFILE"))
+            std::cerr << "# run() " << now() - t_run0 << " s" << std::endl;
+        if (std::getenv("KIMA_PROFILE"))
             std::cerr << "# host threads " << pool->threads() << "  perturb " << prof[0] << " s, stage " << prof[1]
                       << " s, submit " << prof[2] << " s, wait " << prof[3] << " s, phase B " << prof[4]
-                      << " s, bookkeeping " << prof[5] << " s" << std::endl;
+                      << " s, bookkeeping " << prof[5] << " s, exchange " << prof[6] << " s, level copies " << prof[7]
+                      << " s" << std::endl;
         if (rank() == 0) {
             std::fstream fout("sampler_state.txt", std::ios::out);
             this->print(fout);

@@ -91,9 +91,15 @@ GpuSampler<ModelType> gpu_setup(int argc, char** argv)
     // sampler state, rank 0 alone writes the output files
     const char* rk = std::getenv("RANK");
     const bool root = !rk || std::atoi(rk) == 0;
+    const auto t0 = std::chrono::steady_clock::now();
     GpuSampler<ModelType> sampler(options.get_num_threads(), options.get_compression_double(),
                                   sampler_options, root);
+    const auto t1 = std::chrono::steady_clock::now();
     sampler.initialise(options.get_seed_uint());
+    if (std::getenv("KIMA_PROFILE"))
+        std::cerr << "# setup: sampler constructed in " << std::chrono::duration<double>(t1 - t0).count()
+                  << " s, initialised in "
+                  << std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count() << " s" << std::endl;
     return sampler;
 }
 

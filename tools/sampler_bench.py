@@ -33,6 +33,13 @@ OPTIONS = """# DNest4 options for the throughput run
 """
 
 
+def _run_seconds(stderr):
+    for l in stderr.splitlines():
+        if l.startswith("# run() "):
+            return float(l.split()[2])
+    return None
+
+
 def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=1200):
     exe = os.path.join(BUILD, "kima_%s_%s" % (kind, name))
     if not os.path.exists(exe):
@@ -43,7 +50,7 @@ def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=120
             shutil.copy(os.path.join(E2E, f), d)
         with open(os.path.join(d, "OPTIONS"), "w") as fh:
             fh.write(OPTIONS.format(nli=max(2000, threads * thread_steps // 4), ts=thread_steps, saves=saves))
-        e = dict(os.environ)
+        e = dict(os.environ, KIMA_PROFILE="1")
         e.update(env or {})
         t0 = time.perf_counter()
         r = subprocess.run([exe, "-t", str(threads), "-s", str(seed)], cwd=d, capture_output=True, text=True,
@@ -54,10 +61,45 @@ def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=120
         with open(os.path.join(d, "sampler_state.txt")) as fh:
             steps = int(fh.read().split()[-1])
         prof = [l for l in r.stderr.splitlines() if l.startswith("# host threads")]
-        return {"kind": kind, "example": name, "profile": prof[-1] if prof else None, "threads": threads, "thread_steps": thread_steps, "saves": saves,
+        extra = {}
+        run_s = _run_seconds(r.stderr)
+        if run_s:
+            # the sampling loop alone (Sampler::run), without process start, CUDA context and
+            # the prior draws: what a long run converges to
+            extra = {"run_s": run_s, "steps_per_s_run": steps / run_s}
+        return {"kind": kind, "example": name, "profile": prof[-1] if prof else None, **extra, "threads": threads, "thread_steps": thread_steps, "saves": saves,
                 "mcmc_steps": steps, "wall_s": wall, "steps_per_s": steps / wall}
     finally:
         shutil.rmtree(d, ignore_errors=True)
+
+
+def prepare_dir(name, threads, thread_steps, saves):
+    d = tempfile.mkdtemp(prefix="kima_ranks_%s_" % name)
+    for f in DATA[name]:
+        shutil.copy(os.path.join(E2E, f), d)
+    with open(os.path.join(d, "OPTIONS"), "w") as fh:
+        fh.write(OPTIONS.format(nli=max(2000, threads * thread_steps // 4), ts=thread_steps, saves=saves))
+    return d
+
+
+def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, timeout=1200):
+    """This process's rank of a one-process-per-GPU run of the batched GPU sampler in the shared
+    run directory `d` (every rank calls this at the same time)."""
+    exe = os.path.join(BUILD, "kima_gpu_%s" % name)
+    e = dict(os.environ, KIMA_PROFILE="1", RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(local), MASTER_PORT=str(port),
+             KIMA_HOST_THREADS=str(host_threads))
+    e.pop("KIMA_CUDA_DEVICE", None)
+    t0 = time.perf_counter()
+    r = subprocess.run([exe, "-t", str(threads), "-s", str(seed)], cwd=d, capture_output=True, text=True,
+                       timeout=timeout, env=e)
+    wall = time.perf_counter() - t0
+    if r.returncode != 0:
+        return {"error": (r.stdout[-500:] + r.stderr[-500:])}
+    steps = None
+    if rank == 0:
+        with open(os.path.join(d, "sampler_state.txt")) as fh:
+            steps = int(fh.read().split()[-1])
+    return {"wall_s": wall, "mcmc_steps": steps, "run_s": _run_seconds(r.stderr)}
 
 
 def compare(name, lanes, cores, gpu_saves=20, cpu_saves=20, thread_steps=100, env=None):
