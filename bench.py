@@ -327,7 +327,7 @@ def main():
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import sampler_bench
         runs = []
-        for i, name in enumerate(("CoRoT7", "51Peg")):
+        for i, name in enumerate(("CoRoT7",)):
             box = [sampler_bench.prepare_dir(name, 4096 * world, 100, 80) if rank == 0 else None]
             dist.broadcast_object_list(box, src=0)
             dist.barrier()

@@ -270,7 +270,10 @@ class BatchedSampler : public Sampler<ModelType> {
     void mcmc_lockstep()
     {
         const unsigned int T = this->num_threads;
-        if (lane_steps.size() != T) lane_steps.resize(T);
+        if (lane_steps.size() != T) {
+            lane_steps.resize(T);
+            for (auto& st : lane_steps) evaluator->strip(st.proposal);
+        }
         // this rank's lanes [k0, k1), in two groups
         const unsigned int k0 = lane_lo(), k1 = lane_hi(), n = k1 - k0;
         const unsigned int split[3] = {k0, n < 2 ? k1 : k0 + (n + 1) / 2, k1};

@@ -9,6 +9,7 @@
 // O(N Np) / O(N^2) CPU work disappears.  The one piece of state they still own is the
 // `staleness` counter, because RVmodel::print writes it to sample.txt (src/RVmodel.cpp:1003):
 // the rule below is the reference's (src/RVmodel.cpp:296-297, 306, 344-345).
+#include <atomic>
 #include <Eigen/Core>
 #include <Eigen/Dense>
 #include "celerite/celerite.h"
@@ -32,3 +33,14 @@ void RVmodel::calculate_mu()
 void RVmodel::calculate_C() {}
 void RVmodel::add_known_object() {}
 void RVmodel::remove_known_object() {}
+
+// save_setup() writes kima_model_setup.txt from the priors, which are the same objects for
+// every particle; from_prior() calls it for each particle (src/RVmodel.cpp:87-88).  Run the
+// reference's own function (kept reachable as kima_ref_save_setup by host/Makefile) for the
+// first particle only: same file, written once.
+extern "C" void kima_ref_save_setup(RVmodel*);
+void RVmodel::save_setup()
+{
+    static std::atomic<bool> done(false);
+    if (!done.exchange(true)) kima_ref_save_setup(this);
+}

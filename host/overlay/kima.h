@@ -30,6 +30,7 @@
 #include <iostream>
 #include <istream>
 #include <limits>
+#include <malloc.h>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -91,6 +92,11 @@ GpuSampler<ModelType> gpu_setup(int argc, char** argv)
     // sampler state, rank 0 alone writes the output files
     const char* rk = std::getenv("RANK");
     const bool root = !rk || std::atoi(rk) == 0;
+    // Every default-constructed RVmodel allocates (never touches) an N x N matrix and an N vector
+    // (src/RVmodel.h:84,95) until RVmodelEvaluator::strip() drops them; with tens of thousands
+    // of lanes that is one mmap per particle, against vm.max_map_count = 65530.  Serve them from
+    // the heap instead.
+    mallopt(M_MMAP_THRESHOLD, 32 * 1024 * 1024);
     const auto t0 = std::chrono::steady_clock::now();
     GpuSampler<ModelType> sampler(options.get_num_threads(), options.get_compression_double(),
                                   sampler_options, root);

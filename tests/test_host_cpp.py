@@ -79,6 +79,11 @@ def test_example_reproduces_reference_chain(gpu, tmp_path, name):
     ib = np.loadtxt(d / "sample_info.txt", ndmin=2)
     assert ia.shape == ib.shape and np.array_equal(ia[:, 0], ib[:, 0])
     assert np.max(np.abs(ia[:, 1] - ib[:, 1]) / np.abs(ia[:, 1])) <= 1e-10
+    # kima_model_setup.txt (written once here, once per particle by the reference): same content
+    # after its time-stamp line; levels.txt: same levels
+    assert (c / "kima_model_setup.txt").read_text().splitlines()[1:] == \
+        (d / "kima_model_setup.txt").read_text().splitlines()[1:]
+    assert (c / "levels.txt").read_bytes() == (d / "levels.txt").read_bytes()
 
 
 def test_gpu_chain_equals_cpu_chain_on_this_box(gpu, tmp_path):

@@ -82,7 +82,7 @@ def prepare_dir(name, threads, thread_steps, saves):
     return d
 
 
-def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, timeout=1200):
+def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, timeout=420):
     """This process's rank of a one-process-per-GPU run of the batched GPU sampler in the shared
     run directory `d` (every rank calls this at the same time)."""
     exe = os.path.join(BUILD, "kima_gpu_%s" % name)
@@ -90,8 +90,11 @@ def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, 
              KIMA_HOST_THREADS=str(host_threads))
     e.pop("KIMA_CUDA_DEVICE", None)
     t0 = time.perf_counter()
-    r = subprocess.run([exe, "-t", str(threads), "-s", str(seed)], cwd=d, capture_output=True, text=True,
-                       timeout=timeout, env=e)
+    try:
+        r = subprocess.run([exe, "-t", str(threads), "-s", str(seed)], cwd=d, capture_output=True, text=True,
+                           timeout=timeout, env=e)
+    except subprocess.TimeoutExpired:
+        return {"error": "rank %d timed out after %d s" % (rank, timeout)}
     wall = time.perf_counter() - t0
     if r.returncode != 0:
         return {"error": (r.stdout[-500:] + r.stderr[-500:])}
