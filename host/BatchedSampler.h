@@ -22,6 +22,7 @@
 //     explicit Evaluator(int max_batch);  int max_batch() const;
 //     void stage(int slot, const ModelType&);  void evaluate(int B, double* logL);   (group 0, blocking)
 //     void strip(ModelType&);   (drop per-particle host state only the CPU likelihood needs)
+//     void slim_host_data();    (after initialise: drop host copies of the data the sampler no longer reads)
 //     void stage(int g, int slot, const ModelType&);  void submit(int g, int B, double* logL);  void wait(int g);
 //
 // This header must be included after Sampler.h has been included with its private section
@@ -341,6 +342,7 @@ public:
             std::cerr << "# initialise: evaluator " << ti1 - ti0 << " s, prior draws + first likelihoods "
                       << now() - ti1 << " s" << std::endl;
         this->initialise_output_files();
+        evaluator->slim_host_data();  // nothing on the host reads the data arrays from here on
     }
 
     // Alternate lock-step MCMC and bookkeeping until max_num_saves is reached

@@ -168,6 +168,25 @@ public:
         m.C.resize(0, 0);
     }
 
+    // RVmodel::perturb() and print() copy the whole Data singleton by value on every call
+    // (`auto data = Data::get_instance();`, src/RVmodel.cpp:441,444,975) although, with mu
+    // gone from the host, all they still read of it is t_middle and the indicator flags: that
+    // copy (three N-vectors, obsi, actind) is 3/4 of a perturb.  Once the data are on the GPU
+    // and every particle has been drawn (setPriors reads the RV span), shrink the singleton's
+    // arrays to what keeps those getters' values: {min, max} of t and y.
+    void slim_host_data()
+    {
+        Data& D = Data::get_instance();
+        if (D.t.size() <= 2) return;
+        const double tmin = D.get_t_min(), tmax = D.get_t_max();
+        const double ymin = D.get_RV_min(), ymax = D.get_RV_max();
+        D.t = {tmin, tmax};
+        D.y = {ymin, ymax};
+        std::vector<double>().swap(D.sig);
+        std::vector<int>().swap(D.obsi);
+        for (auto& a : D.actind) std::vector<double>().swap(a);
+    }
+
     // Parameters of particle `m` -> column `lane` of the staging block.
     void stage(int lane, const RVmodel& m) { stage(0, lane, m); }
     void stage(int g, int lane, const RVmodel& m)
