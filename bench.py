@@ -223,6 +223,41 @@ def run_workload(eng, lanes: int, steps: int, warmup: int, flops_per_eval: float
     return res
 
 
+def predictive_leg(data, flags, device: int, threads: int, B: int = 1184, nt: int = 1000, cpu_B: int = 4):
+    """posterior-predictive curves (deterministic model + GP mean on a time
+    grid) per second through kc_predict with host buffers, beside the CPU restatement of
+    pykima's per-sample loop (oracle/predictive.py) on a few samples."""
+    from kima_b200 import LikelihoodEngine
+    from oracle import predictive as opred
+    from oracle.oracle import Oracle
+    P, nps = make_params(flags, data, B, "max", seed=47)
+    tg = np.linspace(data.t.min(), data.t.max(), nt)
+    with LikelihoodEngine(data, flags, B, device=device) as eng:
+        eng.predict(P, nps, tg)
+        secs, kms = [], []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            m, g = eng.predict(P, nps, tg)
+            secs.append(time.perf_counter() - t0)
+            kms.append(eng.last_kernel_ms())
+        launches = eng.launch_count()
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    t0 = time.perf_counter()
+    err = 0.0
+    for b in range(cpu_B):
+        want = opred.model(orc, flags, data, P, b, nps[b], tg) + opred.gp_mean(orc, flags, data, P, b, nps[b], tg)
+        err = max(err, float(np.max(np.abs(m[b] + g[b] - want)) / (np.abs(want).max() + 1.0)))
+    cpu_s = time.perf_counter() - t0
+    return {"unit": "predictive curves/s", "workload": "QP-GP N=%d Np=%d, %d posterior samples, %d grid times" % (data.N(), NP, B, nt),
+            "value": B / min(secs), "ms_per_call": 1e3 * min(secs), "kernels_ms": min(kms), "gpu_launches": launches,
+            "d2h_bytes_per_call": 2 * 8 * B * nt,
+            "cpu_baseline": {"value": cpu_B / cpu_s, "unit": "predictive curves/s", "cores": threads, "kind": "port",
+                             "sample": "%d samples, numpy/LAPACK restatement of pykima's per-sample loop, %.1f s" % (cpu_B, cpu_s)},
+            "max_rel_err_vs_cpu": err}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -233,6 +268,7 @@ def main():
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--workloads", default="kep,gp")
     ap.add_argument("--skip-sampler", action="store_true")
+    ap.add_argument("--skip-predictive", action="store_true")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -319,6 +355,8 @@ def main():
         out["sampler"] = {"unit": "MCMC steps/s", "lanes": 4096, "cpu_threads": threads,
                           "runs": [sampler_bench.compare(n, 4096, threads, gpu_saves=80, cpu_saves=100)
                                    for n in ("CoRoT7", "51Peg")]}
+    if rank == 0 and world == 1 and not a.skip_predictive and not a.skip_cpu_baseline:
+        out["predictive"] = predictive_leg(data, fg, local, threads)
     if world > 1 and not a.skip_sampler and os.path.exists(os.path.join(ROOT, "host", "_build", "kima_gpu_CoRoT7")):
         # the same end to end at N GPUs: one C++ process per GPU (host/BatchedSampler.h), lanes
         # sharded, the level-creation barrier over NCCL; 4096 lanes per GPU (weak scaling)

@@ -68,6 +68,13 @@ public:
     void set_option(const char* key, int value) { check(kc_set_option(ctx_, key, value)); }
     long long launch_count() const { return (long long)kc_launch_count(ctx_); }
 
+    // posterior-predictive curves of the first B staged parameter vectors
+    // (pykima/results.py:723-855); t_pred == nullptr means the data epochs
+    void predict(int B, int nt, const double* t_pred, int what, double* model_out, double* gp_out)
+    {
+        check(kc_predict(ctx_, B, nt, t_pred, what, model_out, gp_out));
+    }
+
     // one process per GPU: the level-creation barrier (DNest4/code/SamplerImpl.h:306-329)
     static void unique_id(void* id128) { check(kc_comm_unique_id(id128)); }
     void comm_init(int rank, int nranks, const void* id128) { check(kc_comm_init(ctx_, rank, nranks, id128)); }

@@ -194,6 +194,24 @@ int kc_model_mu(kc_ctx* ctx, int lane, double* mu);
 /* C[N][N] (column-major, full symmetric) of lane `lane` (calculate_C). */
 int kc_gp_cov(kc_ctx* ctx, int lane, double* C);
 
+/* ---- posterior-predictive curves --------------
+ * Replaces the per-sample Python loops of pykima's post-processing,
+ *   KimaResults.model()        pykima/results.py:723-797
+ *   GP.predict(y - model, t)   pykima/GP.py:96-112, per sample at results.py:1313-1318
+ * for the first B staged parameter vectors (kc_host_params) at once.
+ *   t_pred   nt grid times (host), or NULL = the data epochs (then nt must be N)
+ *   what     KC_PRED_MODEL: model_out[b*nt + k] = Keplerians (known objects included) +
+ *            vsys + trend at t_pred[k]; at the data epochs also the instrument offsets and
+ *            indicator terms, i.e. calculate_mu without the MA term
+ *            KC_PRED_GP: gp_out[b*nt + k] = K(t_pred[k], t) C^-1 (y - mu), C and mu those of
+ *            the C++ likelihood (src/RVmodel.cpp:186-216, 286-375); NaN where C is not
+ *            positive definite.  Needs GP=true with the standard kernel.
+ * Outputs are host arrays of B*nt doubles (either may be NULL when not asked for). */
+#define KC_PRED_MODEL 1
+#define KC_PRED_GP 2
+int kc_predict(kc_ctx* ctx, int B, int nt, const double* t_pred, int what,
+               double* model_out, double* gp_out);
+
 /* ---- multi-GPU: the level-creation barrier of DNest4 ----------------------
  * (DNest4/code/SamplerImpl.h:306-329).  One rank per GPU. */
 /* Fills 128 bytes with an NCCL unique id (rank 0 calls, then broadcasts). */

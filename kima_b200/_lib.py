@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(HERE, "libkima_cuda.so")
 
 KC_OK = 0
 KC_ERR_ARG, KC_ERR_CUDA, KC_ERR_UNSUPPORTED, KC_ERR_COMM = 1, 2, 3, 4
+KC_PRED_MODEL, KC_PRED_GP = 1, 2
 
 
 class KimaCudaError(RuntimeError):
@@ -54,6 +55,7 @@ SIGNATURES = {
     "kc_true_anomaly": (ctypes.c_int, [_vp, ctypes.c_int, _dp, _dp, _dp, _dp, _dp]),
     "kc_model_mu": (ctypes.c_int, [_vp, ctypes.c_int, _dp]),
     "kc_gp_cov": (ctypes.c_int, [_vp, ctypes.c_int, _dp]),
+    "kc_predict": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _dp, ctypes.c_int, _dp, _dp]),
     "kc_comm_unique_id": (ctypes.c_int, [_vp]),
     "kc_comm_init": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _vp]),
     "kc_allgather_above": (ctypes.c_int, [_vp, _dp, ctypes.c_int, _dp, ctypes.c_int,

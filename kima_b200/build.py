@@ -15,7 +15,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libkima_cuda.so")
 HOSTCHECK = os.path.join(HERE, "libkc_hostcheck.so")
 
-CU_SOURCES = ["kc_api.cu", "kc_keplerian.cu", "kc_gp.cu", "kc_gp_blocked.cu", "kc_gp_small.cu", "kc_celerite.cu", "kc_comm.cu", "kc_peak.cu"]
+CU_SOURCES = ["kc_api.cu", "kc_keplerian.cu", "kc_gp.cu", "kc_gp_blocked.cu", "kc_gp_small.cu", "kc_celerite.cu", "kc_predict.cu", "kc_comm.cu", "kc_peak.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v", "-diag-suppress", "550",

@@ -70,6 +70,9 @@ struct kc_ctx {
     void* d_comm_buf = nullptr;
     size_t comm_buf_bytes = 0;
     void* d_flush = nullptr;
+    // posterior-predictive scratch, grown on demand
+    double* d_pred = nullptr;
+    size_t pred_doubles = 0;
 };
 
 namespace {
@@ -191,6 +194,7 @@ int kc_destroy(kc_ctx* c)
     cudaFree(c->d_counter);
     cudaFree(c->d_comm_buf);
     cudaFree(c->d_flush);
+    cudaFree(c->d_pred);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -524,6 +528,61 @@ int kc_gp_cov(kc_ctx* c, int lane, double* C)
     CU(cudaMemcpyAsync(C, d, nb, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaFree(d));
+    return KC_OK;
+}
+
+int kc_predict(kc_ctx* c, int B, int nt, const double* t_pred, int what, double* model_out,
+               double* gp_out)
+{
+    int rc = check_ready(c, B);
+    if (rc) return rc;
+    const bool want_model = (what & KC_PRED_MODEL) != 0, want_gp = (what & KC_PRED_GP) != 0;
+    if (!want_model && !want_gp) return fail(KC_ERR_ARG, "what must name KC_PRED_MODEL and/or KC_PRED_GP");
+    if (what & ~(KC_PRED_MODEL | KC_PRED_GP)) return fail(KC_ERR_ARG, "unknown bits in what");
+    if (nt <= 0) return fail(KC_ERR_ARG, "nt <= 0");
+    if (!t_pred && nt != c->N) return fail(KC_ERR_ARG, "t_pred is null (the data epochs) but nt != N");
+    if (want_model && !model_out) return fail(KC_ERR_ARG, "model_out is null");
+    if (want_gp && !gp_out) return fail(KC_ERR_ARG, "gp_out is null");
+    if (want_gp && !(c->F.GP && c->F.kernel == 0))
+        return fail(KC_ERR_UNSUPPORTED, "KC_PRED_GP needs GP=true with the standard kernel");
+    if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is in flight");
+    CU(cudaSetDevice(c->device));
+    if (B == 0) return KC_OK;
+    const size_t out_d = (size_t)B * nt;
+    const size_t need = (size_t)nt + (want_model ? out_d : 0) + (want_gp ? out_d + (size_t)B * c->N : 0);
+    if (need > c->pred_doubles) {
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_pred);
+        c->d_pred = nullptr;
+        c->pred_doubles = 0;
+        CU(cudaMalloc(&c->d_pred, sizeof(double) * need));
+        c->pred_doubles = need;
+    }
+    double* d_t = c->d_pred;
+    double* d_model = d_t + nt;
+    double* d_gp = d_model + (want_model ? out_d : 0);
+    double* d_alpha = d_gp + (want_gp ? out_d : 0);
+    if (t_pred) CU(cudaMemcpyAsync(d_t, t_pred, sizeof(double) * nt, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
+                         sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_np, c->h_np, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
+    kc::KParams p = make_params(c, B, c->d_logL);
+    int n = 0;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    cudaError_t e = cudaSuccess;
+    if (want_model)
+        e = kc::launch_predict_model(p, c->kepler_mode, t_pred ? d_t : nullptr, nt, d_model, c->stream, &n);
+    if (e == cudaSuccess && want_gp) {
+        kc::GpPredict pr{t_pred ? d_t : nullptr, nt, d_alpha, d_gp};
+        e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n, &pr);
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "predict launch");
+    CU(cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->launches += n;
+    if (want_model) CU(cudaMemcpyAsync(model_out, d_model, sizeof(double) * out_d, cudaMemcpyDeviceToHost, c->stream));
+    if (want_gp) CU(cudaMemcpyAsync(gp_out, d_gp, sizeof(double) * out_d, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
     return KC_OK;
 }
 

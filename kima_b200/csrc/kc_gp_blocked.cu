@@ -54,7 +54,7 @@ struct GpbStep {
     int ntile;      // update kernel: row tiles per lane
 };
 
-static size_t gpb_ld(int N) { return ((size_t)N + 1 + 15) & ~(size_t)15; }
+size_t gpb_ld(int N) { return ((size_t)N + 1 + 15) & ~(size_t)15; }
 size_t gpb_slot_doubles(int N) { return gpb_ld(N) * (size_t)N + gpb::PAD_DOUBLES; }
 size_t gpb_lane_bytes() { return sizeof(GpLane); }
 
@@ -534,7 +534,7 @@ __global__ void gpb_finish_kernel(const KParams p, const GpLane* __restrict__ la
 }
 
 cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
-                              cudaStream_t stream, int* n_launches)
+                              cudaStream_t stream, int* n_launches, const GpPredict* pred)
 {
     using namespace gpb;
     if (p.B <= 0) return cudaSuccess;
@@ -598,6 +598,10 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
             *n_launches += 1;
             e = cudaGetLastError();
             if (e != cudaSuccess) return e;
+            if (pred) {  // the wave's factors are about to be overwritten by the next one
+                e = launch_gp_predict_wave(p, ws_g, w.slot_doubles, lanes_g, lane0, n, *pred, st_g, n_launches);
+                if (e != cudaSuccess) return e;
+            }
         }
         if (g > 0) {
             e = cudaEventRecord(w.join[g - 1], st_g);

@@ -165,6 +165,18 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
 // loops over the columns with a rotating register window (x[k] holds element c+k at step c),
 // so register indices stay static and the body stays in the instruction cache; the window
 // narrows from 31 to 15 for the second half of the columns.
+#ifndef KC_GPS_SLEEP_T
+#define KC_GPS_SLEEP_T 20
+#endif
+#ifndef KC_GPS_SLEEP_D
+#define KC_GPS_SLEEP_D 40
+#endif
+#ifndef KC_GPS_SLEEP_F
+#define KC_GPS_SLEEP_F 40
+#endif
+#ifndef KC_GPS_TBATCH
+#define KC_GPS_TBATCH 1
+#endif
 template <int W>
 __device__ __forceinline__ void trsm_steps(double (&x)[T], const double* S, int ldj, int c_lo, int c_hi,
                                            const double* dinv, double* mine, bool ok, double& q,
@@ -174,7 +186,8 @@ __device__ __forceinline__ void trsm_steps(double (&x)[T], const double* S, int 
     for (int c = c_lo; c < c_hi; c++) {
         // follow the diag warp column by column: column c of L_JJ and 1/L(c,c) are published
         if (seen < need0 + c + 1) {
-            while ((seen = ld_uniform(col_done, lane)) < need0 + c + 1) __nanosleep(20);
+            const int want = need0 + min((c / KC_GPS_TBATCH + 1) * KC_GPS_TBATCH, c_hi);
+            while ((seen = ld_uniform(col_done, lane)) < want) __nanosleep(KC_GPS_SLEEP_T);
         }
         const double x0 = x[0] * dinv[c];
         if (ok) mine[(size_t)c * ldj] = x0;
@@ -305,7 +318,7 @@ __global__ void __launch_bounds__(NW * 32, 12 / NW) gps_kernel(const KParams p)
         // ---- diag role ----
         for (int J = 0; J < nb; J++) {
             const int j0 = T * J;
-            while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(40);
+            while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(KC_GPS_SLEEP_D);
             PROF(0);
             const int nv = min(T, N - j0);
             const int ldj = H.ld[J];
@@ -356,7 +369,7 @@ __global__ void __launch_bounds__(NW * 32, 12 / NW) gps_kernel(const KParams p)
                         const int it = claim(H, lane);
                         if (it < total_items) gen_item(H, tS, nS, M, N, it, nb, lane);
                     } else {
-                        __nanosleep(40);
+                        __nanosleep(KC_GPS_SLEEP_F);
                     }
                 }
             }

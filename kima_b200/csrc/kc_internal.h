@@ -53,10 +53,24 @@ struct GpWorkspace {
     cudaStream_t aux[3];
     cudaEvent_t fork, join[3];
 };
+// posterior-predictive GP mean, computed wave by wave while the factors are still in HBM
+// (kc_predict.cu)
+struct GpPredict {
+    const double* t_pred;  // device [nt], null = the data epochs
+    int nt;
+    double* alpha;         // device [B][N]: C^-1 r per lane
+    double* gp_out;        // device [B][nt]
+};
+size_t gpb_ld(int N);
 size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();
 cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
-                              cudaStream_t stream, int* n_launches);
+                              cudaStream_t stream, int* n_launches, const GpPredict* pred = nullptr);
+cudaError_t launch_gp_predict_wave(const KParams& p, const double* ws, size_t slot_doubles,
+                                   const GpLane* lanes, int lane0, int n, const GpPredict& pr,
+                                   cudaStream_t s, int* n_launches);
+cudaError_t launch_predict_model(const KParams& p, int kepler_mode, const double* d_tpred, int nt,
+                                 double* d_out, cudaStream_t s, int* n_launches);
 // small-N path (kc_gp_small.cu): shared-memory-resident, one CTA per particle
 size_t gps_smem_bytes(int N);  // 0 = N does not fit
 cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches);

@@ -136,6 +136,23 @@ class LikelihoodEngine:
         B = self.set_params(params, nps)
         return self.log_likelihood(B)
 
+    # ---- posterior-predictive curves (pykima/results.py:723-855) ------------------------
+    def predict(self, params: np.ndarray, nps: np.ndarray, t: Optional[np.ndarray] = None,
+                model: bool = True, gp: Optional[bool] = None):
+        """Deterministic model and GP predictive mean of every parameter vector on the grid
+        ``t`` (None = the data epochs).  Returns ``(model[B, nt] | None, gp[B, nt] | None)``."""
+        B = self.set_params(params, nps)
+        if gp is None:
+            gp = bool(self.flags.GP) and self.flags.kernel == 0
+        tt = None if t is None else np.ascontiguousarray(t, np.float64)
+        nt = self.data.N() if tt is None else tt.size
+        what = (_lib.KC_PRED_MODEL if model else 0) | (_lib.KC_PRED_GP if gp else 0)
+        m = np.empty((B, nt)) if model else None
+        g = np.empty((B, nt)) if gp else None
+        _lib.check(self.lib.kc_predict(self._ctx, B, nt, None if tt is None else _d(tt), what,
+                                       None if m is None else _d(m), None if g is None else _d(g)))
+        return m, g
+
     @staticmethod
     def likelihood_type_value(logL: np.ndarray) -> np.ndarray:
         """What DNest4's LikelihoodType stores (LikelihoodType.cpp:17-24)."""

@@ -1,0 +1,186 @@
+"""Posterior-predictive path.
+
+CPU part: the oracle's restatement (oracle/predictive.py) against vectors produced by
+pykima's own keplerian() / GP.predict() (tests/golden/make_golden_predictive.py), and the
+sample.txt column map against the reference's CI fixtures.
+GPU part: kc_predict through the C ABI against the oracle and the golden vectors.
+
+Tolerances: deterministic model 1e-10 of its scale against the oracle (same solver);
+1e-7 against pykima (its Newton iteration stops at an L1 step of 1.234e-10 over the whole
+array, keplerian.py:32).  GP mean: 1e-8 of max|mean| against the oracle and pykima (both
+solve with LAPACK; the difference is cond(C) * eps).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from kima_b200 import (KimaCudaError, LikelihoodEngine, ModelFlags, PosteriorPredictive, RVData,
+                       params_from_samples, sample_columns)
+from kima_b200.synthetic import make_data, make_params
+from oracle import predictive as opred
+from oracle.oracle import Oracle
+
+CASES = ["predictive_gp_N60", "predictive_gp_N300_trend", "predictive_kep_N120_hyper"]
+
+
+def load_case(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    flags = ModelFlags(**{k: (bool(v) if isinstance(getattr(ModelFlags(), k), bool) else int(v))
+                          for k, v in json.loads(str(z["flags"])).items()})
+    data = RVData.from_arrays(z["t"], z["y"], z["sig"])
+    return z, flags, data
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_oracle_predictive_against_pykima(name):
+    z, flags, data = load_case(name)
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    P, nps = z["params"], z["nps"]
+    for b in range(nps.size):
+        m = opred.model(orc, flags, data, P, b, nps[b], z["tgrid"])
+        scale = np.abs(z["model_grid"][b]).max() + 1.0
+        assert np.max(np.abs(m - z["model_grid"][b])) <= 1e-7 * scale
+        md = opred.model(orc, flags, data, P, b, nps[b])
+        assert np.max(np.abs(md - z["model_data"][b])) <= 1e-7 * scale
+        if flags.GP:
+            g = opred.gp_mean(orc, flags, data, P, b, nps[b], z["tgrid"])
+            assert np.max(np.abs(g - z["gp_grid"][b])) <= 1e-8 * (np.abs(z["gp_grid"][b]).max() + 1.0)
+
+
+@pytest.mark.parametrize("example,flags,n_inst", [
+    ("51Peg", ModelFlags(npmax=1), 1),
+    ("CoRoT7", ModelFlags(GP=True, hyperpriors=True, npmax=5), 1),
+    ("multi_instrument", ModelFlags(multi_instrument=True, npmax=1), 4),
+    ("studentT", ModelFlags(studentt=True, npmax=1), 1)])
+def test_sample_columns_match_reference_fixtures(example, flags, n_inst):
+    """The column map reproduces the header RVmodel::description() wrote (src/RVmodel.cpp:1011-1091)."""
+    path = os.path.join(GOLDEN, "e2e", example + "_sample_seed43.txt")
+    with open(path) as fh:
+        header = fh.readline().lstrip("#").split()
+    rows = np.atleast_2d(np.loadtxt(path))
+    idx = sample_columns(flags, n_inst, 0)
+    assert idx["n_columns"] == rows.shape[1]
+    # with hyperpriors description() runs "muK" and "Np" together without a separator
+    # (src/RVmodel.cpp:1068-1071): one token short
+    assert len(header) == rows.shape[1] - (1 if flags.hyperpriors else 0)
+    if not flags.hyperpriors:
+        assert header[idx["vsys"].start] == "vsys"
+        assert header[idx["np"].start] == "Np"
+        assert header[idx["P"].start] == "P0" and header[idx["w"].start] == "w0"
+        assert header[idx["jitter"].start] in ("extra_sigma", "jitter1")
+    assert np.all(rows[:, idx["ndim"]] == 5) and np.all(rows[:, idx["npmax"]] == flags.npmax)
+    P, nps = params_from_samples(rows, flags, n_inst, 0)
+    assert np.array_equal(nps, rows[:, idx["np"]].ravel().astype(int))
+    assert np.all(nps >= 0) and np.all(nps <= flags.npmax)
+    with pytest.raises(ValueError):
+        params_from_samples(rows[:, :-1], flags, n_inst, 0)
+
+
+# ---- GPU -------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_gpu_predict_against_pykima_and_oracle(gpu, name):
+    z, flags, data = load_case(name)
+    P, nps = z["params"], z["nps"]
+    B = nps.size
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    with LikelihoodEngine(data, flags, B) as eng:
+        m, g = eng.predict(P, nps, z["tgrid"])
+        md, gd = eng.predict(P, nps, None)
+        assert eng.launch_count() >= 2
+    for b in range(B):
+        scale = np.abs(z["model_grid"][b]).max() + 1.0
+        assert np.max(np.abs(m[b] - z["model_grid"][b])) <= 1e-7 * scale
+        assert np.max(np.abs(m[b] - opred.model(orc, flags, data, P, b, nps[b], z["tgrid"]))) <= 1e-10 * scale
+        assert np.max(np.abs(md[b] - opred.model(orc, flags, data, P, b, nps[b]))) <= 1e-10 * scale
+        if flags.GP:
+            gs = np.abs(z["gp_grid"][b]).max() + 1.0
+            assert np.max(np.abs(g[b] - z["gp_grid"][b])) <= 1e-8 * gs
+            assert np.max(np.abs(g[b] - opred.gp_mean(orc, flags, data, P, b, nps[b], z["tgrid"]))) <= 1e-8 * gs
+            assert np.max(np.abs(gd[b] - opred.gp_mean(orc, flags, data, P, b, nps[b]))) <= 1e-8 * gs
+    if not flags.GP:
+        assert g is None
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("flags,N,n_inst,n_ind", [
+    (ModelFlags(GP=True, npmax=2, multi_instrument=True), 97, 3, 0),
+    (ModelFlags(GP=True, npmax=1, known_object=True, n_known_object=2, trend=True, degree=3), 130, 1, 1),
+    (ModelFlags(GP=True, npmax=3, hyperpriors=True), 1000, 1, 0)])
+def test_gpu_predict_waves_and_flags(gpu, flags, N, n_inst, n_ind):
+    """More lanes than factor slots (several waves, two lane groups), partial blocks,
+    offsets / indicators at the data epochs, known objects on the grid."""
+    data = make_data(N, n_inst=n_inst, n_ind=n_ind)
+    B = 300 if N < 500 else 12
+    P, nps = make_params(flags, data, B, "mix", seed=11)
+    tg = np.linspace(data.t.min() - 5.0, data.t.max() + 5.0, 611)
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    with LikelihoodEngine(data, flags, B, gp_slots=7 if N < 500 else 5) as eng:
+        m, g = eng.predict(P, nps, tg)
+        md, gd = eng.predict(P, nps, None)
+        logL = eng.evaluate(P, nps)
+    for b in list(range(0, B, max(1, B // 9))) + [B - 1]:
+        scale = np.abs(m[b]).max() + 1.0
+        assert np.max(np.abs(m[b] - opred.model(orc, flags, data, P, b, nps[b], tg))) <= 1e-10 * scale
+        assert np.max(np.abs(md[b] - opred.model(orc, flags, data, P, b, nps[b]))) <= 1e-10 * scale
+        want = opred.gp_mean(orc, flags, data, P, b, nps[b], tg)
+        if not np.isfinite(logL[b]):
+            assert np.all(np.isnan(g[b]))
+            continue
+        gs = np.abs(want).max() + 1.0
+        assert np.max(np.abs(g[b] - want)) <= 1e-8 * gs
+        assert np.max(np.abs(gd[b] - opred.gp_mean(orc, flags, data, P, b, nps[b]))) <= 1e-8 * gs
+
+
+@pytest.mark.gpu
+def test_gpu_posterior_predictive_from_sample_rows(gpu):
+    """Rows in sample.txt order -> model / model_stochastic / full_model / residuals."""
+    flags = ModelFlags(GP=True, hyperpriors=True, npmax=5)
+    data = RVData.load(os.path.join(GOLDEN, "e2e", "corot7.txt"), "ms", 2)
+    rows = np.atleast_2d(np.loadtxt(os.path.join(GOLDEN, "e2e", "CoRoT7_sample_seed43.txt")))
+    P, nps = params_from_samples(rows, flags, 1, 0)
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    tg = np.linspace(data.t.min(), data.t.max(), 400)
+    with PosteriorPredictive(data, flags, max_batch=3) as pp:  # forces several calls
+        m = pp.model(rows, tg)
+        s = pp.model_stochastic(rows, tg)
+        f = pp.full_model(rows, tg)
+        res = pp.residuals(rows, full=True)
+    assert m.shape == (rows.shape[0], 400)
+    np.testing.assert_allclose(f, m + s, rtol=0, atol=1e-9)
+    for b in range(rows.shape[0]):
+        scale = np.abs(m[b]).max() + 1.0
+        assert np.max(np.abs(m[b] - opred.model(orc, flags, data, P, b, nps[b], tg))) <= 1e-10 * scale
+        want = opred.gp_mean(orc, flags, data, P, b, nps[b], tg)
+        assert np.max(np.abs(s[b] - want)) <= 1e-8 * (np.abs(want).max() + 1.0)
+        full_d = opred.model(orc, flags, data, P, b, nps[b]) + opred.gp_mean(orc, flags, data, P, b, nps[b])
+        assert np.max(np.abs(res[b] - (data.y - full_d))) <= 1e-8 * (np.abs(full_d).max() + 1.0)
+
+
+@pytest.mark.gpu
+def test_gpu_predict_errors(gpu):
+    d = make_data(40)
+    P, nps = make_params(ModelFlags(npmax=1), d, 4, "mix")
+    with LikelihoodEngine(d, ModelFlags(npmax=1), 4) as eng:
+        with pytest.raises(KimaCudaError):
+            eng.predict(P, nps, np.arange(5.0), gp=True)          # no GP in this model
+        with pytest.raises(KimaCudaError):
+            eng.predict(P, nps, np.arange(5.0), model=False, gp=False)
+        m, g = eng.predict(P, nps, np.arange(5.0) + 50000.0)
+        assert m.shape == (4, 5) and g is None
+    fc = ModelFlags(GP=True, kernel=1, npmax=1)
+    Pc, npc = make_params(fc, d, 2, "mix")
+    with LikelihoodEngine(d, fc, 2) as eng:
+        with pytest.raises(KimaCudaError):
+            eng.predict(Pc, npc, np.arange(5.0), gp=True)         # celerite: not built
