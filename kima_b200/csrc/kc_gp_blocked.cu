@@ -203,7 +203,7 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
     double* LTs = pipe;                                // after the K loop: [32][H_LD], LTs[c][c2] = L11(c2,c)
     double* T21 = pipe + 32 * H_LD;                    // [32][H_LD]: L21 row-major
     __shared__ double dinv_s[NB];
-    __shared__ double colbuf_s[2 * 64];
+    __shared__ __align__(16) double colbuf_s[CHOL_COLBUF];
     __shared__ int fail_s;
     const int warp = tid >> 5, lane = tid & 31;
     const int N = p.N;

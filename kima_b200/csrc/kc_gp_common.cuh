@@ -147,12 +147,19 @@ __device__ __forceinline__ void chol_pivot(double d, double& inv, double& l)
     inv = y;
 }
 
+// Column broadcast buffer of chol32: two parity halves of CHOL_CB_STRIDE doubles.  The lanes
+// read L(c+1..c+W, c) of the finished column as 16-byte pairs, so the column is stored with
+// a shift of one element for even c (element c+1 then sits at an even index either way).
+constexpr int CHOL_CB_STRIDE = 72;
+constexpr int CHOL_COLBUF = 2 * CHOL_CB_STRIDE;
+
 template <int W>
 __device__ __forceinline__ void chol32_steps(double (&s)[32], Chol32State& st, int c_lo, int c_hi, int lane,
                                              int nvalid, double* dinv_out, double* __restrict__ Lout,
                                              size_t ld, double* LT, int lt_ld, double* colbuf,
                                              int* progress, int progress_base)
 {
+    constexpr int NP2 = (W + 1) / 2;
 #pragma unroll 1
     for (int c = c_lo; c < c_hi; c++) {
         if (!(st.d > 0.0)) st.ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
@@ -164,27 +171,51 @@ __device__ __forceinline__ void chol32_steps(double (&s)[32], Chol32State& st, i
         // s'[0] = s[1] - L(c+1,c)^2, the same FMA the update below performs.  Its
         // rsqrt chain (latency-bound) then overlaps the loads + FMAs (issue-bound).
         st.d = __shfl_sync(0xffffffffu, kfma(-lrc, lrc, s[1]), (c + 1) & 31);
-        chol_pivot(st.d, st.inv, st.l);
-        double* cb = colbuf + (c & 1) * 64;
+        const double dn = st.d;
+        const int shift = (c & 1) ^ 1;
+        double* cb = colbuf + (c & 1) * CHOL_CB_STRIDE + shift;
         cb[lane] = lrc;
         cb[lane + 32] = lrc;
         if (lane >= c && lane < nvalid) Lout[(size_t)c * ld + lane] = (lane == c) ? lcc : lrc;
         if (LT) LT[c * lt_ld + lane] = (lane > c) ? lrc : 0.0;
         __syncwarp();
         if (progress && lane == 0) st_release_cta(progress, progress_base + c + 1);
-        const double* col = cb + c;
-        // all loads first, then the FMAs: left alone the compiler pairs each load with its
-        // FMA through one register and the step costs W shared-memory latencies
-        double cv[W + 1];
+        // col2[j] = { L(c+1+2j, c), L(c+2+2j, c) }: c + 1 + shift is even
+        const double2* col2 = reinterpret_cast<const double2*>(cb + c + 1);
+        double2 cv[NP2];
 #pragma unroll
-        for (int k = 1; k <= W; k++) cv[k] = col[k];  // col[k] = L(c+k, c)
-#pragma unroll
-        for (int k = 1; k <= W; k += 8)
-            asm volatile("" : "+d"(cv[k]), "+d"(cv[k + 1]), "+d"(cv[k + 2]), "+d"(cv[k + 3]),
-                              "+d"(cv[k + 4]), "+d"(cv[k + 5]), "+d"(cv[k + 6 <= W ? k + 6 : W]),
-                              "+d"(cv[k + 7 <= W ? k + 7 : W]));
-#pragma unroll
-        for (int k = 1; k <= W; k++) s[k - 1] = kfma(-lrc, cv[k], s[k]);
+        for (int j = 0; j < NP2; j++) cv[j] = col2[j];
+        // A warp issues in order: the pivot chain (chol_pivot, ~10 dependent FP64 operations)
+        // is written out here stage by stage with a group of the W independent update FMAs
+        // after every stage, so that its latency is covered by them instead of preceding them.
+        constexpr int G = (W + 7) / 8;
+#define CHOL_FMAS(g)                                                                            \
+        _Pragma("unroll") for (int k = 1 + (g) * G; k <= W && k <= ((g) + 1) * G; k++) {        \
+            const double v = ((k - 1) & 1) ? cv[(k - 1) >> 1].y : cv[(k - 1) >> 1].x;           \
+            s[k - 1] = kfma(-lrc, v, s[k]);                                                     \
+        }                                                                                       \
+        asm volatile("" : "+d"(y), "+d"(e), "+d"(l), "+d"(s[(g) * G]));
+        double y = rsqrt_seed(dn), e = 0.0, l = 0.0;
+        CHOL_FMAS(0)
+        double hy = 0.5 * y;
+        e = kfma(-dn * y, hy, 0.5);
+        CHOL_FMAS(1)
+        y = kfma(y, e, y);
+        CHOL_FMAS(2)
+        hy = 0.5 * y;
+        l = dn * y;
+        CHOL_FMAS(3)
+        e = kfma(-l, hy, 0.5);
+        CHOL_FMAS(4)
+        y = kfma(y, e, y);
+        CHOL_FMAS(5)
+        e = kfma(-l, l, dn);
+        CHOL_FMAS(6)
+        l = kfma(e, 0.5 * y, l);
+        CHOL_FMAS(7)
+#undef CHOL_FMAS
+        st.inv = y;
+        st.l = l;
         s[W] = 0.0;
     }
 }
@@ -195,9 +226,9 @@ __device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, 
                                                      double* LT, int lt_ld, double* colbuf,
                                                      int* progress = nullptr, int progress_base = 0)
 {
-    // colbuf: [2][64] doubles of shared memory; the finished column is broadcast through it
-    // (written twice, 32 apart, so that L(c+k, c) is colbuf[c+k] without wrap-around;
-    // double-buffered by the parity of c: one __syncwarp per column)
+    // colbuf: CHOL_COLBUF doubles of 16-byte-aligned shared memory; the finished column is
+    // broadcast through it (written twice, 32 apart, so that L(c+k, c) is read without
+    // wrap-around; double-buffered by the parity of c: one __syncwarp per column)
     Chol32State st;
     st.ok = true;
     st.lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant

@@ -33,7 +33,7 @@ namespace gps {
 constexpr int T = 32;
 constexpr int REGS_PER_THREAD = 168;  // 1 x 12, 2 x 6 or 3 x 4 warps fill the register file
 constexpr int MAXBLK = 8;
-constexpr int GW = 2;              // columns per generation item (one qp_kernel2 call per lane)
+constexpr int GW = 4;              // columns per generation item: two qp_kernel2 calls, four independent chains per lane
 constexpr int GQ = T / GW;         // generation items per 32x32 tile
 constexpr int SLACK = 64;          // doubles past the last block column (strips read, never use, rows > N)
 constexpr size_t SMEM_LIMIT = 227 * 1024;
@@ -43,7 +43,7 @@ struct Hdr {
     ParticleScalars sc;
     GpConsts g;
     double dinv[T];
-    double colbuf[128];
+    alignas(16) double colbuf[CHOL_COLBUF];
     double quad;
     int base[MAXBLK];
     int ld[MAXBLK];
@@ -82,7 +82,7 @@ __device__ __forceinline__ int ld_uniform(const int* p, int lane)
     return __shfl_sync(0xffffffffu, v, 0);
 }
 
-// One generation item: rows 32I .. 32I+31 (a row per lane) x 8 columns of block column J.
+// One generation item: rows 32I .. 32I+31 (a row per lane) x GW columns of block column J.
 __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS, double* M,
                                          int N, int item, int nb, int lane)
 {
@@ -98,7 +98,7 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
     double* dst = M + H.base[J] + (size_t)(GW * q) * H.ld[J] + (row - j0);
     const int ldj = H.ld[J];
     const GpConsts g = H.g;
-#pragma unroll 1
+#pragma unroll
     for (int cc = 0; cc < GW; cc += 2) {
         const int ca = c0 + cc, cb = ca + 1;
         // t[i]-t[j] with i<j (:193): i is the column (smaller index) of the lower triangle
