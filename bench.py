@@ -146,10 +146,12 @@ def cpu_arm(kind_pref: str, flags: ModelFlags, data, lanes: int, threads: int, r
 NCU_TRAFFIC = {
     "kep": {"kernel": "keplerian_warp_kernel<0,0>", "traffic": 3.50e6,
             "algorithmic_bytes": 8192 * (52 * 8 + 4 + 8) + 4 * 8000,
-            "source": "profiles/ncu_keplerian_r01b.json (8192 lanes: parameters in, logL out, data arrays once)"},
-    "gp": {"kernel": "gpb_update_kernel (block column 8 of 16, j0=512)", "traffic": 2.84e9 + 0.25e9,
-           "algorithmic_bytes": 1184 * (576 * 512 + 512 * 64) * 8,
-           "source": "profiles/ncu_gp_update_r01b.json (1184 lanes: panel rows re-read once, L tile written once)"},
+            "source": "profiles/ncu_kep_r01d.json (8192 lanes: parameters in, logL out, data arrays once)"},
+    "gp": {"kernel": "gpb_update_kernel (block column 8 of 16, j0=512, one lane group of 592)",
+           "traffic": 1.424e9 + 0.118e9,
+           "algorithmic_bytes": 592 * ((425 + 64) * 512 + 425 * 64) * 8,
+           "source": "profiles/ncu_gp_r01d.json (592 lanes: 425 panel rows x 512 columns and the 64-row block "
+                     "row read once, 425 x 64 tile of L written once)"},
 }
 
 
@@ -214,8 +216,9 @@ def run_workload(eng, lanes: int, steps: int, warmup: int, flops_per_eval: float
                      "traffic_detail": NCU_TRAFFIC[key],
                      "pipe": "FP64 tensor (DMMA.8x8x4)" if key == "gp" else "FP64 vector (DFMA); no tensor-core instructions",
                      "flops_per_eval": flops_per_eval,
-                     "per": "one step = one evaluation of all lanes (GP: 34 launches; the dominant "
-                            "kernel gpb_update_kernel is 85% of the step, profiles/launches_gp_r01b.csv)",
+                     "per": "one step = one evaluation of all lanes (Keplerian: 1 launch; GP: 68 launches, two "
+                            "lane groups x (prep + 16 diag + 16 update + finish); the dominant kernel "
+                            "gpb_update_kernel is 82% of the step's kernel time, profiles/launches_r01d.csv)",
                      "peak_source": "kc_measure_fp64_peak in this run (max of DFMA / DMMA m8n8k4); "
                                     "MEASURED_PEAKS.json has no FP64 entry"},
         "clocks": clocks, "wall_s_timed_region": wall, "finite": bool(np.all(np.isfinite(out))),
