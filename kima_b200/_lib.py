@@ -6,6 +6,7 @@ import ctypes
 import os
 
 from .flags import CLayout, CModelFlags
+from .sampler_types import SAMPLER_SIGNATURES
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkima_cuda.so")
@@ -64,6 +65,9 @@ SIGNATURES = {
     "kc_allreduce_levels": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     "kc_comm_destroy": (ctypes.c_int, [_vp]),
 }
+
+# ... and every symbol include/kima_sampler.h declares
+SIGNATURES.update(SAMPLER_SIGNATURES)
 
 _lib = None
 

@@ -15,7 +15,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libkima_cuda.so")
 HOSTCHECK = os.path.join(HERE, "libkc_hostcheck.so")
 
-CU_SOURCES = ["kc_api.cu", "kc_keplerian.cu", "kc_gp.cu", "kc_gp_blocked.cu", "kc_gp_small.cu", "kc_celerite.cu", "kc_predict.cu", "kc_comm.cu", "kc_peak.cu"]
+CU_SOURCES = ["kc_api.cu", "kc_keplerian.cu", "kc_gp.cu", "kc_gp_blocked.cu", "kc_gp_small.cu", "kc_celerite.cu", "kc_predict.cu", "kc_comm.cu", "kc_peak.cu", "kc_sampler.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v", "-diag-suppress", "550",
@@ -38,7 +38,8 @@ def _newer(target: str, deps) -> bool:
 
 def _deps():
     d = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
-    d.append(os.path.join(HERE, "..", "include", "kima_cuda.h"))
+    for h in ("kima_cuda.h", "kima_sampler.h", "kc_philox.h"):
+        d.append(os.path.join(HERE, "..", "include", h))
     d.append(os.path.abspath(__file__))
     return d
 
@@ -75,7 +76,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     # host instantiation of the device math headers, for CPU unit tests only
     cxx = shutil.which("g++") or "g++"
     r = subprocess.run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-o", HOSTCHECK,
-                        os.path.join(CSRC, "host_check.cpp")], capture_output=True, text=True)
+                        os.path.join(CSRC, "host_check.cpp"), os.path.join(CSRC, "host_check_sampler.cpp")],
+                       capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("host_check build failed:\n%s\n%s" % (r.stdout, r.stderr))
     return LIB

@@ -6,12 +6,13 @@
 #include <cstring>
 #include <string>
 #include <vector>
-#include "kc_internal.h"
+#include "kc_ctx.h"
 
 namespace {
-
 thread_local std::string g_err;
+}
 
+namespace kc {
 int fail(int code, const std::string& msg)
 {
     g_err = msg;
@@ -22,6 +23,10 @@ int fail_cuda(cudaError_t e, const char* what)
     g_err = std::string(what) + ": " + cudaGetErrorString(e);
     return KC_ERR_CUDA;
 }
+}  // namespace kc
+using kc::fail;
+using kc::fail_cuda;
+namespace {
 #define CU(call)                                                  \
     do {                                                          \
         cudaError_t e_ = (call);                                  \
@@ -30,55 +35,12 @@ int fail_cuda(cudaError_t e, const char* what)
 
 }  // namespace
 
-struct kc_ctx {
-    int device = 0;
-    int sm_count = 0;
-    cudaStream_t stream = nullptr;
-    // data
-    int N = 0, n_inst = 1, n_ind = 0;
-    double M0_epoch = 0, t_middle = 0;
-    double *d_t = nullptr, *d_y = nullptr, *d_sig2 = nullptr, *d_actind = nullptr;
-    int32_t* d_obsi = nullptr;
-    bool have_data = false;
-    // model
-    kc_model_flags F{};
-    kc_layout L{};
-    bool configured = false;
-    int max_batch = 0, ld = 0;
-    double *h_params = nullptr, *d_params = nullptr;
-    int32_t *h_np = nullptr, *d_np = nullptr;
-    double *d_logL = nullptr, *h_logL = nullptr;
-    int* d_counter = nullptr;
-    // GP
-    kc::GpWorkspace gp{};
-    int gp_streams_opt = 2;
-    double* d_resid = nullptr;   // kernel = celerite: residuals, [N][ld]
-    // options / instrumentation
-    int kepler_mode = 0;
-    int gp_slots_opt = 0;
-    int gp_small_opt = 1;   // 1 = shared-memory-resident kernel whenever N fits, 0 = always blocked
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    bool timed = false;
-    float last_ms = 0.f;
-    int64_t launches = 0;
-    double* pending_out = nullptr;
-    int pending_B = 0;
-    // comm
-    void* nccl_lib = nullptr;
-    void* nccl_comm = nullptr;
-    int rank = 0, nranks = 1;
-    void* d_comm_buf = nullptr;
-    size_t comm_buf_bytes = 0;
-    void* d_flush = nullptr;
-    // posterior-predictive scratch, grown on demand
-    double* d_pred = nullptr;
-    size_t pred_doubles = 0;
-};
 
 namespace {
 
 void free_model(kc_ctx* c)
 {
+    kc::sampler_free(c);
     if (c->h_params) cudaFreeHost(c->h_params);
     if (c->h_np) cudaFreeHost(c->h_np);
     if (c->h_logL) cudaFreeHost(c->h_logL);
@@ -104,21 +66,25 @@ void free_data(kc_ctx* c)
     c->have_data = false;
 }
 
-kc::KParams make_params(kc_ctx* c, int B, double* d_logL)
+kc::KParams make_params(kc_ctx* c, int B, double* d_logL, const double* d_params = nullptr,
+                        const int32_t* d_np = nullptr)
 {
     kc::KParams p{};
     p.t = c->d_t; p.y = c->d_y; p.sig2 = c->d_sig2; p.obsi = c->d_obsi; p.actind = c->d_actind;
     p.N = c->N; p.n_inst = c->n_inst; p.n_ind = c->n_ind;
     p.M0_epoch = c->M0_epoch; p.t_middle = c->t_middle;
     p.F = c->F; p.L = c->L;
-    p.params = c->d_params; p.np = c->d_np; p.ld = c->ld; p.B = B;
+    p.params = d_params ? d_params : c->d_params; p.np = d_np ? d_np : c->d_np; p.ld = c->ld; p.B = B;
     p.logL = d_logL; p.counter = c->d_counter;
     return p;
 }
 
-int run_kernels(kc_ctx* c, int B, double* d_logL)
+}  // namespace
+
+namespace kc {
+int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np)
 {
-    kc::KParams p = make_params(c, B, d_logL);
+    kc::KParams p = make_params(c, B, d_logL, d_params, d_np);
     int n = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
@@ -143,7 +109,10 @@ int check_ready(kc_ctx* c, int B)
     if (B < 0 || B > c->max_batch) return fail(KC_ERR_ARG, "B outside [0, max_batch]");
     return KC_OK;
 }
-
+}  // namespace kc
+using kc::check_ready;
+namespace {
+int run_kernels(kc_ctx* c, int B, double* d_logL) { return kc::run_kernels(c, B, d_logL, nullptr, nullptr); }
 }  // namespace
 
 namespace kc {

@@ -21,6 +21,8 @@ from kima_b200.flags import CLayout, CModelFlags, ModelFlags
 HERE = os.path.dirname(os.path.abspath(__file__))
 PORT_SO = os.path.join(HERE, "libkima_oracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libkima_ref.so")
+# the reference sources minus DNest4/code/RNG.cpp, on the counter-based stream (oracle/philox_rng.cpp)
+PHILOX_SO = os.path.join(HERE, "_ref", "libkima_ref_philox.so")
 REFERENCE_ROOT = "/root/reference"
 
 _dp = ctypes.POINTER(ctypes.c_double)
@@ -52,10 +54,13 @@ def have_reference() -> bool:
 
 class Oracle:
     def __init__(self, kind: str = "port"):
-        if kind not in ("port", "reference"):
+        if kind not in ("port", "reference", "philox"):
             raise ValueError(kind)
+        path = PORT_SO if kind == "port" else (REF_SO if kind == "reference" else PHILOX_SO)
+        # "philox" is the reference harness as well, in a shared object of its own (own Data
+        # singleton, own flags) that also holds the sampler harness (oracle/ref_sampler.py)
+        kind = "port" if kind == "port" else "reference"
         self.kind = kind
-        path = PORT_SO if kind == "port" else REF_SO
         if not os.path.exists(path):
             raise FileNotFoundError(
                 "%s is not built: run `make -C oracle %s`" % (path, "oracle" if kind == "port" else "ref"))
