@@ -1,7 +1,7 @@
 // Device-side proposals and accept logic: the per-lane part of
 // one DNest4 MCMC step, restated from the reference operation for operation and random draw
 // for random draw, so that the unmodified reference sampler driven by the same stream
-// (oracle/philox_rng.cpp) takes the same decisions.
+// (the RNG stand-in of the test harness) takes the same decisions.
 //
 //   Sampler::mcmc_thread / update_particle / update_level_assignment
 //                                   DNest4/code/SamplerImpl.h:134-265
@@ -25,9 +25,12 @@
 #include "../../include/kima_sampler.h"
 #include "../../include/kc_philox.h"
 
+// KS_FN functions are real calls on the device (__noinline__): the step is branchy scalar code
+// whose call tree (16 distributions x cdf / cdf_inverse / log_pdf under every move of
+// perturb) would otherwise be inlined into each of the kernels that reach it.
 #if defined(__CUDACC__)
 #define KS_HD __host__ __device__ __forceinline__
-#define KS_FN __host__ __device__
+#define KS_FN __host__ __device__ __noinline__
 #else
 #define KS_HD inline
 #define KS_FN inline
@@ -41,8 +44,8 @@ constexpr double KS_PI = 3.14159265358979323846;  // M_PI
 // ---- the lane's random stream (include/kc_philox.h) ---------------------------------------
 struct Rng {
     uint64_t key, ctr;
-    KS_HD double rand() { return kc_philox_uniform(key, ctr++); }
-    KS_HD double randn()
+    KS_FN double rand() { return kc_philox_uniform(key, ctr++); }
+    KS_FN double randn()
     {
         const double u1 = rand();
         const double u2 = rand();
@@ -54,7 +57,7 @@ struct Rng {
         const double u = rand();
         return n / sqrt(-log(u));
     }
-    KS_HD double randh()  // RNG.cpp:44-49 (randh_is_randh2 is false everywhere in kima)
+    KS_FN double randh()  // RNG.cpp:44-49 (randh_is_randh2 is false everywhere in kima)
     {
         const double t = randt2();
         const double n = randn();

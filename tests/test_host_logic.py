@@ -14,7 +14,8 @@ from kima_b200.dist import merge_above_and_create_level, shard_lanes
 
 
 def test_library_exports_every_declared_symbol():
-    hdr = open(os.path.join(ROOT, "include", "kima_cuda.h")).read()
+    hdr = open(os.path.join(ROOT, "include", "kima_cuda.h")).read() + \
+        open(os.path.join(ROOT, "include", "kima_sampler.h")).read()
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
     declared = set(re.findall(r"\b(kc_[A-Za-z0-9_]+)\s*\(", hdr)) - {"kc_layout_from_flags"}
     assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
