@@ -298,6 +298,211 @@ class BatchedSampler : public Sampler<ModelType> {
         }
     }
 
+
+    // ---- device-side proposals (KIMA_DEVICE_PROPOSALS=1) ----------
+    // mcmc_thread of every lane runs on the GPU (include/kima_sampler.h): the particles live in
+    // HBM, a block of thread_steps steps is one asynchronous enqueue, and the host only does the
+    // thread-0 duties of run_thread (SamplerImpl.h:296-331) and do_bookkeeping (:377-440) between
+    // blocks.  The algorithm is the reference's; the lanes' random streams are counter-based
+    // (include/kc_philox.h), so the chains are not the reference's mt19937 chains: this path is
+    // opt-in, the default stays byte-identical.  rngs[0] (bookkeeping draws) stays the host's.
+    unsigned int seed0 = 0;
+    unsigned int deletions_dev = 0;
+
+    static bool device_proposals_requested()
+    {
+        const char* e = std::getenv("KIMA_DEVICE_PROPOSALS");
+        return e && std::atoi(e) != 0;
+    }
+
+    // kill_lagging_particles (SamplerImpl.h:534-587) with the copies done in HBM: same draws from
+    // rngs[0], same messages
+    void kill_lagging_device()
+    {
+        const size_t n = this->particles.size();
+        std::vector<bool> good(n, true);
+        double max_log_push = -std::numeric_limits<double>::max();
+        unsigned int num_bad = 0;
+        double kill_probability = 0.0;
+        for (size_t i = 0; i < n; ++i) {
+            if (this->log_push(this->level_assignments[i]) > max_log_push)
+                max_log_push = this->log_push(this->level_assignments[i]);
+            kill_probability = pow(1.0 - 1.0 / (1.0 + exp(-this->log_push(this->level_assignments[i]) - 4.0)), 3);
+            if (this->rngs[0].rand() <= kill_probability) {
+                good[i] = false;
+                ++num_bad;
+            }
+        }
+        if (num_bad >= n) return;
+        std::vector<int32_t> dst, src;
+        for (size_t i = 0; i < n; ++i) {
+            if (good[i]) continue;
+            int i_copy;
+            do {
+                i_copy = this->rngs[0].rand_int((int)n);
+            } while (!good[i_copy] ||
+                     this->rngs[0].rand() >= exp(this->log_push(this->level_assignments[i_copy]) - max_log_push));
+            dst.push_back((int32_t)i);
+            src.push_back((int32_t)i_copy);
+            this->log_likelihoods[i] = this->log_likelihoods[i_copy];
+            this->level_assignments[i] = this->level_assignments[i_copy];
+            ++deletions_dev;
+            std::cout << "# Replacing lagging particle.";
+            std::cout << " This has happened " << deletions_dev;
+            std::cout << " times." << std::endl;
+        }
+        evaluator->sampler_ctx().sampler_copy_particles((int)dst.size(), dst.data(), src.data());
+    }
+
+    // save_particle (SamplerImpl.h:503-531): the one particle that is printed comes back from HBM
+    void save_particle_device()
+    {
+        ++this->count_saves;
+        this->count_mcmc_steps_since_save = 0;
+        if (!this->save_to_disk) return;
+        if (this->count_saves % this->thin_print == 0)
+            std::cout << "# Saving particle to disk. N = " << this->count_saves << "." << std::endl;
+        std::fstream fout;
+        const int which = this->rngs[0].rand_int((int)this->particles.size());
+        evaluator->sampler_get_particle(which, this->particles[which]);
+        fout.open(this->options.sample_file, std::ios::out | std::ios::app);
+        this->particles[which].print(fout);
+        fout << std::endl;
+        fout.close();
+        fout.open(this->options.sample_info_file, std::ios::out | std::ios::app);
+        fout << std::setprecision(12);
+        fout << this->level_assignments[which] << ' ';
+        fout << this->log_likelihoods[which].get_value() << ' ';
+        fout << this->log_likelihoods[which].get_tiebreaker() << ' ';
+        fout << which << std::endl;
+        fout.close();
+    }
+
+    // do_bookkeeping (SamplerImpl.h:377-440), particles in HBM
+    void bookkeeping_device()
+    {
+        bool created_level = false;
+        if (!this->enough_levels(this->levels) && (this->all_above.size() >= this->options.new_level_interval)) {
+            std::sort(this->all_above.begin(), this->all_above.end());
+            const int index = static_cast<int>((1. - 1. / this->compression) * this->all_above.size());
+            std::cout << "# Creating level " << this->levels.size() << " with log likelihood = ";
+            std::cout << std::setprecision(12);
+            std::cout << this->all_above[index].get_value() << "." << std::endl;
+            this->levels.push_back(Level(this->all_above[index]));
+            this->all_above.erase(this->all_above.begin(), this->all_above.begin() + index + 1);
+            if (this->enough_levels(this->levels)) {
+                const double reg = this->options.new_level_interval * sqrt(this->options.lambda);
+                Level::renormalise_visits(this->levels, static_cast<int>(reg));
+                this->all_above.clear();
+                this->options.max_num_levels = this->levels.size();
+                std::cout << "# Done creating levels." << std::endl;
+            } else {
+                kill_lagging_device();
+            }
+            created_level = true;
+        }
+        Level::recalculate_log_X(this->levels, this->compression,
+                                 this->options.new_level_interval * sqrt(this->options.lambda));
+        if (created_level) this->save_levels();
+        if (this->count_mcmc_steps_since_save >= this->options.save_interval) {
+            save_particle_device();
+            if (!created_level) this->save_levels();
+        }
+        // record holder (:433-439)
+        size_t best = 0;
+        for (size_t i = 1; i < this->log_likelihoods.size(); ++i)
+            if (this->log_likelihoods[best] < this->log_likelihoods[i]) best = i;
+        if (this->best_ever_log_likelihood < this->log_likelihoods[best]) {
+            evaluator->sampler_get_particle((int)best, this->particles[best]);
+            this->best_ever_particle = this->particles[best];
+            this->best_ever_log_likelihood = this->log_likelihoods[best];
+        }
+    }
+
+    // false = the model has a prior without a device counterpart: the caller runs host proposals
+    bool run_device()
+    {
+        if (world() > 1) throw std::invalid_argument("KIMA_DEVICE_PROPOSALS runs in one process per run for now");
+        const unsigned int T = this->num_threads, P = this->options.num_particles;
+        const size_t n = this->particles.size();
+        kc_sampler_config cfg{};
+        cfg.lanes = (int32_t)T;
+        cfg.num_particles = (int32_t)P;
+        cfg.max_steps = (int32_t)this->options.thread_steps;
+        cfg.max_levels = this->options.max_num_levels ? (int32_t)this->options.max_num_levels : 1024;
+        cfg.lambda = this->options.lambda;
+        cfg.beta = this->options.beta;
+        cfg.seed = seed0;
+        cfg.lane0 = 0;
+        const std::string bad = evaluator->sampler_create(this->particles[0], cfg);
+        if (!bad.empty()) {
+            std::cerr << "# KIMA_DEVICE_PROPOSALS: " << bad << " has no device counterpart; proposals stay on the host"
+                      << std::endl;
+            return false;
+        }
+        std::vector<double> logl(n), tb(n);
+        std::vector<int32_t> level(n);
+        for (size_t i = 0; i < n; ++i) {
+            logl[i] = this->log_likelihoods[i].get_value();
+            tb[i] = this->log_likelihoods[i].get_tiebreaker();
+            level[i] = (int32_t)this->level_assignments[i];
+        }
+        evaluator->sampler_upload(this->particles, logl, tb, level);
+        kimacuda::Context& ctx = evaluator->sampler_ctx();
+        const int max_pairs = (int)(T * this->options.thread_steps);
+        std::vector<double> above(2 * (size_t)max_pairs);
+        std::vector<double> lv_logl, lv_tb, lv_logX;
+        std::vector<uint64_t> lv_tries, counters;
+        double t_dev = 0, t_book = 0;
+        while (true) {
+            const size_t L = this->levels.size();
+            lv_logl.resize(L); lv_tb.resize(L); lv_logX.resize(L); lv_tries.resize(L); counters.resize(4 * L);
+            for (size_t j = 0; j < L; ++j) {
+                lv_logl[j] = this->levels[j].get_log_likelihood().get_value();
+                lv_tb[j] = this->levels[j].get_log_likelihood().get_tiebreaker();
+                lv_logX[j] = this->levels[j].get_log_X();
+                lv_tries[j] = this->levels[j].tries;
+            }
+            if (this->options.max_num_saves != 0 && this->count_saves != 0 &&
+                (this->count_saves % this->options.max_num_saves == 0))
+                break;
+            const double t0 = now();
+            ctx.sampler_set_levels((int)L, lv_logl.data(), lv_tb.data(), lv_logX.data(), lv_tries.data(),
+                                   this->enough_levels(this->levels), L == this->options.max_num_levels);
+            ctx.sampler_run((int)this->options.thread_steps);
+            const int n_above = ctx.sampler_collect(counters.data(), above.data(), max_pairs);
+            ctx.sampler_download(nullptr, nullptr, logl.data(), tb.data(), level.data());
+            const double t1 = now();
+            t_dev += t1 - t0;
+            const unsigned long long done = (unsigned long long)T * this->options.thread_steps;
+            this->count_mcmc_steps += done;
+            this->count_mcmc_steps_since_save += done;
+            for (size_t j = 0; j < L; ++j) {
+                // (the members directly: the increment_* methods take an int, Level.h:56-59)
+                this->levels[j].accepts += counters[4 * j + 0];
+                this->levels[j].tries += counters[4 * j + 1];
+                this->levels[j].visits += counters[4 * j + 2];
+                this->levels[j].exceeds += counters[4 * j + 3];
+            }
+            for (int i = 0; i < n_above && i < max_pairs; ++i)
+                this->all_above.push_back(LikelihoodType(above[2 * i], above[2 * i + 1]));
+            for (size_t i = 0; i < n; ++i) {
+                this->log_likelihoods[i] = LikelihoodType(logl[i], tb[i]);
+                this->level_assignments[i] = (unsigned int)level[i];
+            }
+            bookkeeping_device();
+            t_book += now() - t1;
+        }
+        if (std::getenv("KIMA_PROFILE"))
+            std::cerr << "# device proposals: steps + barrier transfers " << t_dev << " s, bookkeeping " << t_book << " s"
+                      << std::endl;
+        evaluator->sampler_get_all(this->particles);
+        std::fstream fout("sampler_state.txt", std::ios::out);
+        this->print(fout);
+        fout.close();
+        return true;
+    }
+
 public:
     BatchedSampler() {}
     BatchedSampler(unsigned int num_threads, double compression, const Options& options,
@@ -311,6 +516,7 @@ public:
     void initialise(unsigned int first_seed)
     {
         RNG& rng = this->rngs[0];
+        seed0 = first_seed;
         this->all_above.reserve(2 * this->options.new_level_interval);
         for (auto& a : this->above) a.reserve(2 * this->options.new_level_interval);
         std::cout << "# Seeding random number generators. First seed = ";
@@ -352,6 +558,10 @@ public:
         this->thin_print = thin;
         const double t_run0 = now();
         ensure_evaluator();
+        if (device_proposals_requested() && run_device()) {
+            if (std::getenv("KIMA_PROFILE")) std::cerr << "# run() " << now() - t_run0 << " s (device proposals)" << std::endl;
+            return;
+        }
         const unsigned int T = this->num_threads;
         if (T % (unsigned int)world() != 0)
             throw std::invalid_argument("the number of lanes (-t) must be a multiple of the number of ranks");

@@ -19,6 +19,7 @@
 #include <limits>
 #include <vector>
 #include "kima_cuda.hpp"
+#include "PriorTable.h"
 
 // the nine model flags every kima_setup.cpp defines (src/RVmodel.h:16-34)
 extern const bool GP, MA, hyperpriors, trend, multi_instrument, known_object, studentt;
@@ -247,6 +248,60 @@ public:
     void wait(int g) { ctx_[g]->wait(); }
 
     long long launches() const { return ctx_[0]->launch_count() + ctx_[1]->launch_count(); }
+
+    // ---- device-side proposals (include/kima_sampler.h) ------------
+    // The particles move to the GPU (context 0) and stay there: perturb, prior-ratio test,
+    // likelihood, accept, level assignment, level counters and `above` all run in HBM; the host
+    // keeps DNest4's bookkeeping between blocks of thread_steps steps.
+    //
+    // "" when every prior of `proto` (a particle on which setPriors() has run) has a device
+    // counterpart and the sampler was created; otherwise the name of the first one that has not
+    // (Empirical, mixGaussianLogUniform, Gaussian_from_Tc, Jeffreys: host proposals only).
+    std::string sampler_create(const RVmodel& proto, const kc_sampler_config& cfg)
+    {
+        kc_prior_table T;
+        const std::string bad = extract_prior_table(proto, T, &kc_prior_make);
+        if (!bad.empty()) return bad;
+        ctx_[0]->sampler_create(T, cfg);
+        return "";
+    }
+    struct ColRef {
+        double* base;
+        size_t ld;
+        double& operator()(int row) const { return base[(size_t)row * ld]; }
+    };
+    // every particle's state, likelihood and level assignment -> HBM
+    void sampler_upload(const std::vector<RVmodel>& particles, const std::vector<double>& logl,
+                        const std::vector<double>& tb, const std::vector<int32_t>& level)
+    {
+        const kc_sampler_layout& SL = ctx_[0]->sampler_layout();
+        const size_t n = particles.size();
+        std::vector<double> state((size_t)SL.n_state * n, 0.0);
+        std::vector<int32_t> np(n);
+        for (size_t i = 0; i < n; i++)
+            model_to_column(particles[i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
+        ctx_[0]->sampler_upload(state.data(), np.data(), logl.data(), tb.data(), level.data());
+    }
+    // particle `which` back into a host RVmodel (save_particle, the end-of-run state file)
+    void sampler_get_particle(int which, RVmodel& m)
+    {
+        const kc_sampler_layout& SL = ctx_[0]->sampler_layout();
+        std::vector<double> col(SL.n_state);
+        int32_t np = 0;
+        ctx_[0]->sampler_get_particle(which, col.data(), &np);
+        column_to_model(m, ctx_[0]->layout(), SL, ColRef{col.data(), 1}, np);
+    }
+    void sampler_get_all(std::vector<RVmodel>& particles)
+    {
+        const kc_sampler_layout& SL = ctx_[0]->sampler_layout();
+        const size_t n = particles.size();
+        std::vector<double> state((size_t)SL.n_state * n);
+        std::vector<int32_t> np(n);
+        ctx_[0]->sampler_download(state.data(), np.data(), nullptr, nullptr, nullptr);
+        for (size_t i = 0; i < n; i++)
+            column_to_model(particles[i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
+    }
+    kimacuda::Context& sampler_ctx() { return *ctx_[0]; }
 
 private:
     // NCCL's unique id travels through a file in the run directory (all ranks of one node

@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include "kima_cuda.h"
+#include "kima_sampler.h"
 
 namespace kimacuda {
 
@@ -86,12 +87,43 @@ public:
     void allreduce_levels(uint64_t* counters, int n) { check(kc_allreduce_levels(ctx_, counters, n)); }
     kc_ctx* raw() { return ctx_; }
 
+    // ---- device-side proposals (include/kima_sampler.h) -------------------------------------
+    void sampler_create(const kc_prior_table& priors, const kc_sampler_config& cfg)
+    {
+        check(kc_sampler_create(ctx_, &priors, &cfg));
+        check(kc_sampler_get_layout(ctx_, &sampler_layout_));
+    }
+    const kc_sampler_layout& sampler_layout() const { return sampler_layout_; }
+    void sampler_upload(const double* state, const int32_t* np, const double* logl, const double* tb, const int32_t* level)
+    {
+        check(kc_sampler_upload(ctx_, state, np, logl, tb, level));
+    }
+    void sampler_download(double* state, int32_t* np, double* logl, double* tb, int32_t* level)
+    {
+        check(kc_sampler_download(ctx_, state, np, logl, tb, level));
+    }
+    void sampler_get_particle(int which, double* col, int32_t* np) { check(kc_sampler_get_particle(ctx_, which, col, np)); }
+    void sampler_copy_particles(int n, const int32_t* dst, const int32_t* src) { check(kc_sampler_copy_particles(ctx_, n, dst, src)); }
+    void sampler_set_levels(int L, const double* logl, const double* tb, const double* log_X, const uint64_t* tries,
+                            bool enough, bool at_max)
+    {
+        check(kc_sampler_set_levels(ctx_, L, logl, tb, log_X, tries, enough, at_max));
+    }
+    void sampler_run(int steps) { check(kc_sampler_run(ctx_, steps)); }
+    int sampler_collect(uint64_t* counters, double* above_pairs, int max_pairs)
+    {
+        int n = 0;
+        check(kc_sampler_collect(ctx_, counters, above_pairs, max_pairs, &n));
+        return n;
+    }
+
 private:
     kc_ctx* ctx_ = nullptr;
     kc_layout layout_{};
     double* params_ = nullptr;
     int32_t* np_ = nullptr;
     int ld_ = 0, max_batch_ = 0;
+    kc_sampler_layout sampler_layout_{};
 };
 
 }  // namespace kimacuda

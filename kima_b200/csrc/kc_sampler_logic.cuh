@@ -350,7 +350,8 @@ KS_FN void update_level_assignment(const SamplerParams& sp, Rng& rng, int lane, 
     if (sp.at_max) {
         const uint64_t tc = sp.lv_tries[cur] + counter(sp, 1, cur, lane);
         const uint64_t tp = sp.lv_tries[proposal] + counter(sp, 1, proposal, lane);
-        log_A += sp.beta * log((double)(tc + 1) / (double)(tp + 1));
+        // Level::get_tries() returns unsigned int (Level.h:50-51): 32-bit arithmetic, as there
+        log_A += sp.beta * log((double)((uint32_t)tc + 1u) / (double)((uint32_t)tp + 1u));
     }
     if (log_A > 0.) log_A = 0.;
     const double r = rng.rand();

@@ -178,3 +178,41 @@ def test_prior_is_the_stationary_distribution(gpu, ref):
     want, _ = ref.oracle.eval_batch(S2[:L["n_rows"]], np2, nthreads=8)
     want = np.where(np.isfinite(want), want, -1e300)
     np.testing.assert_allclose(logl2, want, rtol=1e-9)
+
+
+def test_many_barriers_on_device_match_reference(gpu, ref):
+    """Blocks of steps with the barrier's hand-over in between (counters folded into the level
+    table, `above` lists emptied, stream positions carried over): 12 barriers x 40 steps of 256
+    lanes stay equal to the reference's mcmc_thread run barrier by barrier."""
+    flags, data, pri = _setup(ref, "fixed_np")
+    T, P, steps, L_levels = 256, 2, 40, 12
+    n = T * P
+    S, nps, L = make_state(flags, data, pri, n, seed=11)
+    logl, _ = ref.oracle.eval_batch(S[:L["n_rows"]], nps, nthreads=8)
+    logl = np.where(np.isfinite(logl), logl, -1e300)
+    rng = np.random.default_rng(2)
+    tb = rng.uniform(0.01, 0.99, n)
+    lv_logl, lv_tb, lv_logX, cnt = make_levels(logl, L_levels)
+    level = np.array([rng.integers(0, 1 + np.searchsorted(lv_logl[1:], v)) for v in logl], np.int32)
+    ctr = np.zeros(T, np.uint64)
+    with LikelihoodEngine(data, flags, T) as eng:
+        ds = DeviceSampler(eng, pri, SamplerOptions(lanes=T, num_particles=P, thread_steps=steps, max_levels=64))
+        ds.upload(S, nps, logl, tb, level)
+        ds.set_counters(ctr)
+        state = dict(state=S, np=nps, logl=logl, tb=tb, level=level, ctr=ctr)
+        cnt = cnt.copy()
+        for barrier in range(12):
+            want = ref.mcmc(T, P, steps, state["state"], state["np"], state["logl"], state["tb"], state["level"],
+                            lv_logl, lv_tb, lv_logX, cnt, 10.0, 100.0, L_levels, 43, state["ctr"])
+            ds.set_levels(lv_logl, lv_tb, lv_logX, cnt[:, 1], True, True)
+            ds.run(steps)
+            gcnt, gabove = ds.collect()
+            gS, gnp, glogl, gtb, glevel = ds.download()
+            np.testing.assert_array_equal(ds.get_counters(), want["ctr"], err_msg="barrier %d" % barrier)
+            np.testing.assert_array_equal(glevel, want["level"], err_msg="barrier %d" % barrier)
+            np.testing.assert_array_equal(gcnt, want["counters"], err_msg="barrier %d" % barrier)
+            # (the reference's incremental mu against from-scratch kernels: 1e-9 seen at logL ~ -1e3)
+            np.testing.assert_allclose(glogl, want["logl"], rtol=1e-7)
+            cnt = cnt + want["counters"]
+            state = want
+        ds.close()
