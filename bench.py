@@ -358,6 +358,13 @@ def main():
         out["sampler"] = {"unit": "MCMC steps/s", "lanes": 4096, "cpu_threads": threads,
                           "runs": [sampler_bench.compare(n, 4096, threads, gpu_saves=80, cpu_saves=100)
                                    for n in ("CoRoT7", "51Peg")]}
+        # the same examples with proposals, prior test, accept logic and level
+        # counters on the GPU as well (KIMA_DEVICE_PROPOSALS=1, include/kima_sampler.h): particles stay
+        # in HBM, the host only does DNest4's bookkeeping between blocks of thread_steps steps
+        dev_env = {"KIMA_DEVICE_PROPOSALS": "1"}
+        out["sampler"]["device_proposals"] = [
+            sampler_bench.run("gpu", "51Peg", 65536, 100, 20, env=dev_env),
+            sampler_bench.run("gpu", "CoRoT7", 16384, 100, 10, env=dev_env)]
     if rank == 0 and world == 1 and not a.skip_predictive and not a.skip_cpu_baseline:
         out["predictive"] = predictive_leg(data, fg, local, threads)
     if world > 1 and not a.skip_sampler and os.path.exists(os.path.join(ROOT, "host", "_build", "kima_gpu_CoRoT7")):

@@ -383,8 +383,12 @@ class BatchedSampler : public Sampler<ModelType> {
     {
         bool created_level = false;
         if (!this->enough_levels(this->levels) && (this->all_above.size() >= this->options.new_level_interval)) {
-            std::sort(this->all_above.begin(), this->all_above.end());
+            // the reference sorts all_above and keeps what lies above position `index`; only that
+            // element and the SET above it matter afterwards (the next creation orders again), so a
+            // selection does the same in O(n): with millions of lanes-times-steps entries per
+            // barrier the full sort was most of the bookkeeping
             const int index = static_cast<int>((1. - 1. / this->compression) * this->all_above.size());
+            std::nth_element(this->all_above.begin(), this->all_above.begin() + index, this->all_above.end());
             std::cout << "# Creating level " << this->levels.size() << " with log likelihood = ";
             std::cout << std::setprecision(12);
             std::cout << this->all_above[index].get_value() << "." << std::endl;
@@ -453,7 +457,7 @@ class BatchedSampler : public Sampler<ModelType> {
         std::vector<double> above(2 * (size_t)max_pairs);
         std::vector<double> lv_logl, lv_tb, lv_logX;
         std::vector<uint64_t> lv_tries, counters;
-        double t_dev = 0, t_book = 0;
+        double t_dev = 0, t_book = 0, t_xfer = 0, t_fold = 0;
         while (true) {
             const size_t L = this->levels.size();
             lv_logl.resize(L); lv_tb.resize(L); lv_logX.resize(L); lv_tries.resize(L); counters.resize(4 * L);
@@ -471,9 +475,11 @@ class BatchedSampler : public Sampler<ModelType> {
                                    this->enough_levels(this->levels), L == this->options.max_num_levels);
             ctx.sampler_run((int)this->options.thread_steps);
             const int n_above = ctx.sampler_collect(counters.data(), above.data(), max_pairs);
+            const double tc = now();
             ctx.sampler_download(nullptr, nullptr, logl.data(), tb.data(), level.data());
             const double t1 = now();
-            t_dev += t1 - t0;
+            t_dev += tc - t0;
+            t_xfer += t1 - tc;
             const unsigned long long done = (unsigned long long)T * this->options.thread_steps;
             this->count_mcmc_steps += done;
             this->count_mcmc_steps_since_save += done;
@@ -484,17 +490,28 @@ class BatchedSampler : public Sampler<ModelType> {
                 this->levels[j].visits += counters[4 * j + 2];
                 this->levels[j].exceeds += counters[4 * j + 3];
             }
-            for (int i = 0; i < n_above && i < max_pairs; ++i)
-                this->all_above.push_back(LikelihoodType(above[2 * i], above[2 * i + 1]));
-            for (size_t i = 0; i < n; ++i) {
-                this->log_likelihoods[i] = LikelihoodType(logl[i], tb[i]);
-                this->level_assignments[i] = (unsigned int)level[i];
+            {
+                const size_t base = this->all_above.size(), take = (size_t)std::min(n_above, max_pairs);
+                this->all_above.resize(base + take);
+                LikelihoodType* dst = this->all_above.data() + base;
+                pool->run(0, (int)take, [&](int a, int b) {
+                    for (int i = a; i < b; ++i) dst[i] = LikelihoodType(above[2 * (size_t)i], above[2 * (size_t)i + 1]);
+                });
             }
+            pool->run(0, (int)n, [&](int a, int b) {
+                for (int i = a; i < b; ++i) {
+                    this->log_likelihoods[i] = LikelihoodType(logl[i], tb[i]);
+                    this->level_assignments[i] = (unsigned int)level[i];
+                }
+            });
+            const double t2 = now();
+            t_fold += t2 - t1;
             bookkeeping_device();
-            t_book += now() - t1;
+            t_book += now() - t2;
         }
         if (std::getenv("KIMA_PROFILE"))
-            std::cerr << "# device proposals: steps + barrier transfers " << t_dev << " s, bookkeeping " << t_book << " s"
+            std::cerr << "# device proposals: steps + collect " << t_dev << " s, particle arrays back " << t_xfer
+                      << " s, folding counters / above / likelihoods in " << t_fold << " s, bookkeeping " << t_book << " s"
                       << std::endl;
         evaluator->sampler_get_all(this->particles);
         std::fstream fout("sampler_state.txt", std::ios::out);

@@ -150,6 +150,10 @@ int kc_sampler_run(kc_ctx* ctx, int steps);
 int kc_sampler_collect(kc_ctx* ctx, uint64_t* counters, double* above_pairs, int max_pairs,
                        int* n_above);
 
+/* Device time (CUDA events on the context stream) of the last kc_sampler_run, all kernels of
+ * its steps included; waits for the run to finish. */
+int kc_sampler_last_run_ms(kc_ctx* ctx, float* ms);
+
 /* Stream positions of the lanes (the number of uniforms each has drawn); set for tests. */
 int kc_sampler_get_counters(kc_ctx* ctx, uint64_t* ctr);
 int kc_sampler_set_counters(kc_ctx* ctx, const uint64_t* ctr);

@@ -49,6 +49,8 @@ struct SamplerState {
     uint64_t* h_cnt_sum = nullptr;   // pinned
     int32_t* h_total = nullptr;      // pinned
     double* h_above = nullptr;       // pinned, [T * max_steps * 2]
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the last kc_sampler_run
+    bool timed = false;
     std::vector<void*> allocs;
 };
 
@@ -203,6 +205,8 @@ void sampler_free(kc_ctx* c)
     if (s->h_cnt_sum) cudaFreeHost(s->h_cnt_sum);
     if (s->h_total) cudaFreeHost(s->h_total);
     if (s->h_above) cudaFreeHost(s->h_above);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
     delete s;
     c->sampler = nullptr;
 }
@@ -317,6 +321,8 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     CU(cudaMallocHost(&s->h_cnt_sum, sizeof(uint64_t) * 4 * sp.Lcap));
     CU(cudaMallocHost(&s->h_total, sizeof(int32_t)));
     CU(cudaMallocHost(&s->h_above, sizeof(double) * (size_t)T * sp.max_steps * 2));
+    CU(cudaEventCreate(&s->ev0));
+    CU(cudaEventCreate(&s->ev1));
     // the perturb call tree keeps its component vectors on the local stack
     size_t stack = 0;
     CU(cudaDeviceGetLimit(&stack, cudaLimitStackSize));
@@ -447,6 +453,7 @@ int kc_sampler_run(kc_ctx* c, int steps)
     if (steps == 0) return KC_OK;
     CU(cudaSetDevice(c->device));
     const int grid = kc::lane_grid(sp);
+    CU(cudaEventRecord(s->ev0, c->stream));
     kc::smp_propose_kernel<<<grid, kc::LANE_THREADS, 0, c->stream>>>(sp);
     c->launches += 1;
     for (int i = 0; i < steps; i++) {
@@ -456,7 +463,21 @@ int kc_sampler_run(kc_ctx* c, int steps)
         else kc::smp_accept_kernel<<<grid, kc::LANE_THREADS, 0, c->stream>>>(sp);
         c->launches += 1;
     }
+    CU(cudaEventRecord(s->ev1, c->stream));
+    s->timed = true;
     CU(cudaGetLastError());
+    return KC_OK;
+}
+
+int kc_sampler_last_run_ms(kc_ctx* c, float* ms)
+{
+    int rc = kc::need_sampler(c);
+    if (rc) return rc;
+    if (!ms) return fail(KC_ERR_ARG, "ms is null");
+    if (!c->sampler->timed) return fail(KC_ERR_ARG, "no kc_sampler_run has been timed yet");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventSynchronize(c->sampler->ev1));
+    CU(cudaEventElapsedTime(ms, c->sampler->ev0, c->sampler->ev1));
     return KC_OK;
 }
 

@@ -136,3 +136,132 @@ class DeviceSampler:
         end = ctypes.c_uint64()
         _lib.check(self.lib.kc_rng_draws(self.ctx, key, ctr0, what, n, _d(out), ctypes.byref(end)))
         return out, end.value
+
+    def last_run_ms(self) -> float:
+        ms = ctypes.c_float()
+        _lib.check(self.lib.kc_sampler_last_run_ms(self.ctx, ctypes.byref(ms)))
+        return ms.value
+
+
+def make_prior(name: str, *pars) -> CPrior:
+    """``make_prior<T>(args...)`` (src/RVmodel.h:165-166) as data: kc_prior_make."""
+    q = CPrior()
+    p = np.asarray(pars, np.float64)
+    _lib.check(_lib.load_library().kc_prior_make(PRIOR_TYPES[name], _d(p), p.size, ctypes.byref(q)))
+    return q
+
+
+def default_prior_table(flags, data, fix: bool = False) -> CPriorTable:
+    """The priors an RVmodel has when the user's constructor sets none: RVmodel::setPriors
+    (src/RVmodel.cpp:23-85) and the RVConditionalPrior constructor
+    (src/RVConditionalPrior.cpp:10-54).  Known-object priors have no defaults there (setPriors
+    throws): the caller fills KO_*prior in."""
+    T = CPriorTable()
+    for name, _ in CPriorTable._fields_:
+        f = getattr(T, name)
+        if isinstance(f, CPrior):
+            f.type = KC_PRIOR_NONE
+        elif hasattr(f, "__len__"):
+            for q in f:
+                q.type = KC_PRIOR_NONE
+    T.betaprior = make_prior("Gaussian", 0.0, 1.0)
+    T.sigmaMA_prior = make_prior("Uniform", -1.0, 1.0)
+    T.tauMA_prior = make_prior("LogUniform", 1.0, 100.0)
+    T.Cprior = make_prior("Uniform", data.get_RV_min(), data.get_RV_max())
+    span = data.get_max_RV_span()
+    T.Jprior = make_prior("ModifiedLogUniform", min(1.0, 0.1 * span), span)
+    if flags.trend:
+        if flags.degree >= 1:
+            T.slope_prior = make_prior("Gaussian", 0.0, 10.0 ** data.get_trend_magnitude(1))
+        if flags.degree >= 2:
+            T.quadr_prior = make_prior("Gaussian", 0.0, 10.0 ** data.get_trend_magnitude(2))
+        if flags.degree == 3:
+            T.cubic_prior = make_prior("Gaussian", 0.0, 10.0 ** data.get_trend_magnitude(3))
+    T.offsets_prior = make_prior("Uniform", -data.get_RV_span(), data.get_RV_span())
+    if flags.GP:
+        T.log_eta1_prior = make_prior("Uniform", -5.0, 5.0)
+        T.eta2_prior = make_prior("LogUniform", 1.0, 100.0)
+        T.eta3_prior = make_prior("Uniform", 10.0, 40.0)
+        if flags.kernel == 0:
+            T.log_eta4_prior = make_prior("Uniform", -1.0, 1.0)
+    if flags.studentt:
+        T.nu_prior = make_prior("LogUniform", 2.0, 1000.0)
+    if flags.hyperpriors:
+        T.log_muP_prior = make_prior("TruncatedCauchy", np.log(365), 1.0, np.log(365) - 21, np.log(365) + 21)
+        T.wP_prior = make_prior("Uniform", 0.1, 3.0)
+        T.log_muK_prior = make_prior("TruncatedCauchy", 0.0, 1.0, 0.0 - 21, 0.0 + 21)
+        T.Pprior.type = PRIOR_TYPES["Laplace"]
+        T.Kprior.type = PRIOR_TYPES["Exponential"]
+    else:
+        T.Pprior = make_prior("LogUniform", 1.0, 1e5)
+        T.Kprior = make_prior("ModifiedLogUniform", 1.0, 1e3)
+    T.eprior = make_prior("Uniform", 0.0, 1.0)
+    T.phiprior = make_prior("Uniform", 0.0, 2 * np.pi)
+    T.wprior = make_prior("Uniform", 0.0, 2 * np.pi)
+    T.fix = int(fix)
+    return T
+
+
+def draw_from_prior(sampler: DeviceSampler, flags, priors: CPriorTable, n: int, seed: int = 43):
+    """n particle states drawn from the prior, as RVmodel::from_prior leaves them
+    (src/RVmodel.cpp:88-160, RJObject::from_prior RJObjectImpl.h:19-42): every value is
+    ``prior.cdf_inverse(u)`` of a uniform u (ContinuousDistribution::generate), evaluated by the
+    library; the uniforms here are numpy's (the reference draws them from thread 0's RNG).
+    Returns (state [n_state][n], np [n])."""
+    L = sampler.engine.layout
+    rng = np.random.default_rng(seed)
+    S = np.zeros((sampler.n_state, n))
+    npm = flags.npmax
+
+    def gen(prior, rows=1):
+        u = rng.uniform(0.0, 1.0, (rows, n))
+        return u, sampler.prior_eval(prior, 1, u.ravel()).reshape(rows, n)
+
+    rh = sampler.row_hyper
+    if flags.hyperpriors:
+        S[rh + 0] = gen(priors.log_muP_prior)[1][0]
+        S[rh + 1] = gen(priors.wP_prior)[1][0]
+        S[rh + 2] = np.exp(gen(priors.log_muK_prior)[1][0])
+    nps = np.full(n, npm, np.int32) if priors.fix else rng.integers(0, npm + 1, n).astype(np.int32)
+    cond = (priors.Pprior, priors.Kprior, priors.phiprior, priors.eprior, priors.wprior)
+    for j in range(npm):
+        alive = nps > j
+        for d in range(5):
+            u = rng.uniform(0.0, 1.0, n)
+            if flags.hyperpriors and d == 0:      # Laplace(center, width)
+                c, w = S[rh + 0], S[rh + 1]
+                v = c - w * np.sign(u - 0.5) * np.log(1.0 - 2.0 * np.abs(u - 0.5))
+            elif flags.hyperpriors and d == 1:    # Exponential(muK)
+                v = -S[rh + 2] * np.log(1.0 - u)
+            else:
+                v = sampler.prior_eval(cond[d], 1, u)
+            S[sampler.row_u + d * npm + j] = np.where(alive, u, 0.0)
+            S[L["row_P"] + d * npm + j] = np.where(alive, v, 0.0)
+    S[L["row_vsys"]] = gen(priors.Cprior)[1][0]
+    S[L["row_jit"]:L["row_jit"] + L["n_jit"]] = gen(priors.Jprior, L["n_jit"])[1]
+    if L["n_off"]:
+        S[L["row_off"]:L["row_off"] + L["n_off"]] = gen(priors.offsets_prior, L["n_off"])[1]
+    if flags.trend:
+        for k, pr in enumerate((priors.slope_prior, priors.quadr_prior, priors.cubic_prior)):
+            if flags.degree >= k + 1:
+                S[L["row_trend"] + k] = gen(pr)[1][0]
+    if L["n_beta"]:
+        S[L["row_beta"]:L["row_beta"] + L["n_beta"]] = gen(priors.betaprior, L["n_beta"])[1]
+    if flags.GP:
+        S[L["row_eta"] + 0] = np.exp(gen(priors.log_eta1_prior)[1][0])
+        S[L["row_eta"] + 1] = gen(priors.eta2_prior)[1][0]
+        S[L["row_eta"] + 2] = gen(priors.eta3_prior)[1][0]
+        if flags.kernel == 0:
+            S[L["row_eta"] + 3] = np.exp(gen(priors.log_eta4_prior)[1][0])
+    if flags.MA:
+        S[L["row_MA"] + 0] = gen(priors.sigmaMA_prior)[1][0]
+        S[L["row_MA"] + 1] = gen(priors.tauMA_prior)[1][0]
+    if flags.studentt:
+        S[L["row_nu"]] = gen(priors.nu_prior)[1][0]
+    for i in range(L["n_ko"]):
+        S[L["row_KO_P"] + i] = gen(priors.KO_Pprior[i])[1][0]
+        S[L["row_KO_K"] + i] = gen(priors.KO_Kprior[i])[1][0]
+        S[L["row_KO_e"] + i] = gen(priors.KO_eprior[i])[1][0]
+        S[L["row_KO_phi"] + i] = gen(priors.KO_phiprior[i])[1][0]
+        S[L["row_KO_w"] + i] = gen(priors.KO_wprior[i])[1][0]
+    return np.ascontiguousarray(S), nps

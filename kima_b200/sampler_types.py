@@ -74,6 +74,7 @@ SAMPLER_SIGNATURES = {
                                              ctypes.c_int, ctypes.c_int]),
     "kc_sampler_run": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "kc_sampler_collect": (ctypes.c_int, [ctypes.c_void_p, _up, _dp, ctypes.c_int, _ip]),
+    "kc_sampler_last_run_ms": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_float)]),
     "kc_sampler_get_counters": (ctypes.c_int, [ctypes.c_void_p, _up]),
     "kc_sampler_set_counters": (ctypes.c_int, [ctypes.c_void_p, _up]),
     "kc_prior_eval": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(CPrior), ctypes.c_int, ctypes.c_int, _dp, _dp]),

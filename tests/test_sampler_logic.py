@@ -169,3 +169,35 @@ def test_mcmc_steps_match_reference(ref, name, P, L_levels, at_max):
             gS[tw.row_u + d * flags.npmax + j, dead] = 0.0
     np.testing.assert_allclose(gS, want["state"], rtol=1e-12, atol=1e-300)
     assert gcnt[:, 1].sum() == T * steps  # one try per lane and step
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_default_prior_table_equals_setPriors(ref, name):
+    """kima_b200.sampler.default_prior_table (the host mirror's restatement of setPriors and of the
+    RVConditionalPrior constructor) against the table extracted from the reference's own objects."""
+    from kima_b200.sampler import default_prior_table
+    flags, data, fix = case(name)
+    ref.oracle.set_flags(flags, fix)
+    ref.oracle.set_rvdata(data)
+    ref.lib.rs_set_priors(None)
+    want = ref.default_priors()
+    got = default_prior_table(flags, data, fix)
+
+    def same(a, b, what):
+        assert a.type == b.type, what
+        if a.type >= 0:
+            assert list(a.p) == list(b.p) and list(a.k) == list(b.k), what
+
+    for f, _ in CPriorTable._fields_:
+        a, b = getattr(got, f), getattr(want, f)
+        if isinstance(a, CPrior):
+            # slots the flags never read may be filled on one side only (setPriors fills offsets_prior
+            # and Jprior always, nu_prior only under studentt, ...): compare what perturb() can reach
+            used = {"slope_prior": flags.trend, "quadr_prior": flags.trend and flags.degree >= 2,
+                    "cubic_prior": flags.trend and flags.degree == 3, "log_eta1_prior": flags.GP, "eta2_prior": flags.GP,
+                    "eta3_prior": flags.GP, "log_eta4_prior": flags.GP and flags.kernel == 0, "nu_prior": flags.studentt,
+                    "log_muP_prior": flags.hyperpriors, "wP_prior": flags.hyperpriors, "log_muK_prior": flags.hyperpriors,
+                    "Pprior": not flags.hyperpriors, "Kprior": not flags.hyperpriors}.get(f, True)
+            if used:
+                same(a, b, f)
+    assert got.fix == want.fix

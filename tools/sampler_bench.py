@@ -60,7 +60,7 @@ def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=120
             return {"error": (r.stdout[-500:] + r.stderr[-500:])}
         with open(os.path.join(d, "sampler_state.txt")) as fh:
             steps = int(fh.read().split()[-1])
-        prof = [l for l in r.stderr.splitlines() if l.startswith("# host threads")]
+        prof = [l for l in r.stderr.splitlines() if l.startswith("# host threads") or l.startswith("# device proposals")]
         extra = {}
         run_s = _run_seconds(r.stderr)
         if run_s:
