@@ -375,20 +375,23 @@ def main():
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import sampler_bench
         runs = []
-        for i, name in enumerate(("CoRoT7",)):
-            box = [sampler_bench.prepare_dir(name, 4096 * world, 100, 80) if rank == 0 else None]
+        # (example, lanes per GPU, saves, device proposals?): host proposals as in the 1-GPU leg, and the
+        # 51Peg example with the whole step on the GPUs (each rank keeps its lanes' particles in HBM)
+        for i, (name, lpg, saves, dev) in enumerate((("CoRoT7", 4096, 80, False), ("51Peg", 16384, 20, True))):
+            box = [sampler_bench.prepare_dir(name, lpg * world, 100, saves) if rank == 0 else None]
             dist.broadcast_object_list(box, src=0)
             dist.barrier()
-            r = sampler_bench.run_rank(name, box[0], 4096 * world, rank, world, local,
+            r = sampler_bench.run_rank(name, box[0], lpg * world, rank, world, local,
                                        int(os.environ.get("MASTER_PORT", "29500")) + 11 + i,
-                                       max(1, threads // world))
+                                       max(1, threads // world),
+                                       env={"KIMA_DEVICE_PROPOSALS": "1"} if dev else None)
             wall = exch.max_float(float(r.get("wall_s", 0.0)))
             bad = exch.max_float(1.0 if "error" in r else 0.0)
             if rank == 0:
                 if bad or not r.get("mcmc_steps"):
                     runs.append({"example": name, "error": r.get("error", "a rank failed")})
                 else:
-                    runs.append({"example": name, "lanes": 4096 * world, "mcmc_steps": r["mcmc_steps"],
+                    runs.append({"example": name, "lanes": lpg * world, "device_proposals": dev, "mcmc_steps": r["mcmc_steps"],
                                  "wall_s": wall, "steps_per_s": r["mcmc_steps"] / wall,
                                  "run_s": r.get("run_s"),
                                  "steps_per_s_run": r["mcmc_steps"] / r["run_s"] if r.get("run_s") else None})

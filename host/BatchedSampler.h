@@ -315,8 +315,35 @@ class BatchedSampler : public Sampler<ModelType> {
         return e && std::atoi(e) != 0;
     }
 
+    // One process per GPU: rank r owns the lanes [lane_lo, lane_hi) and keeps their particles in
+    // its GPU's HBM; likelihoods, level assignments, levels and rngs[0] are replicated (every rank
+    // runs the same bookkeeping on the same data), particle columns travel only when asked for.
+    size_t part_lo() const { return (size_t)lane_lo() * this->options.num_particles; }
+    size_t part_hi() const { return (size_t)lane_hi() * this->options.num_particles; }
+    int owner_of(size_t i) const { return (int)(i / (this->particles.size() / (size_t)world())); }
+
+    // column of global particle `which` on every rank (its owner fetches it from HBM)
+    void fetch_particle(size_t which, std::vector<double>& col, int32_t& np)
+    {
+        const int S = evaluator->sampler_state_rows();
+        std::vector<double> mine((size_t)S + 1, 0.0);
+        const int own = owner_of(which);
+        if (own == rank()) {
+            int32_t k = 0;
+            evaluator->sampler_ctx().sampler_get_particle((int)(which - part_lo()), mine.data(), &k);
+            mine[S] = (double)k;
+        }
+        if (world() > 1) {
+            std::vector<double> all(((size_t)S + 1) * world());
+            evaluator->allgather_bytes(mine.data(), sizeof(double) * (S + 1), all.data());
+            mine.assign(all.begin() + (size_t)own * (S + 1), all.begin() + (size_t)(own + 1) * (S + 1));
+        }
+        np = (int32_t)mine[S];
+        col.assign(mine.begin(), mine.begin() + S);
+    }
+
     // kill_lagging_particles (SamplerImpl.h:534-587) with the copies done in HBM: same draws from
-    // rngs[0], same messages
+    // rngs[0], same messages; a replacement taken from another rank's lane travels as one column
     void kill_lagging_device()
     {
         const size_t n = this->particles.size();
@@ -334,7 +361,7 @@ class BatchedSampler : public Sampler<ModelType> {
             }
         }
         if (num_bad >= n) return;
-        std::vector<int32_t> dst, src;
+        std::vector<size_t> dst, src;
         for (size_t i = 0; i < n; ++i) {
             if (good[i]) continue;
             int i_copy;
@@ -342,16 +369,51 @@ class BatchedSampler : public Sampler<ModelType> {
                 i_copy = this->rngs[0].rand_int((int)n);
             } while (!good[i_copy] ||
                      this->rngs[0].rand() >= exp(this->log_push(this->level_assignments[i_copy]) - max_log_push));
-            dst.push_back((int32_t)i);
-            src.push_back((int32_t)i_copy);
+            dst.push_back(i);
+            src.push_back((size_t)i_copy);
             this->log_likelihoods[i] = this->log_likelihoods[i_copy];
             this->level_assignments[i] = this->level_assignments[i_copy];
             ++deletions_dev;
-            std::cout << "# Replacing lagging particle.";
-            std::cout << " This has happened " << deletions_dev;
-            std::cout << " times." << std::endl;
+            if (rank() == 0) {
+                std::cout << "# Replacing lagging particle.";
+                std::cout << " This has happened " << deletions_dev;
+                std::cout << " times." << std::endl;
+            }
         }
-        evaluator->sampler_ctx().sampler_copy_particles((int)dst.size(), dst.data(), src.data());
+        // sources are good particles and never overwritten: the copies are independent
+        std::vector<int32_t> ldst, lsrc;
+        std::vector<size_t> cross;
+        for (size_t k = 0; k < dst.size(); ++k) {
+            const int od = owner_of(dst[k]), os = owner_of(src[k]);
+            if (od == os) {
+                if (od == rank()) {
+                    ldst.push_back((int32_t)(dst[k] - part_lo()));
+                    lsrc.push_back((int32_t)(src[k] - part_lo()));
+                }
+            } else {
+                cross.push_back(k);
+            }
+        }
+        kimacuda::Context& ctx = evaluator->sampler_ctx();
+        ctx.sampler_copy_particles((int)ldst.size(), ldst.data(), lsrc.data());
+        if (cross.empty()) return;
+        const int S = evaluator->sampler_state_rows();
+        const size_t slot = (size_t)S + 1, K = cross.size();
+        std::vector<double> mine(slot * K, 0.0), all(slot * K * world());
+        for (size_t q = 0; q < K; ++q)
+            if (owner_of(src[cross[q]]) == rank()) {
+                int32_t np = 0;
+                ctx.sampler_get_particle((int)(src[cross[q]] - part_lo()), mine.data() + q * slot, &np);
+                mine[q * slot + S] = (double)np;
+            }
+        evaluator->allgather_bytes(mine.data(), sizeof(double) * slot * K, all.data());
+        for (size_t q = 0; q < K; ++q) {
+            const size_t d = dst[cross[q]];
+            if (owner_of(d) != rank()) continue;
+            const double* col = all.data() + ((size_t)owner_of(src[cross[q]]) * K + q) * slot;
+            ctx.sampler_set_particle((int)(d - part_lo()), col, (int32_t)col[S], this->log_likelihoods[d].get_value(),
+                                     this->log_likelihoods[d].get_tiebreaker(), (int32_t)this->level_assignments[d]);
+        }
     }
 
     // save_particle (SamplerImpl.h:503-531): the one particle that is printed comes back from HBM
@@ -359,12 +421,17 @@ class BatchedSampler : public Sampler<ModelType> {
     {
         ++this->count_saves;
         this->count_mcmc_steps_since_save = 0;
-        if (!this->save_to_disk) return;
-        if (this->count_saves % this->thin_print == 0)
+        if (rank() == 0 && this->save_to_disk && this->count_saves % this->thin_print == 0)
             std::cout << "# Saving particle to disk. N = " << this->count_saves << "." << std::endl;
-        std::fstream fout;
+        if (world() == 1 && !this->save_to_disk) return;  // the reference returns before drawing `which`
+        // every rank draws `which` (rngs[0] is replicated) and takes part in the fetch
         const int which = this->rngs[0].rand_int((int)this->particles.size());
-        evaluator->sampler_get_particle(which, this->particles[which]);
+        std::vector<double> col;
+        int32_t np = 0;
+        fetch_particle((size_t)which, col, np);
+        if (!this->save_to_disk) return;
+        evaluator->column_into(this->particles[which], col.data(), np);
+        std::fstream fout;
         fout.open(this->options.sample_file, std::ios::out | std::ios::app);
         this->particles[which].print(fout);
         fout << std::endl;
@@ -417,7 +484,10 @@ class BatchedSampler : public Sampler<ModelType> {
         for (size_t i = 1; i < this->log_likelihoods.size(); ++i)
             if (this->log_likelihoods[best] < this->log_likelihoods[i]) best = i;
         if (this->best_ever_log_likelihood < this->log_likelihoods[best]) {
-            evaluator->sampler_get_particle((int)best, this->particles[best]);
+            std::vector<double> col;
+            int32_t np = 0;
+            fetch_particle(best, col, np);
+            evaluator->column_into(this->particles[best], col.data(), np);
             this->best_ever_particle = this->particles[best];
             this->best_ever_log_likelihood = this->log_likelihoods[best];
         }
@@ -426,18 +496,21 @@ class BatchedSampler : public Sampler<ModelType> {
     // false = the model has a prior without a device counterpart: the caller runs host proposals
     bool run_device()
     {
-        if (world() > 1) throw std::invalid_argument("KIMA_DEVICE_PROPOSALS runs in one process per run for now");
         const unsigned int T = this->num_threads, P = this->options.num_particles;
-        const size_t n = this->particles.size();
+        const int W = world();
+        if (T % (unsigned int)W != 0)
+            throw std::invalid_argument("the number of lanes (-t) must be a multiple of the number of ranks");
+        const size_t n = this->particles.size(), p0 = part_lo(), p1 = part_hi(), nl = p1 - p0;
+        const unsigned int Tl = lane_hi() - lane_lo();
         kc_sampler_config cfg{};
-        cfg.lanes = (int32_t)T;
+        cfg.lanes = (int32_t)Tl;
         cfg.num_particles = (int32_t)P;
         cfg.max_steps = (int32_t)this->options.thread_steps;
         cfg.max_levels = this->options.max_num_levels ? (int32_t)this->options.max_num_levels : 1024;
         cfg.lambda = this->options.lambda;
         cfg.beta = this->options.beta;
         cfg.seed = seed0;
-        cfg.lane0 = 0;
+        cfg.lane0 = (int32_t)lane_lo();  // lane k of the run draws from stream seed + k whatever rank steps it
         const std::string bad = evaluator->sampler_create(this->particles[0], cfg);
         if (!bad.empty()) {
             std::cerr << "# KIMA_DEVICE_PROPOSALS: " << bad << " has no device counterpart; proposals stay on the host"
@@ -451,12 +524,13 @@ class BatchedSampler : public Sampler<ModelType> {
             tb[i] = this->log_likelihoods[i].get_tiebreaker();
             level[i] = (int32_t)this->level_assignments[i];
         }
-        evaluator->sampler_upload(this->particles, logl, tb, level);
+        evaluator->sampler_upload(this->particles, p0, p1, logl, tb, level);
         kimacuda::Context& ctx = evaluator->sampler_ctx();
-        const int max_pairs = (int)(T * this->options.thread_steps);
-        std::vector<double> above(2 * (size_t)max_pairs);
-        std::vector<double> lv_logl, lv_tb, lv_logX;
+        const int max_local = (int)(Tl * this->options.thread_steps), max_pairs = max_local * W;
+        std::vector<double> above(2 * (size_t)max_pairs), above_local(W > 1 ? 2 * (size_t)max_local : 0);
+        std::vector<double> lv_logl, lv_tb, lv_logX, xs(W > 1 ? 3 * nl : 0), xr(W > 1 ? 3 * n : 0);
         std::vector<uint64_t> lv_tries, counters;
+        std::vector<int> counts(W);
         double t_dev = 0, t_book = 0, t_xfer = 0, t_fold = 0;
         while (true) {
             const size_t L = this->levels.size();
@@ -474,9 +548,29 @@ class BatchedSampler : public Sampler<ModelType> {
             ctx.sampler_set_levels((int)L, lv_logl.data(), lv_tb.data(), lv_logX.data(), lv_tries.data(),
                                    this->enough_levels(this->levels), L == this->options.max_num_levels);
             ctx.sampler_run((int)this->options.thread_steps);
-            const int n_above = ctx.sampler_collect(counters.data(), above.data(), max_pairs);
+            int n_above = ctx.sampler_collect(counters.data(), W > 1 ? above_local.data() : above.data(), max_local);
             const double tc = now();
-            ctx.sampler_download(nullptr, nullptr, logl.data(), tb.data(), level.data());
+            ctx.sampler_download(nullptr, nullptr, logl.data() + p0, tb.data() + p0, level.data() + p0);
+            if (W > 1) {
+                // the barrier between processes (SamplerImpl.h:306-329): counters summed, `above` lists
+                // concatenated in rank (= lane) order, likelihoods and level assignments to everybody
+                evaluator->allreduce_levels(counters.data(), (int)counters.size());
+                evaluator->allgather_above(above_local.data(), std::min(n_above, max_local), above.data(), max_pairs,
+                                           counts.data());
+                n_above = 0;
+                for (int c : counts) n_above += c;
+                for (size_t i = 0; i < nl; ++i) {
+                    xs[3 * i] = logl[p0 + i];
+                    xs[3 * i + 1] = tb[p0 + i];
+                    xs[3 * i + 2] = (double)level[p0 + i];
+                }
+                evaluator->allgather_bytes(xs.data(), sizeof(double) * 3 * nl, xr.data());
+                for (size_t i = 0; i < n; ++i) {
+                    logl[i] = xr[3 * i];
+                    tb[i] = xr[3 * i + 1];
+                    level[i] = (int32_t)xr[3 * i + 2];
+                }
+            }
             const double t1 = now();
             t_dev += tc - t0;
             t_xfer += t1 - tc;
@@ -510,13 +604,35 @@ class BatchedSampler : public Sampler<ModelType> {
             t_book += now() - t2;
         }
         if (std::getenv("KIMA_PROFILE"))
-            std::cerr << "# device proposals: steps + collect " << t_dev << " s, particle arrays back " << t_xfer
+            std::cerr << "# device proposals: steps + collect " << t_dev << " s, particle arrays back / exchange " << t_xfer
                       << " s, folding counters / above / likelihoods in " << t_fold << " s, bookkeeping " << t_book << " s"
                       << std::endl;
-        evaluator->sampler_get_all(this->particles);
-        std::fstream fout("sampler_state.txt", std::ios::out);
-        this->print(fout);
-        fout.close();
+        // the end-of-run state file holds every particle: the ranks' columns go to everybody
+        {
+            std::vector<double> st;
+            std::vector<int32_t> np;
+            evaluator->sampler_local_state(st, np);
+            if (W == 1) {
+                evaluator->columns_into(this->particles, 0, st, np);
+            } else {
+                const size_t S = (size_t)evaluator->sampler_state_rows(), blob = (S + 1) * nl;
+                std::vector<double> send(blob), recv(blob * W);
+                std::copy(st.begin(), st.end(), send.begin());
+                for (size_t i = 0; i < nl; ++i) send[S * nl + i] = (double)np[i];
+                evaluator->allgather_bytes(send.data(), sizeof(double) * blob, recv.data());
+                for (int r = 0; r < W; ++r) {
+                    const double* b = recv.data() + blob * r;
+                    st.assign(b, b + S * nl);
+                    for (size_t i = 0; i < nl; ++i) np[i] = (int32_t)b[S * nl + i];
+                    evaluator->columns_into(this->particles, (size_t)r * nl, st, np);
+                }
+            }
+        }
+        if (rank() == 0) {
+            std::fstream fout("sampler_state.txt", std::ios::out);
+            this->print(fout);
+            fout.close();
+        }
         return true;
     }
 

@@ -270,36 +270,48 @@ public:
         size_t ld;
         double& operator()(int row) const { return base[(size_t)row * ld]; }
     };
-    // every particle's state, likelihood and level assignment -> HBM
-    void sampler_upload(const std::vector<RVmodel>& particles, const std::vector<double>& logl,
+    // the particles [i0, i1) (this rank's lanes) with likelihoods and level assignments -> HBM;
+    // the arrays are indexed like `particles`
+    void sampler_upload(const std::vector<RVmodel>& particles, size_t i0, size_t i1, const std::vector<double>& logl,
                         const std::vector<double>& tb, const std::vector<int32_t>& level)
     {
         const kc_sampler_layout& SL = ctx_[0]->sampler_layout();
-        const size_t n = particles.size();
+        const size_t n = i1 - i0;
         std::vector<double> state((size_t)SL.n_state * n, 0.0);
         std::vector<int32_t> np(n);
         for (size_t i = 0; i < n; i++)
-            model_to_column(particles[i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
-        ctx_[0]->sampler_upload(state.data(), np.data(), logl.data(), tb.data(), level.data());
+            model_to_column(particles[i0 + i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
+        ctx_[0]->sampler_upload(state.data(), np.data(), logl.data() + i0, tb.data() + i0, level.data() + i0);
     }
-    // particle `which` back into a host RVmodel (save_particle, the end-of-run state file)
+    int sampler_state_rows() const { return ctx_[0]->sampler_layout().n_state; }
+    // one column (n_state doubles) <-> a host RVmodel
+    void column_into(RVmodel& m, const double* col, int32_t np) const
+    {
+        column_to_model(m, ctx_[0]->layout(), ctx_[0]->sampler_layout(), ColRef{const_cast<double*>(col), 1}, np);
+    }
+    // local particle `which` back into a host RVmodel (save_particle, the record holder)
     void sampler_get_particle(int which, RVmodel& m)
     {
-        const kc_sampler_layout& SL = ctx_[0]->sampler_layout();
-        std::vector<double> col(SL.n_state);
+        std::vector<double> col(sampler_state_rows());
         int32_t np = 0;
         ctx_[0]->sampler_get_particle(which, col.data(), &np);
-        column_to_model(m, ctx_[0]->layout(), SL, ColRef{col.data(), 1}, np);
+        column_into(m, col.data(), np);
     }
-    void sampler_get_all(std::vector<RVmodel>& particles)
+    // all local particles: state [n_state][n_local] and np
+    void sampler_local_state(std::vector<double>& state, std::vector<int32_t>& np)
     {
         const kc_sampler_layout& SL = ctx_[0]->sampler_layout();
-        const size_t n = particles.size();
-        std::vector<double> state((size_t)SL.n_state * n);
-        std::vector<int32_t> np(n);
+        state.resize((size_t)SL.n_state * SL.n_particles);
+        np.resize(SL.n_particles);
         ctx_[0]->sampler_download(state.data(), np.data(), nullptr, nullptr, nullptr);
+    }
+    void columns_into(std::vector<RVmodel>& particles, size_t i0, const std::vector<double>& state,
+                      const std::vector<int32_t>& np)
+    {
+        const size_t n = np.size();
         for (size_t i = 0; i < n; i++)
-            column_to_model(particles[i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
+            column_to_model(particles[i0 + i], ctx_[0]->layout(), ctx_[0]->sampler_layout(),
+                            ColRef{const_cast<double*>(state.data()) + i, n}, np[i]);
     }
     kimacuda::Context& sampler_ctx() { return *ctx_[0]; }
 

@@ -103,6 +103,10 @@ public:
         check(kc_sampler_download(ctx_, state, np, logl, tb, level));
     }
     void sampler_get_particle(int which, double* col, int32_t* np) { check(kc_sampler_get_particle(ctx_, which, col, np)); }
+    void sampler_set_particle(int which, const double* col, int32_t np, double logl, double tb, int32_t level)
+    {
+        check(kc_sampler_set_particle(ctx_, which, col, np, logl, tb, level));
+    }
     void sampler_copy_particles(int n, const int32_t* dst, const int32_t* src) { check(kc_sampler_copy_particles(ctx_, n, dst, src)); }
     void sampler_set_levels(int L, const double* logl, const double* tb, const double* log_X, const uint64_t* tries,
                             bool enough, bool at_max)

@@ -128,6 +128,10 @@ int kc_sampler_download(kc_ctx* ctx, double* state, int32_t* np, double* logl, d
                         int32_t* level);
 /* One particle's column (save_particle, SamplerImpl.h:503-531). */
 int kc_sampler_get_particle(kc_ctx* ctx, int which, double* state_col, int32_t* np);
+/* The reverse: overwrite one particle (a replacement that kill_lagging_particles takes from a lane
+ * another rank owns, SamplerImpl.h:571-573 across processes). */
+int kc_sampler_set_particle(kc_ctx* ctx, int which, const double* state_col, int32_t np, double logl,
+                            double tiebreaker, int32_t level);
 /* particles[dst[i]] = particles[src[i]] with likelihood and level assignment
  * (kill_lagging_particles, SamplerImpl.h:566-577); no dst may also be a src. */
 int kc_sampler_copy_particles(kc_ctx* ctx, int n, const int32_t* dst, const int32_t* src);

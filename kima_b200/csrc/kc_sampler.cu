@@ -394,6 +394,25 @@ int kc_sampler_get_particle(kc_ctx* c, int which, double* state_col, int32_t* np
     return KC_OK;
 }
 
+int kc_sampler_set_particle(kc_ctx* c, int which, const double* state_col, int32_t np, double logl,
+                            double tiebreaker, int32_t level)
+{
+    int rc = kc::need_sampler(c);
+    if (rc) return rc;
+    const SamplerParams& sp = c->sampler->sp;
+    if (which < 0 || which >= sp.SL.n_particles) return fail(KC_ERR_ARG, "particle index out of range");
+    if (!state_col) return fail(KC_ERR_ARG, "state_col is null");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpy2DAsync(sp.S + which, sizeof(double) * sp.ldp, state_col, sizeof(double), sizeof(double),
+                         sp.SL.n_state, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(sp.np + which, &np, sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(sp.logl + which, &logl, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(sp.tb + which, &tiebreaker, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(sp.level + which, &level, sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return KC_OK;
+}
+
 int kc_sampler_copy_particles(kc_ctx* c, int n, const int32_t* dst, const int32_t* src)
 {
     int rc = kc::need_sampler(c);

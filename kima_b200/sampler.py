@@ -79,6 +79,11 @@ class DeviceSampler:
         _lib.check(self.lib.kc_sampler_get_particle(self.ctx, which, _d(col), ctypes.byref(n)))
         return col, n.value
 
+    def set_particle(self, which: int, col, np_: int, logl: float, tiebreaker: float, level: int) -> None:
+        col = np.ascontiguousarray(col, np.float64)
+        assert col.size == self.n_state
+        _lib.check(self.lib.kc_sampler_set_particle(self.ctx, which, _d(col), np_, logl, tiebreaker, level))
+
     def copy_particles(self, dst, src) -> None:
         dst = np.ascontiguousarray(dst, np.int32)
         src = np.ascontiguousarray(src, np.int32)

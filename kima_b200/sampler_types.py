@@ -69,6 +69,8 @@ SAMPLER_SIGNATURES = {
     "kc_sampler_upload": (ctypes.c_int, [ctypes.c_void_p, _dp, _ip, _dp, _dp, _ip]),
     "kc_sampler_download": (ctypes.c_int, [ctypes.c_void_p, _dp, _ip, _dp, _dp, _ip]),
     "kc_sampler_get_particle": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _dp, _ip]),
+    "kc_sampler_set_particle": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _dp, ctypes.c_int32, ctypes.c_double,
+                                              ctypes.c_double, ctypes.c_int32]),
     "kc_sampler_copy_particles": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _ip, _ip]),
     "kc_sampler_set_levels": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _dp, _dp, _dp, _up,
                                              ctypes.c_int, ctypes.c_int]),

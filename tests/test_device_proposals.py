@@ -107,3 +107,34 @@ def test_evidence_at_many_lanes_matches_host_proposals(gpu, tmp_path):
     se = np.sqrt(dev.var(ddof=1) / 3 + host.var(ddof=1) / 3)
     assert abs(dev.mean() - host.mean()) < 1.0 + 3.0 * se, z
     assert abs(dev.mean() - (-146.0)) < 5.0, z   # the reference's CPU runs give -143.6 ... -147
+
+
+def test_two_ranks_reproduce_the_single_process_device_chain(gpu, tmp_path):
+    """One process per GPU with device proposals: each rank keeps its lanes' particles in its own
+    HBM, lane k draws from stream seed + k whoever steps it, and the barrier (counters summed,
+    `above` lists concatenated, likelihoods / level assignments gathered; a lagging particle's
+    replacement travels as one column) leaves every rank with the state a single process has:
+    2 ranks x 8 lanes write, byte for byte, the files of 1 process x 16 lanes."""
+    from test_host_cpp import _gpu_count
+    if _gpu_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    opts = "2\n50\n10\n5\n0\n1\n100\n600\n"  # lambda = 1: lagging particles get replaced early and often
+    one = run("gpu", "BL2009", tmp_path, "one", 16, 43, True, opts)
+    exe = os.path.join(BUILD, "kima_gpu_BL2009")
+    d = tmp_path / "two"
+    d.mkdir()
+    for f in CASES["BL2009"][0]:
+        shutil.copy(os.path.join(E2E, f), d)
+    (d / "OPTIONS").write_text(opts)
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_PORT="29577",
+                   KIMA_DEVICE_PROPOSALS="1")
+        procs.append(subprocess.Popen([exe, "-t", "16", "-s", "43"], cwd=d, env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=600) for p in procs]
+    for p, (so, se) in zip(procs, outs):
+        assert p.returncode == 0, so[-1500:] + se[-1500:]
+    assert "Replacing lagging particle" in outs[0][0]  # replacements happened (half of them cross ranks on average)
+    for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
+        assert (one / f).read_bytes() == (d / f).read_bytes(), f

@@ -139,6 +139,10 @@ def test_mcmc_on_device_matches_reference(gpu, ref, name, P, L_levels, at_max):
         for d, s_ in ((0, 7), (5, 9)):
             np.testing.assert_array_equal(S2[:, d], S2[:, s_])
             assert (np2[d], l2[d], t2[d], lev2[d]) == (np2[s_], l2[s_], t2[s_], lev2[s_])
+        ds.set_particle(2, S2[:, 11], int(np2[11]), -12.5, 0.25, 1)
+        S3, np3, l3, t3, lev3 = ds.download()
+        np.testing.assert_array_equal(S3[:, 2], S2[:, 11])
+        assert (np3[2], l3[2], t3[2], lev3[2]) == (np2[11], -12.5, 0.25, 1)
         ds.close()
 
 

@@ -82,13 +82,14 @@ def prepare_dir(name, threads, thread_steps, saves):
     return d
 
 
-def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, timeout=420):
+def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, timeout=420, env=None):
     """This process's rank of a one-process-per-GPU run of the batched GPU sampler in the shared
     run directory `d` (every rank calls this at the same time)."""
     exe = os.path.join(BUILD, "kima_gpu_%s" % name)
     e = dict(os.environ, KIMA_PROFILE="1", RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(local), MASTER_PORT=str(port),
              KIMA_HOST_THREADS=str(host_threads))
     e.pop("KIMA_CUDA_DEVICE", None)
+    e.update(env or {})
     t0 = time.perf_counter()
     try:
         r = subprocess.run([exe, "-t", str(threads), "-s", str(seed)], cwd=d, capture_output=True, text=True,
