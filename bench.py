@@ -309,6 +309,11 @@ def main():
         print(json.dumps(out))
         return 0
 
+    # stdout carries exactly one JSON line: whatever libraries write there meanwhile (NCCL's version
+    # banner at the first collective, ...) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank, world, local = init_dist(a.gpus)
     from kima_b200 import LikelihoodEngine
     from kima_b200.dist import TorchBarrierExchange
@@ -403,6 +408,9 @@ def main():
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    os.close(saved_stdout)
     if rank == 0:
         print(json.dumps(out))
     return 0
