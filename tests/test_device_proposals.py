@@ -138,3 +138,28 @@ def test_two_ranks_reproduce_the_single_process_device_chain(gpu, tmp_path):
     assert "Replacing lagging particle" in outs[0][0]  # replacements happened (half of them cross ranks on average)
     for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
         assert (one / f).read_bytes() == (d / f).read_bytes(), f
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_every_shipped_example_runs_with_device_proposals(gpu, tmp_path, name):
+    """The reference's CI set-up (tests/test_suite/OPTIONS, -t 4 -s 43) of every example — GP with
+    hyperpriors, Student-t, several instruments, free and fixed Np — through run_device: no fallback to
+    host proposals, the reference's columns, finite likelihoods, levels being built."""
+    ci = open(os.path.join(E2E, "OPTIONS")).read()
+    exe = os.path.join(BUILD, "kima_gpu_%s" % name)
+    d = tmp_path / name
+    d.mkdir()
+    for f in CASES[name][0]:
+        shutil.copy(os.path.join(E2E, f), d)
+    (d / "OPTIONS").write_text(ci)
+    env = dict(os.environ, KIMA_DEVICE_PROPOSALS="1", KIMA_PROFILE="1")
+    r = subprocess.run([exe, "-t", "4", "-s", "43"], cwd=d, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "(device proposals)" in r.stderr and "proposals stay on the host" not in r.stderr
+    hdr, rows = load_sample(d / "sample.txt")
+    hg, rg = load_sample(os.path.join(E2E, "%s_sample_seed43.txt" % name))
+    assert hdr == hg and rows.shape == rg.shape
+    info = np.loadtxt(d / "sample_info.txt", ndmin=2)
+    assert np.all(np.isfinite(info[:, 1])) and np.all(info[:, 1] > -1e299)
+    levels = np.loadtxt(d / "levels.txt", ndmin=2)
+    assert len(levels) >= 3 and np.all(np.diff(levels[1:, 1]) > 0)
