@@ -261,6 +261,45 @@ def predictive_leg(data, flags, device: int, threads: int, B: int = 1184, nt: in
             "max_rel_err_vs_cpu": err}
 
 
+def sampler_device_leg(local: int, lanes: int = 65536, steps: int = 50, reps: int = 3):
+    """SURVEY.md 8 row f1, device-timed: whole MCMC steps (proposal, prior test, likelihood, accept, level
+    move, counters) of `lanes` lanes on the GPU through kc_sampler_run, synthetic white-noise data of the
+    51Peg shape (N=256, Np in {0,1}); CUDA events on the library's stream around each block of steps."""
+    from kima_b200 import LikelihoodEngine
+    from kima_b200.sampler import DeviceSampler, SamplerOptions, default_prior_table, draw_from_prior
+    flags = ModelFlags(npmax=1)
+    data = make_data(256)
+    pri = default_prior_table(flags, data)
+    with LikelihoodEngine(data, flags, lanes, device=local) as eng:
+        ds = DeviceSampler(eng, pri, SamplerOptions(lanes=lanes, num_particles=1, thread_steps=steps, max_levels=64))
+        S, nps = draw_from_prior(ds, flags, pri, lanes)
+        logl = eng.evaluate(S[:eng.layout["n_rows"]], nps)
+        logl = np.where(np.isfinite(logl), logl, -1e300)
+        tb = np.random.default_rng(1).uniform(0.01, 0.99, lanes)
+        lv_logl = np.concatenate([[-1e300], np.quantile(logl, np.linspace(0.1, 0.8, 7))])
+        ds.upload(S, nps, logl, tb, np.zeros(lanes, np.int32))
+        tries = np.full(8, 1000, np.uint64)
+        ms = []
+        launches0 = eng.launch_count()
+        for _ in range(reps + 1):  # the first block is the warm-up
+            ds.set_levels(lv_logl, np.full(8, 0.5), -np.arange(8.0), tries, True, True)
+            ds.run(steps)
+            cnt, _ = ds.collect()
+            ms.append(ds.last_run_ms())
+            tries = tries + cnt[:, 1]
+        launches = eng.launch_count() - launches0
+        eng.log_likelihood_device(lanes)
+        eng.sync()
+        lk = eng.last_kernel_ms()
+        ds.close()
+    best = min(ms[1:])
+    return {"unit": "MCMC steps/s", "workload": "white noise N=256, Np<=1 (51Peg shape), %d lanes x 1 particle, "
+            "8 levels, blocks of %d lock-step steps" % (lanes, steps), "value": lanes * steps / best * 1e3,
+            "ms_per_step": best / steps, "likelihood_kernel_ms_per_step": lk, "gpu_launches": launches,
+            "accept_rate": float(cnt[:, 0].sum() / max(1, cnt[:, 1].sum())),
+            "kernels": "smp_accept_propose_kernel + keplerian kernel per step (profiles/launches_sampler_r01e_summary.txt)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -370,6 +409,7 @@ def main():
         out["sampler"]["device_proposals"] = [
             sampler_bench.run("gpu", "51Peg", 65536, 100, 20, env=dev_env),
             sampler_bench.run("gpu", "CoRoT7", 16384, 100, 10, env=dev_env)]
+        out["sampler"]["device_steps"] = sampler_device_leg(local)
     if rank == 0 and world == 1 and not a.skip_predictive and not a.skip_cpu_baseline:
         out["predictive"] = predictive_leg(data, fg, local, threads)
     if world > 1 and not a.skip_sampler and os.path.exists(os.path.join(ROOT, "host", "_build", "kima_gpu_CoRoT7")):
