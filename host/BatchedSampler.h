@@ -308,6 +308,10 @@ class BatchedSampler : public Sampler<ModelType> {
     // opt-in, the default stays byte-identical.  rngs[0] (bookkeeping draws) stays the host's.
     unsigned int seed0 = 0;
     unsigned int deletions_dev = 0;
+    // one process: all_above stays in HBM (kc_sampler_collect_pool / kc_sampler_pool_select), the host
+    // only knows its size; several processes: the lists are gathered on the host as before
+    bool pool_mode = false;
+    int64_t pool_n = 0;
 
     static bool device_proposals_requested()
     {
@@ -449,24 +453,40 @@ class BatchedSampler : public Sampler<ModelType> {
     void bookkeeping_device()
     {
         bool created_level = false;
-        if (!this->enough_levels(this->levels) && (this->all_above.size() >= this->options.new_level_interval)) {
+        const size_t n_all = pool_mode ? (size_t)pool_n : this->all_above.size();
+        if (!this->enough_levels(this->levels) && (n_all >= this->options.new_level_interval)) {
             // the reference sorts all_above and keeps what lies above position `index`; only that
-            // element and the SET above it matter afterwards (the next creation orders again), so a
-            // selection does the same in O(n): with millions of lanes-times-steps entries per
-            // barrier the full sort was most of the bookkeeping
-            const int index = static_cast<int>((1. - 1. / this->compression) * this->all_above.size());
-            std::nth_element(this->all_above.begin(), this->all_above.begin() + index, this->all_above.end());
-            std::cout << "# Creating level " << this->levels.size() << " with log likelihood = ";
-            std::cout << std::setprecision(12);
-            std::cout << this->all_above[index].get_value() << "." << std::endl;
-            this->levels.push_back(Level(this->all_above[index]));
-            this->all_above.erase(this->all_above.begin(), this->all_above.begin() + index + 1);
+            // element and the SET above it matter afterwards (the next creation orders again)
+            const int index = static_cast<int>((1. - 1. / this->compression) * n_all);
+            LikelihoodType new_level;
+            if (pool_mode) {
+                // ordered and cut on the GPU, where the lists already are: one pair comes back
+                double v = 0, t = 0;
+                evaluator->sampler_ctx().sampler_pool_select(index, &v, &t, &pool_n);
+                new_level = LikelihoodType(v, t);
+            } else {
+                // a selection does the same in O(n): with millions of lanes-times-steps entries per
+                // barrier the full sort was most of the bookkeeping
+                std::nth_element(this->all_above.begin(), this->all_above.begin() + index, this->all_above.end());
+                new_level = this->all_above[index];
+                this->all_above.erase(this->all_above.begin(), this->all_above.begin() + index + 1);
+            }
+            if (rank() == 0) {
+                std::cout << "# Creating level " << this->levels.size() << " with log likelihood = ";
+                std::cout << std::setprecision(12);
+                std::cout << new_level.get_value() << "." << std::endl;
+            }
+            this->levels.push_back(Level(new_level));
             if (this->enough_levels(this->levels)) {
                 const double reg = this->options.new_level_interval * sqrt(this->options.lambda);
                 Level::renormalise_visits(this->levels, static_cast<int>(reg));
                 this->all_above.clear();
+                if (pool_mode) {
+                    evaluator->sampler_ctx().sampler_pool_clear();
+                    pool_n = 0;
+                }
                 this->options.max_num_levels = this->levels.size();
-                std::cout << "# Done creating levels." << std::endl;
+                if (rank() == 0) std::cout << "# Done creating levels." << std::endl;
             } else {
                 kill_lagging_device();
             }
@@ -511,6 +531,9 @@ class BatchedSampler : public Sampler<ModelType> {
         cfg.beta = this->options.beta;
         cfg.seed = seed0;
         cfg.lane0 = (int32_t)lane_lo();  // lane k of the run draws from stream seed + k whatever rank steps it
+        pool_mode = (W == 1) && !(std::getenv("KIMA_HOST_ABOVE") && std::atoi(std::getenv("KIMA_HOST_ABOVE")));
+        pool_n = 0;
+        cfg.pool_reserve = pool_mode ? (int32_t)this->options.new_level_interval : 0;
         const std::string bad = evaluator->sampler_create(this->particles[0], cfg);
         if (!bad.empty()) {
             std::cerr << "# KIMA_DEVICE_PROPOSALS: " << bad << " has no device counterpart; proposals stay on the host"
@@ -527,7 +550,7 @@ class BatchedSampler : public Sampler<ModelType> {
         evaluator->sampler_upload(this->particles, p0, p1, logl, tb, level);
         kimacuda::Context& ctx = evaluator->sampler_ctx();
         const int max_local = (int)(Tl * this->options.thread_steps), max_pairs = max_local * W;
-        std::vector<double> above(2 * (size_t)max_pairs), above_local(W > 1 ? 2 * (size_t)max_local : 0);
+        std::vector<double> above(pool_mode ? 0 : 2 * (size_t)max_pairs), above_local(W > 1 ? 2 * (size_t)max_local : 0);
         std::vector<double> lv_logl, lv_tb, lv_logX, xs(W > 1 ? 3 * nl : 0), xr(W > 1 ? 3 * n : 0);
         std::vector<uint64_t> lv_tries, counters;
         std::vector<int> counts(W);
@@ -548,7 +571,13 @@ class BatchedSampler : public Sampler<ModelType> {
             ctx.sampler_set_levels((int)L, lv_logl.data(), lv_tb.data(), lv_logX.data(), lv_tries.data(),
                                    this->enough_levels(this->levels), L == this->options.max_num_levels);
             ctx.sampler_run((int)this->options.thread_steps);
-            int n_above = ctx.sampler_collect(counters.data(), W > 1 ? above_local.data() : above.data(), max_local);
+            int n_above = 0;
+            if (pool_mode) {
+                int64_t n_new = 0;
+                ctx.sampler_collect_pool(counters.data(), &n_new, &pool_n);
+            } else {
+                n_above = ctx.sampler_collect(counters.data(), W > 1 ? above_local.data() : above.data(), max_local);
+            }
             const double tc = now();
             ctx.sampler_download(nullptr, nullptr, logl.data() + p0, tb.data() + p0, level.data() + p0);
             if (W > 1) {

@@ -114,6 +114,16 @@ public:
         check(kc_sampler_set_levels(ctx_, L, logl, tb, log_X, tries, enough, at_max));
     }
     void sampler_run(int steps) { check(kc_sampler_run(ctx_, steps)); }
+    // `all_above` kept in HBM
+    void sampler_collect_pool(uint64_t* counters, int64_t* n_new, int64_t* n_pool)
+    {
+        check(kc_sampler_collect_pool(ctx_, counters, n_new, n_pool));
+    }
+    void sampler_pool_select(int64_t index, double* value, double* tb, int64_t* n_pool)
+    {
+        check(kc_sampler_pool_select(ctx_, index, value, tb, n_pool));
+    }
+    void sampler_pool_clear() { check(kc_sampler_pool_clear(ctx_)); }
     int sampler_collect(uint64_t* counters, double* above_pairs, int max_pairs)
     {
         int n = 0;

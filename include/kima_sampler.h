@@ -100,7 +100,8 @@ typedef struct kc_sampler_config {
     double beta;             /* strength of the uniform-exploration term                */
     uint64_t seed;           /* lane k draws from the stream with key seed + lane0 + k  */
     int32_t lane0;           /* index of this context's first lane in the whole run     */
-    int32_t reserved;
+    int32_t pool_reserve;    /* extra capacity of the device-resident `all_above` pool:
+                                options.new_level_interval (0 = the pool is not used)   */
 } kc_sampler_config;
 
 /* Rows of a particle's state column: the kc_layout rows (what the likelihood reads), then
@@ -153,6 +154,23 @@ int kc_sampler_run(kc_ctx* ctx, int steps);
  * (at most max_pairs; *n_above receives the number found).  Either output may be NULL. */
 int kc_sampler_collect(kc_ctx* ctx, uint64_t* counters, double* above_pairs, int max_pairs,
                        int* n_above);
+
+/* ---- `all_above` kept in HBM (one process per run) -----------------------------------------
+ * Sampler::all_above (Sampler.h:59; SamplerImpl.h:324-329, 384-399) grows by up to lanes x
+ * thread_steps (value, tiebreaker) pairs per barrier and is only ever (a) counted, (b) ordered to
+ * place a new level at position `index` and cut at that position, (c) cleared.  With tens of
+ * thousands of lanes, shipping and ordering it on the host is most of the barrier; these entry
+ * points keep it on the device.
+ * kc_sampler_collect_pool: kc_sampler_collect with the lanes' `above` lists appended to the pool
+ * instead of returned; *n_new = pairs appended, *n_pool = pool size afterwards.
+ * kc_sampler_pool_select: orders the pool by (value, tiebreaker) (LikelihoodType::operator<),
+ * returns the element at position `index` and keeps the elements after it — do_bookkeeping's
+ * sort + levels.push_back(all_above[index]) + erase(begin, begin + index + 1).
+ * kc_sampler_pool_clear: all_above.clear().  kc_sampler_pool_fetch: test hook (pool order). */
+int kc_sampler_collect_pool(kc_ctx* ctx, uint64_t* counters, int64_t* n_new, int64_t* n_pool);
+int kc_sampler_pool_select(kc_ctx* ctx, int64_t index, double* value, double* tiebreaker, int64_t* n_pool);
+int kc_sampler_pool_clear(kc_ctx* ctx);
+int kc_sampler_pool_fetch(kc_ctx* ctx, double* pairs, int64_t max_pairs, int64_t* n);
 
 /* Device time (CUDA events on the context stream) of the last kc_sampler_run, all kernels of
  * its steps included; waits for the run to finish. */

@@ -21,6 +21,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <cub/device/device_radix_sort.cuh>
 #include "kc_ctx.h"
 #include "kc_sampler_logic.cuh"
 
@@ -50,6 +51,14 @@ struct SamplerState {
     int32_t* h_total = nullptr;      // pinned
     double* h_above = nullptr;       // pinned, [T * max_steps * 2]
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the last kc_sampler_run
+    // `all_above` in HBM: values and tiebreakers (SoA), ping-pong buffers for the ordered cut
+    double *pool_v[2] = {nullptr, nullptr}, *pool_t[2] = {nullptr, nullptr};
+    uint64_t *pool_key[2] = {nullptr, nullptr};
+    uint32_t *pool_idx[2] = {nullptr, nullptr};
+    void* pool_tmp = nullptr;
+    size_t pool_tmp_bytes = 0, pool_cap = 0, pool_n = 0;
+    int pool_cur = 0;
+    double* h_pivot = nullptr;  // pinned, 2 doubles
     bool timed = false;
     std::vector<void*> allocs;
 };
@@ -132,6 +141,55 @@ __global__ void smp_gather_above_kernel(SamplerParams sp, const int32_t* offsets
     for (int i = 0; i < 2 * n; i++) o[i] = a[i];
 }
 
+// the lanes' `above` lists appended to the pool (SoA) at `base`, in lane order
+__global__ void smp_gather_pool_kernel(SamplerParams sp, const int32_t* offsets, double* pv, double* pt, size_t base)
+{
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= sp.lanes) return;
+    const int n = sp.n_above[lane];
+    const double* a = sp.above + (size_t)lane * sp.max_steps * 2;
+    const size_t o = base + (size_t)offsets[lane];
+    for (int i = 0; i < n; i++) {
+        pv[o + i] = a[2 * i];
+        pt[o + i] = a[2 * i + 1];
+    }
+}
+// order-preserving map double -> uint64 (radix sort key)
+__device__ __forceinline__ uint64_t ordered_key(double x)
+{
+    const uint64_t b = (uint64_t)__double_as_longlong(x);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__global__ void smp_pool_keys_kernel(const double* src, const uint32_t* idx, size_t n, uint64_t* key, uint32_t* iota)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    key[i] = ordered_key(idx ? src[idx[i]] : src[i]);
+    if (iota) iota[i] = (uint32_t)i;
+}
+// entries of sorted rank > index, in order, into the other buffers; the pivot to `pivot`
+__global__ void smp_pool_cut_kernel(const double* v, const double* t, const uint32_t* perm, size_t n, size_t index,
+                                    double* vo, double* to, double* pivot)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t src = perm[i];
+    if (i == index) {
+        pivot[0] = v[src];
+        pivot[1] = t[src];
+    } else if (i > index) {
+        vo[i - index - 1] = v[src];
+        to[i - index - 1] = t[src];
+    }
+}
+__global__ void smp_pool_pairs_kernel(const double* v, const double* t, size_t n, double* out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[2 * i] = v[i];
+    out[2 * i + 1] = t[i];
+}
+
 __global__ void smp_copy_particles_kernel(SamplerParams sp, int n, const int32_t* dst, const int32_t* src)
 {
     const int i = blockIdx.x;
@@ -205,6 +263,7 @@ void sampler_free(kc_ctx* c)
     if (s->h_cnt_sum) cudaFreeHost(s->h_cnt_sum);
     if (s->h_total) cudaFreeHost(s->h_total);
     if (s->h_above) cudaFreeHost(s->h_above);
+    if (s->h_pivot) cudaFreeHost(s->h_pivot);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     delete s;
@@ -323,6 +382,26 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     CU(cudaMallocHost(&s->h_above, sizeof(double) * (size_t)T * sp.max_steps * 2));
     CU(cudaEventCreate(&s->ev0));
     CU(cudaEventCreate(&s->ev1));
+    if (cfg->pool_reserve > 0) {
+        // leftovers of a cut are at most 1/compression of the pool; without a cut the pool stops
+        // growing at new_level_interval + one barrier's worth
+        s->pool_cap = (size_t)3 * T * sp.max_steps + (size_t)cfg->pool_reserve;
+        for (int k = 0; k < 2; k++) {
+            cudaError_t e1 = kc::dalloc(s, &s->pool_v[k], s->pool_cap), e2 = kc::dalloc(s, &s->pool_t[k], s->pool_cap);
+            cudaError_t e3 = kc::dalloc(s, &s->pool_key[k], s->pool_cap), e4 = kc::dalloc(s, &s->pool_idx[k], s->pool_cap);
+            if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess) {
+                kc::sampler_free(c);
+                return fail(KC_ERR_CUDA, "sampler allocation (above pool)");
+            }
+        }
+        size_t bytes = 0;
+        CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, s->pool_key[0], s->pool_key[1], s->pool_idx[0], s->pool_idx[1],
+                                           (int64_t)s->pool_cap, 0, 64, c->stream));
+        s->pool_tmp_bytes = bytes;
+        cudaError_t e = kc::dalloc(s, (char**)&s->pool_tmp, bytes);
+        if (e != cudaSuccess) { kc::sampler_free(c); return fail_cuda(e, "sampler allocation (sort scratch)"); }
+        CU(cudaMallocHost(&s->h_pivot, 2 * sizeof(double)));
+    }
     // the perturb call tree keeps its component vectors on the local stack
     size_t stack = 0;
     CU(cudaDeviceGetLimit(&stack, cudaLimitStackSize));
@@ -534,6 +613,102 @@ int kc_sampler_collect(kc_ctx* c, uint64_t* counters, double* above_pairs, int m
     CU(cudaGetLastError());
     if (counters) std::memcpy(counters, s->h_cnt_sum, sizeof(uint64_t) * 4 * L);
     if (n_above) *n_above = total;
+    return KC_OK;
+}
+
+int kc_sampler_collect_pool(kc_ctx* c, uint64_t* counters, int64_t* n_new, int64_t* n_pool)
+{
+    int rc = kc::need_sampler(c);
+    if (rc) return rc;
+    SamplerState* s = c->sampler;
+    const SamplerParams& sp = s->sp;
+    if (!s->pool_cap) return fail(KC_ERR_ARG, "the sampler was created without an above pool (pool_reserve = 0)");
+    if (sp.n_levels < 1) return fail(KC_ERR_ARG, "kc_sampler_set_levels has not been called");
+    CU(cudaSetDevice(c->device));
+    const int L = sp.n_levels, T = sp.lanes;
+    if (counters) {
+        kc::smp_reduce_counters_kernel<<<dim3(L, 4), 256, 0, c->stream>>>(sp, s->d_cnt_sum);
+        CU(cudaMemcpyAsync(s->h_cnt_sum, s->d_cnt_sum, sizeof(uint64_t) * 4 * L, cudaMemcpyDeviceToHost, c->stream));
+        c->launches += 1;
+    }
+    kc::smp_scan_above_kernel<<<1, 1024, 0, c->stream>>>(sp.n_above, T, s->d_offsets);
+    CU(cudaMemcpyAsync(s->h_total, s->d_offsets + T, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    // capacity is checked before the append lands: one barrier adds at most T * max_steps
+    if (s->pool_n + (size_t)T * sp.max_steps > s->pool_cap)
+        return fail(KC_ERR_ARG, "above pool full: place a level (kc_sampler_pool_select) or clear it");
+    kc::smp_gather_pool_kernel<<<(T + 127) / 128, 128, 0, c->stream>>>(sp, s->d_offsets, s->pool_v[s->pool_cur],
+                                                                      s->pool_t[s->pool_cur], s->pool_n);
+    c->launches += 2;
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    s->pool_n += (size_t)*s->h_total;
+    if (counters) std::memcpy(counters, s->h_cnt_sum, sizeof(uint64_t) * 4 * L);
+    if (n_new) *n_new = *s->h_total;
+    if (n_pool) *n_pool = (int64_t)s->pool_n;
+    return KC_OK;
+}
+
+int kc_sampler_pool_select(kc_ctx* c, int64_t index, double* value, double* tiebreaker, int64_t* n_pool)
+{
+    int rc = kc::need_sampler(c);
+    if (rc) return rc;
+    SamplerState* s = c->sampler;
+    if (!s->pool_cap) return fail(KC_ERR_ARG, "the sampler was created without an above pool (pool_reserve = 0)");
+    const size_t n = s->pool_n;
+    if (index < 0 || (size_t)index >= n) return fail(KC_ERR_ARG, "index outside the pool");
+    CU(cudaSetDevice(c->device));
+    const int cur = s->pool_cur, alt = cur ^ 1;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    // lexicographic (value, tiebreaker) with a stable LSD sort: by tiebreaker first, then by value
+    kc::smp_pool_keys_kernel<<<grid, 256, 0, c->stream>>>(s->pool_t[cur], nullptr, n, s->pool_key[0], s->pool_idx[0]);
+    size_t bytes = s->pool_tmp_bytes;
+    CU(cub::DeviceRadixSort::SortPairs(s->pool_tmp, bytes, s->pool_key[0], s->pool_key[1], s->pool_idx[0], s->pool_idx[1],
+                                       (int64_t)n, 0, 64, c->stream));
+    kc::smp_pool_keys_kernel<<<grid, 256, 0, c->stream>>>(s->pool_v[cur], s->pool_idx[1], n, s->pool_key[0], nullptr);
+    bytes = s->pool_tmp_bytes;
+    CU(cub::DeviceRadixSort::SortPairs(s->pool_tmp, bytes, s->pool_key[0], s->pool_key[1], s->pool_idx[1], s->pool_idx[0],
+                                       (int64_t)n, 0, 64, c->stream));
+    double* d_pivot = reinterpret_cast<double*>(s->pool_key[0]);  // keys are dead after the second sort
+    kc::smp_pool_cut_kernel<<<grid, 256, 0, c->stream>>>(s->pool_v[cur], s->pool_t[cur], s->pool_idx[0], n, (size_t)index,
+                                                        s->pool_v[alt], s->pool_t[alt], d_pivot);
+    CU(cudaMemcpyAsync(s->h_pivot, d_pivot, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    c->launches += 3;
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    s->pool_cur = alt;
+    s->pool_n = n - (size_t)index - 1;
+    if (value) *value = s->h_pivot[0];
+    if (tiebreaker) *tiebreaker = s->h_pivot[1];
+    if (n_pool) *n_pool = (int64_t)s->pool_n;
+    return KC_OK;
+}
+
+int kc_sampler_pool_clear(kc_ctx* c)
+{
+    int rc = kc::need_sampler(c);
+    if (rc) return rc;
+    c->sampler->pool_n = 0;
+    return KC_OK;
+}
+
+int kc_sampler_pool_fetch(kc_ctx* c, double* pairs, int64_t max_pairs, int64_t* n)
+{
+    int rc = kc::need_sampler(c);
+    if (rc) return rc;
+    SamplerState* s = c->sampler;
+    if (!s->pool_cap) return fail(KC_ERR_ARG, "the sampler was created without an above pool (pool_reserve = 0)");
+    CU(cudaSetDevice(c->device));
+    const size_t take = s->pool_n < (size_t)max_pairs ? s->pool_n : (size_t)max_pairs;
+    if (take && pairs) {
+        double* d = nullptr;
+        CU(cudaMalloc(&d, sizeof(double) * 2 * take));
+        kc::smp_pool_pairs_kernel<<<(unsigned)((take + 255) / 256), 256, 0, c->stream>>>(s->pool_v[s->pool_cur],
+                                                                                       s->pool_t[s->pool_cur], take, d);
+        CU(cudaMemcpyAsync(pairs, d, sizeof(double) * 2 * take, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaFree(d));
+    }
+    if (n) *n = (int64_t)s->pool_n;
     return KC_OK;
 }
 

@@ -32,10 +32,11 @@ class SamplerOptions:
     beta: float = 100.0
     seed: int = 43
     lane0: int = 0
+    pool_reserve: int = 0
 
     def to_c(self) -> CSamplerConfig:
         return CSamplerConfig(self.lanes, self.num_particles, self.thread_steps, self.max_levels,
-                              self.lambda_, self.beta, self.seed, self.lane0, 0)
+                              self.lambda_, self.beta, self.seed, self.lane0, self.pool_reserve)
 
 
 class DeviceSampler:
@@ -110,6 +111,29 @@ class DeviceSampler:
         n = ctypes.c_int32()
         _lib.check(self.lib.kc_sampler_collect(self.ctx, _u(cnt), _d(above), max_pairs, ctypes.byref(n)))
         return cnt[:self.n_levels], above[:min(n.value, max_pairs)].copy()
+
+    # ---- `all_above` kept in HBM ----------------------------------------------------------
+    def collect_pool(self):
+        """(counters[L][4], pairs appended, pool size)"""
+        cnt = np.zeros((max(self.n_levels, 1), 4), np.uint64)
+        a, b = ctypes.c_int64(), ctypes.c_int64()
+        _lib.check(self.lib.kc_sampler_collect_pool(self.ctx, _u(cnt), ctypes.byref(a), ctypes.byref(b)))
+        return cnt[:self.n_levels], a.value, b.value
+
+    def pool_select(self, index: int):
+        """(value, tiebreaker) at sorted position `index`; the pool keeps what lies above it."""
+        v, t, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_int64()
+        _lib.check(self.lib.kc_sampler_pool_select(self.ctx, index, ctypes.byref(v), ctypes.byref(t), ctypes.byref(n)))
+        return v.value, t.value, n.value
+
+    def pool_clear(self) -> None:
+        _lib.check(self.lib.kc_sampler_pool_clear(self.ctx))
+
+    def pool_fetch(self, max_pairs: int) -> np.ndarray:
+        out = np.empty((max(max_pairs, 1), 2))
+        n = ctypes.c_int64()
+        _lib.check(self.lib.kc_sampler_pool_fetch(self.ctx, _d(out), max_pairs, ctypes.byref(n)))
+        return out[:n.value].copy()
 
     def get_counters(self) -> np.ndarray:
         c = np.empty(self.opt.lanes, np.uint64)

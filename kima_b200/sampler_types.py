@@ -52,7 +52,7 @@ class CSamplerConfig(ctypes.Structure):
     """``kc_sampler_config``"""
     _fields_ = [("lanes", ctypes.c_int32), ("num_particles", ctypes.c_int32), ("max_steps", ctypes.c_int32),
                 ("max_levels", ctypes.c_int32), ("lambda_", ctypes.c_double), ("beta", ctypes.c_double),
-                ("seed", ctypes.c_uint64), ("lane0", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+                ("seed", ctypes.c_uint64), ("lane0", ctypes.c_int32), ("pool_reserve", ctypes.c_int32)]
 
 
 class CSamplerLayout(ctypes.Structure):
@@ -76,6 +76,11 @@ SAMPLER_SIGNATURES = {
                                              ctypes.c_int, ctypes.c_int]),
     "kc_sampler_run": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "kc_sampler_collect": (ctypes.c_int, [ctypes.c_void_p, _up, _dp, ctypes.c_int, _ip]),
+    "kc_sampler_collect_pool": (ctypes.c_int, [ctypes.c_void_p, _up, ctypes.POINTER(ctypes.c_int64),
+                                              ctypes.POINTER(ctypes.c_int64)]),
+    "kc_sampler_pool_select": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64, _dp, _dp, ctypes.POINTER(ctypes.c_int64)]),
+    "kc_sampler_pool_clear": (ctypes.c_int, [ctypes.c_void_p]),
+    "kc_sampler_pool_fetch": (ctypes.c_int, [ctypes.c_void_p, _dp, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
     "kc_sampler_last_run_ms": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_float)]),
     "kc_sampler_get_counters": (ctypes.c_int, [ctypes.c_void_p, _up]),
     "kc_sampler_set_counters": (ctypes.c_int, [ctypes.c_void_p, _up]),

@@ -26,7 +26,7 @@ pytestmark = pytest.mark.gpu
 OPTIONS = "2\n1000\n500\n100\n0\n10\n100\n4000\n"
 
 
-def run(kind, name, tmp_path, tag, lanes, seed, device, options=OPTIONS):
+def run(kind, name, tmp_path, tag, lanes, seed, device, options=OPTIONS, extra_env=None):
     exe = os.path.join(BUILD, "kima_%s_%s" % (kind, name))
     if not os.path.exists(exe):
         pytest.fail("%s is missing: build it here with `make -C host` (needs /root/reference)" % exe)
@@ -39,6 +39,7 @@ def run(kind, name, tmp_path, tag, lanes, seed, device, options=OPTIONS):
     env.pop("KIMA_DEVICE_PROPOSALS", None)
     if device:
         env["KIMA_DEVICE_PROPOSALS"] = "1"
+    env.update(extra_env or {})
     r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, capture_output=True, text=True,
                        timeout=900, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
@@ -52,6 +53,11 @@ def test_device_run_is_reproducible_and_keeps_the_file_formats(gpu, tmp_path):
     h = run("gpu", "BL2009", tmp_path, "h", 16, 43, False, small)
     for f in ("sample.txt", "sample_info.txt", "levels.txt"):
         assert (a / f).read_bytes() == (b / f).read_bytes(), f
+    # all_above ordered and cut in HBM (the default in one process) or gathered and selected on the host:
+    # the same levels, hence the same chain
+    c = run("gpu", "BL2009", tmp_path, "c", 16, 43, True, small, {"KIMA_HOST_ABOVE": "1"})
+    for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
+        assert (a / f).read_bytes() == (c / f).read_bytes(), f
     ha, ra = load_sample(a / "sample.txt")
     hh, rh = load_sample(h / "sample.txt")
     assert ha == hh and ra.shape == rh.shape       # same columns, same number of saves

@@ -220,3 +220,43 @@ def test_many_barriers_on_device_match_reference(gpu, ref):
             cnt = cnt + want["counters"]
             state = want
         ds.close()
+
+
+def test_above_pool_in_hbm_orders_and_cuts_like_the_host(gpu, ref):
+    """kc_sampler_collect_pool / kc_sampler_pool_select against numpy on the lists kc_sampler_collect
+    returns: append in lane order over two barriers, lexicographic (value, tiebreaker) order with ties
+    (a particle that stays above the top level is listed again every step), cut at `index`."""
+    flags, data, pri = _setup(ref, "white")
+    T, P, steps = 512, 1, 30
+    S, nps, L = make_state(flags, data, pri, T, seed=5)
+    logl, _ = ref.oracle.eval_batch(S[:L["n_rows"]], nps, nthreads=8)
+    logl = np.where(np.isfinite(logl), logl, -1e300)
+    tb = np.random.default_rng(3).uniform(0.01, 0.99, T)
+    lv_logl, lv_tb, lv_logX, cnt = make_levels(logl, 3)
+    with LikelihoodEngine(data, flags, T) as eng:
+        ds = DeviceSampler(eng, pri, SamplerOptions(lanes=T, num_particles=P, thread_steps=steps, max_levels=16,
+                                                    pool_reserve=1000))
+        ds.upload(S, nps, logl, tb, np.zeros(T, np.int32))
+        want = []
+        for barrier in range(2):
+            ds.set_levels(lv_logl, lv_tb, lv_logX, cnt[:, 1], False, False)
+            ds.run(steps)
+            c1, above = ds.collect()
+            c2, n_new, n_pool = ds.collect_pool()
+            np.testing.assert_array_equal(c1, c2)
+            want.append(above)
+            assert n_new == len(above) and n_pool == sum(len(a) for a in want)
+        allp = np.concatenate(want)
+        np.testing.assert_array_equal(ds.pool_fetch(len(allp) + 5), allp)
+        assert len(np.unique(allp, axis=0)) < len(allp)  # ties are in
+        order = np.lexsort((allp[:, 1], allp[:, 0]))
+        srt = allp[order]
+        index = int((1.0 - 1.0 / np.e) * len(allp))
+        v, t, left = ds.pool_select(index)
+        assert (v, t) == (srt[index, 0], srt[index, 1]) and left == len(allp) - index - 1
+        np.testing.assert_array_equal(ds.pool_fetch(len(allp)), srt[index + 1:])
+        v2, t2, left2 = ds.pool_select(0)
+        assert (v2, t2) == (srt[index + 1, 0], srt[index + 1, 1]) and left2 == left - 1
+        ds.pool_clear()
+        assert len(ds.pool_fetch(10)) == 0
+        ds.close()
