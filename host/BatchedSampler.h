@@ -516,6 +516,7 @@ class BatchedSampler : public Sampler<ModelType> {
     // false = the model has a prior without a device counterpart: the caller runs host proposals
     bool run_device()
     {
+        const double t_begin = now();
         const unsigned int T = this->num_threads, P = this->options.num_particles;
         const int W = world();
         if (T % (unsigned int)W != 0)
@@ -555,6 +556,7 @@ class BatchedSampler : public Sampler<ModelType> {
         std::vector<uint64_t> lv_tries, counters;
         std::vector<int> counts(W);
         double t_dev = 0, t_book = 0, t_xfer = 0, t_fold = 0;
+        const double t_loop0 = now();
         while (true) {
             const size_t L = this->levels.size();
             lv_logl.resize(L); lv_tb.resize(L); lv_logX.resize(L); lv_tries.resize(L); counters.resize(4 * L);
@@ -632,6 +634,10 @@ class BatchedSampler : public Sampler<ModelType> {
             bookkeeping_device();
             t_book += now() - t2;
         }
+        const double t_loop1 = now();
+        if (std::getenv("KIMA_PROFILE"))
+            std::cerr << "# sampling loop " << t_loop1 - t_loop0 << " s (particles to HBM before it: " << t_loop0 - t_begin
+                      << " s)" << std::endl;
         if (std::getenv("KIMA_PROFILE"))
             std::cerr << "# device proposals: steps + collect " << t_dev << " s, particle arrays back / exchange " << t_xfer
                       << " s, folding counters / above / likelihoods in " << t_fold << " s, bookkeeping " << t_book << " s"

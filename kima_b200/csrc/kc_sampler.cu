@@ -49,7 +49,7 @@ struct SamplerState {
     double* d_above_compact = nullptr;
     uint64_t* h_cnt_sum = nullptr;   // pinned
     int32_t* h_total = nullptr;      // pinned
-    double* h_above = nullptr;       // pinned, [T * max_steps * 2]
+    double* h_above = nullptr;       // pinned, [T * max_steps * 2], allocated by the first kc_sampler_collect that returns pairs
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the last kc_sampler_run
     // `all_above` in HBM: values and tiebreakers (SoA), ping-pong buffers for the ordered cut
     double *pool_v[2] = {nullptr, nullptr}, *pool_t[2] = {nullptr, nullptr};
@@ -379,7 +379,6 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     CU(cudaMemcpy(s->d_pri, priors, sizeof(kc_prior_table), cudaMemcpyHostToDevice));
     CU(cudaMallocHost(&s->h_cnt_sum, sizeof(uint64_t) * 4 * sp.Lcap));
     CU(cudaMallocHost(&s->h_total, sizeof(int32_t)));
-    CU(cudaMallocHost(&s->h_above, sizeof(double) * (size_t)T * sp.max_steps * 2));
     CU(cudaEventCreate(&s->ev0));
     CU(cudaEventCreate(&s->ev1));
     if (cfg->pool_reserve > 0) {
@@ -603,6 +602,8 @@ int kc_sampler_collect(kc_ctx* c, uint64_t* counters, double* above_pairs, int m
         total = *s->h_total;
         const int take = total < max_pairs ? total : max_pairs;
         if (above_pairs && take > 0) {
+            // pinned staging for the pairs: only runs that keep all_above on the host pay for it
+            if (!s->h_above) CU(cudaMallocHost(&s->h_above, sizeof(double) * (size_t)T * sp.max_steps * 2));
             CU(cudaMemcpyAsync(s->h_above, s->d_above_compact, sizeof(double) * 2 * take, cudaMemcpyDeviceToHost, c->stream));
             CU(cudaStreamSynchronize(c->stream));
             std::memcpy(above_pairs, s->h_above, sizeof(double) * 2 * take);

@@ -11,3 +11,5 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_r
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
    --log-file $OUT/launches_sampler.csv python tools/dev_sampler_prof.py 65536 20 1 > $OUT/ncu_list_sampler.log 2>&1
 tail -5 $OUT/pytest_gpu.log; tail -8 $OUT/smoke.log; cat $OUT/bench.json | head -c 3000
+timeout 300 python tools/dev_devprop_bench2.py > $OUT/devprop_e2e.jsonl 2> $OUT/devprop_e2e.err
+cat $OUT/devprop_e2e.jsonl

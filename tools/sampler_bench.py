@@ -33,6 +33,13 @@ OPTIONS = """# DNest4 options for the throughput run
 """
 
 
+def _loop_seconds(stderr):
+    for l in stderr.splitlines():
+        if l.startswith("# sampling loop "):
+            return float(l.split()[3])
+    return None
+
+
 def _run_seconds(stderr):
     for l in stderr.splitlines():
         if l.startswith("# run() "):
@@ -67,6 +74,11 @@ def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=120
             # the sampling loop alone (Sampler::run), without process start, CUDA context and
             # the prior draws: what a long run converges to
             extra = {"run_s": run_s, "steps_per_s_run": steps / run_s}
+        loop_s = _loop_seconds(r.stderr)
+        if loop_s:
+            # device proposals: barriers only (steps on the GPU + bookkeeping), without the one-off upload
+            # of the particles before and the sampler_state.txt of all particles after
+            extra.update({"loop_s": loop_s, "steps_per_s_loop": steps / loop_s})
         return {"kind": kind, "example": name, "profile": prof[-1] if prof else None, **extra, "threads": threads, "thread_steps": thread_steps, "saves": saves,
                 "mcmc_steps": steps, "wall_s": wall, "steps_per_s": steps / wall}
     finally:
