@@ -532,7 +532,8 @@ class BatchedSampler : public Sampler<ModelType> {
         cfg.beta = this->options.beta;
         cfg.seed = seed0;
         cfg.lane0 = (int32_t)lane_lo();  // lane k of the run draws from stream seed + k whatever rank steps it
-        pool_mode = (W == 1) && !(std::getenv("KIMA_HOST_ABOVE") && std::atoi(std::getenv("KIMA_HOST_ABOVE")));
+        // all_above lives in HBM (with several ranks: replicated, the ranks' lists exchanged GPU to GPU)
+        pool_mode = !(std::getenv("KIMA_HOST_ABOVE") && std::atoi(std::getenv("KIMA_HOST_ABOVE")));
         pool_n = 0;
         cfg.pool_reserve = pool_mode ? (int32_t)this->options.new_level_interval : 0;
         const std::string bad = evaluator->sampler_create(this->particles[0], cfg);
@@ -551,7 +552,8 @@ class BatchedSampler : public Sampler<ModelType> {
         evaluator->sampler_upload(this->particles, p0, p1, logl, tb, level);
         kimacuda::Context& ctx = evaluator->sampler_ctx();
         const int max_local = (int)(Tl * this->options.thread_steps), max_pairs = max_local * W;
-        std::vector<double> above(pool_mode ? 0 : 2 * (size_t)max_pairs), above_local(W > 1 ? 2 * (size_t)max_local : 0);
+        std::vector<double> above(pool_mode ? 0 : 2 * (size_t)max_pairs),
+            above_local(W > 1 && !pool_mode ? 2 * (size_t)max_local : 0);
         std::vector<double> lv_logl, lv_tb, lv_logX, xs(W > 1 ? 3 * nl : 0), xr(W > 1 ? 3 * n : 0);
         std::vector<uint64_t> lv_tries, counters;
         std::vector<int> counts(W);
@@ -585,11 +587,13 @@ class BatchedSampler : public Sampler<ModelType> {
             if (W > 1) {
                 // the barrier between processes (SamplerImpl.h:306-329): counters summed, `above` lists
                 // concatenated in rank (= lane) order, likelihoods and level assignments to everybody
-                evaluator->allreduce_levels(counters.data(), (int)counters.size());
-                evaluator->allgather_above(above_local.data(), std::min(n_above, max_local), above.data(), max_pairs,
-                                           counts.data());
-                n_above = 0;
-                for (int c : counts) n_above += c;
+                if (!pool_mode) {  // (with the pool, kc_sampler_collect_pool has done both between the GPUs)
+                    evaluator->allreduce_levels(counters.data(), (int)counters.size());
+                    evaluator->allgather_above(above_local.data(), std::min(n_above, max_local), above.data(), max_pairs,
+                                               counts.data());
+                    n_above = 0;
+                    for (int c : counts) n_above += c;
+                }
                 for (size_t i = 0; i < nl; ++i) {
                     xs[3 * i] = logl[p0 + i];
                     xs[3 * i + 1] = tb[p0 + i];

@@ -155,7 +155,7 @@ int kc_sampler_run(kc_ctx* ctx, int steps);
 int kc_sampler_collect(kc_ctx* ctx, uint64_t* counters, double* above_pairs, int max_pairs,
                        int* n_above);
 
-/* ---- `all_above` kept in HBM (one process per run) -----------------------------------------
+/* ---- `all_above` kept in HBM ----------------------------------------------------------------
  * Sampler::all_above (Sampler.h:59; SamplerImpl.h:324-329, 384-399) grows by up to lanes x
  * thread_steps (value, tiebreaker) pairs per barrier and is only ever (a) counted, (b) ordered to
  * place a new level at position `index` and cut at that position, (c) cleared.  With tens of
@@ -163,6 +163,11 @@ int kc_sampler_collect(kc_ctx* ctx, uint64_t* counters, double* above_pairs, int
  * points keep it on the device.
  * kc_sampler_collect_pool: kc_sampler_collect with the lanes' `above` lists appended to the pool
  * instead of returned; *n_new = pairs appended, *n_pool = pool size afterwards.
+ * On a context with a communicator (kc_comm_init before kc_sampler_create) it is a collective:
+ * the counters come back summed over the ranks and every rank's pool receives the lists of all
+ * ranks in rank order (NCCL all-gather between the GPUs), so the pools stay equal and
+ * kc_sampler_pool_select returns the same pair on every rank — the host-side
+ * kc_allreduce_levels / kc_allgather_above are not needed then.
  * kc_sampler_pool_select: orders the pool by (value, tiebreaker) (LikelihoodType::operator<),
  * returns the element at position `index` and keeps the elements after it — do_bookkeeping's
  * sort + levels.push_back(all_above[index]) + erase(begin, begin + index + 1).

@@ -81,6 +81,30 @@ int ensure_buf(kc::CommView& v, size_t bytes)
 
 }  // namespace
 
+// Collectives on buffers that already sit in HBM, enqueued on the context's stream (kc_sampler.cu: the
+// `above` lists and the level counters meet on the GPUs, SamplerImpl.h:306-329, without touching the hosts).
+namespace kc {
+int comm_ranks(kc_ctx* c)
+{
+    CommView v = comm_view(c);
+    return *v.nccl_comm ? *v.nranks : 1;
+}
+int comm_allgather_dev(kc_ctx* c, const void* d_send, void* d_recv, size_t nbytes)
+{
+    CommView v = comm_view(c);
+    if (!*v.nccl_comm) return comm_fail(KC_ERR_ARG, "kc_comm_init has not been called");
+    NC(g_nccl.AllGather(d_send, d_recv, nbytes, ncclChar, (ncclComm_t)*v.nccl_comm, v.stream));
+    return KC_OK;
+}
+int comm_allreduce_u64_dev(kc_ctx* c, uint64_t* d, size_t n)
+{
+    CommView v = comm_view(c);
+    if (!*v.nccl_comm) return comm_fail(KC_ERR_ARG, "kc_comm_init has not been called");
+    NC(g_nccl.AllReduce(d, d, n, ncclUint64, ncclSum, (ncclComm_t)*v.nccl_comm, v.stream));
+    return KC_OK;
+}
+}  // namespace kc
+
 extern "C" {
 
 int kc_comm_unique_id(void* id128)

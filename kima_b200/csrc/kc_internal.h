@@ -99,4 +99,8 @@ struct kc_ctx;
 namespace kc {
 CommView comm_view(kc_ctx* c);                       // kc_api.cu
 int comm_fail(int code, const std::string& msg);     // kc_api.cu
+// kc_comm.cu: device-to-device collectives on the context's stream
+int comm_ranks(kc_ctx* c);  // 1 without a communicator
+int comm_allgather_dev(kc_ctx* c, const void* d_send, void* d_recv, size_t nbytes);
+int comm_allreduce_u64_dev(kc_ctx* c, uint64_t* d, size_t n);
 }  // namespace kc

@@ -58,6 +58,9 @@ struct SamplerState {
     void* pool_tmp = nullptr;
     size_t pool_tmp_bytes = 0, pool_cap = 0, pool_n = 0;
     int pool_cur = 0;
+    int pool_ranks = 1;                // processes whose lists meet in the pool (the communicator's size at creation)
+    int32_t* d_rank_counts = nullptr;  // [pool_ranks]
+    int32_t* h_rank_counts = nullptr;  // pinned
     double* h_pivot = nullptr;  // pinned, 2 doubles
     bool timed = false;
     std::vector<void*> allocs;
@@ -152,6 +155,21 @@ __global__ void smp_gather_pool_kernel(SamplerParams sp, const int32_t* offsets,
     for (int i = 0; i < n; i++) {
         pv[o + i] = a[2 * i];
         pt[o + i] = a[2 * i + 1];
+    }
+}
+// the ranks' staged lists (rank r: values at recv[r*2M .. +counts[r]), tiebreakers M further) appended to
+// the pool in rank order = the order in which one process would have concatenated its threads' lists
+__global__ void smp_pool_append_ranks_kernel(const double* recv, const int32_t* counts, int R, size_t M, double* pv,
+                                             double* pt, size_t base)
+{
+    const int r = blockIdx.y;
+    size_t o = base;
+    for (int k = 0; k < r; k++) o += (size_t)counts[k];
+    const size_t n = (size_t)counts[r];
+    const double* src = recv + (size_t)r * 2 * M;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        pv[o + i] = src[i];
+        pt[o + i] = src[M + i];
     }
 }
 // order-preserving map double -> uint64 (radix sort key)
@@ -262,6 +280,7 @@ void sampler_free(kc_ctx* c)
     for (void* p : s->allocs) cudaFree(p);
     if (s->h_cnt_sum) cudaFreeHost(s->h_cnt_sum);
     if (s->h_total) cudaFreeHost(s->h_total);
+    if (s->h_rank_counts) cudaFreeHost(s->h_rank_counts);
     if (s->h_above) cudaFreeHost(s->h_above);
     if (s->h_pivot) cudaFreeHost(s->h_pivot);
     if (s->ev0) cudaEventDestroy(s->ev0);
@@ -384,7 +403,14 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     if (cfg->pool_reserve > 0) {
         // leftovers of a cut are at most 1/compression of the pool; without a cut the pool stops
         // growing at new_level_interval + one barrier's worth
-        s->pool_cap = (size_t)3 * T * sp.max_steps + (size_t)cfg->pool_reserve;
+        // with a communicator every rank keeps the whole run's pool (the lists of all ranks, in rank order)
+        s->pool_ranks = kc::comm_ranks(c);
+        s->pool_cap = (size_t)3 * T * sp.max_steps * s->pool_ranks + (size_t)cfg->pool_reserve;
+        if (kc::dalloc(s, &s->d_rank_counts, (size_t)s->pool_ranks) != cudaSuccess) {
+            kc::sampler_free(c);
+            return fail(KC_ERR_CUDA, "sampler allocation (rank counts)");
+        }
+        CU(cudaMallocHost(&s->h_rank_counts, sizeof(int32_t) * s->pool_ranks));
         for (int k = 0; k < 2; k++) {
             cudaError_t e1 = kc::dalloc(s, &s->pool_v[k], s->pool_cap), e2 = kc::dalloc(s, &s->pool_t[k], s->pool_cap);
             cudaError_t e3 = kc::dalloc(s, &s->pool_key[k], s->pool_cap), e4 = kc::dalloc(s, &s->pool_idx[k], s->pool_cap);
@@ -629,22 +655,51 @@ int kc_sampler_collect_pool(kc_ctx* c, uint64_t* counters, int64_t* n_new, int64
     const int L = sp.n_levels, T = sp.lanes;
     if (counters) {
         kc::smp_reduce_counters_kernel<<<dim3(L, 4), 256, 0, c->stream>>>(sp, s->d_cnt_sum);
-        CU(cudaMemcpyAsync(s->h_cnt_sum, s->d_cnt_sum, sizeof(uint64_t) * 4 * L, cudaMemcpyDeviceToHost, c->stream));
         c->launches += 1;
     }
-    kc::smp_scan_above_kernel<<<1, 1024, 0, c->stream>>>(sp.n_above, T, s->d_offsets);
-    CU(cudaMemcpyAsync(s->h_total, s->d_offsets + T, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-    // capacity is checked before the append lands: one barrier adds at most T * max_steps
-    if (s->pool_n + (size_t)T * sp.max_steps > s->pool_cap)
+    const int R = s->pool_ranks;
+    const size_t M = (size_t)T * sp.max_steps;
+    // capacity is checked before the append lands: one barrier adds at most R * T * max_steps
+    if (s->pool_n + M * R > s->pool_cap)
         return fail(KC_ERR_ARG, "above pool full: place a level (kc_sampler_pool_select) or clear it");
-    kc::smp_gather_pool_kernel<<<(T + 127) / 128, 128, 0, c->stream>>>(sp, s->d_offsets, s->pool_v[s->pool_cur],
-                                                                      s->pool_t[s->pool_cur], s->pool_n);
-    c->launches += 2;
-    CU(cudaStreamSynchronize(c->stream));
-    CU(cudaGetLastError());
-    s->pool_n += (size_t)*s->h_total;
+    if (counters && R > 1) {
+        int e = kc::comm_allreduce_u64_dev(c, s->d_cnt_sum, (size_t)4 * L);  // every rank folds the same sums in
+        if (e) return e;
+    }
+    if (counters)
+        CU(cudaMemcpyAsync(s->h_cnt_sum, s->d_cnt_sum, sizeof(uint64_t) * 4 * L, cudaMemcpyDeviceToHost, c->stream));
+    kc::smp_scan_above_kernel<<<1, 1024, 0, c->stream>>>(sp.n_above, T, s->d_offsets);
+    size_t added = 0;
+    if (R == 1) {
+        CU(cudaMemcpyAsync(s->h_total, s->d_offsets + T, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        kc::smp_gather_pool_kernel<<<(T + 127) / 128, 128, 0, c->stream>>>(sp, s->d_offsets, s->pool_v[s->pool_cur],
+                                                                          s->pool_t[s->pool_cur], s->pool_n);
+        c->launches += 2;
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaGetLastError());
+        added = (size_t)*s->h_total;
+    } else {
+        // own lists compacted into a staging block (the sort's key arrays are idle between level creations),
+        // every rank's block and count to every GPU over NVLink, appended in rank order: the pools stay equal
+        double* stage = reinterpret_cast<double*>(s->pool_key[1]);  // [2M]: values, then tiebreakers
+        double* recv = reinterpret_cast<double*>(s->pool_key[0]);   // [R][2M]
+        kc::smp_gather_pool_kernel<<<(T + 127) / 128, 128, 0, c->stream>>>(sp, s->d_offsets, stage, stage + M, 0);
+        int e = kc::comm_allgather_dev(c, s->d_offsets + T, s->d_rank_counts, sizeof(int32_t));
+        if (e) return e;
+        e = kc::comm_allgather_dev(c, stage, recv, sizeof(double) * 2 * M);
+        if (e) return e;
+        CU(cudaMemcpyAsync(s->h_rank_counts, s->d_rank_counts, sizeof(int32_t) * R, cudaMemcpyDeviceToHost, c->stream));
+        kc::smp_pool_append_ranks_kernel<<<dim3(296, R), 256, 0, c->stream>>>(recv, s->d_rank_counts, R, M,
+                                                                            s->pool_v[s->pool_cur], s->pool_t[s->pool_cur],
+                                                                            s->pool_n);
+        c->launches += 3;
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaGetLastError());
+        for (int r = 0; r < R; r++) added += (size_t)s->h_rank_counts[r];
+    }
+    s->pool_n += added;
     if (counters) std::memcpy(counters, s->h_cnt_sum, sizeof(uint64_t) * 4 * L);
-    if (n_new) *n_new = *s->h_total;
+    if (n_new) *n_new = (int64_t)added;
     if (n_pool) *n_pool = (int64_t)s->pool_n;
     return KC_OK;
 }

@@ -115,12 +115,15 @@ def test_evidence_at_many_lanes_matches_host_proposals(gpu, tmp_path):
     assert abs(dev.mean() - (-146.0)) < 5.0, z   # the reference's CPU runs give -143.6 ... -147
 
 
-def test_two_ranks_reproduce_the_single_process_device_chain(gpu, tmp_path):
+@pytest.mark.parametrize("host_above", ["0", "1"])
+def test_two_ranks_reproduce_the_single_process_device_chain(gpu, tmp_path, host_above):
     """One process per GPU with device proposals: each rank keeps its lanes' particles in its own
     HBM, lane k draws from stream seed + k whoever steps it, and the barrier (counters summed,
     `above` lists concatenated, likelihoods / level assignments gathered; a lagging particle's
     replacement travels as one column) leaves every rank with the state a single process has:
-    2 ranks x 8 lanes write, byte for byte, the files of 1 process x 16 lanes."""
+    2 ranks x 8 lanes write, byte for byte, the files of 1 process x 16 lanes — with all_above replicated in
+    the GPUs' HBM (lists and counters exchanged device to device by kc_sampler_collect_pool) and with
+    KIMA_HOST_ABOVE=1 (lists meeting on the hosts)."""
     from test_host_cpp import _gpu_count
     if _gpu_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -134,8 +137,8 @@ def test_two_ranks_reproduce_the_single_process_device_chain(gpu, tmp_path):
     (d / "OPTIONS").write_text(opts)
     procs = []
     for r in range(2):
-        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_PORT="29577",
-                   KIMA_DEVICE_PROPOSALS="1")
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_PORT=str(29577 + int(host_above)),
+                   KIMA_DEVICE_PROPOSALS="1", KIMA_HOST_ABOVE=host_above)
         procs.append(subprocess.Popen([exe, "-t", "16", "-s", "43"], cwd=d, env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.PIPE, text=True))
     outs = [p.communicate(timeout=600) for p in procs]
