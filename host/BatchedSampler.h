@@ -82,6 +82,38 @@ class BatchedSampler : public Sampler<ModelType> {
         int nt = (int)std::thread::hardware_concurrency();
         if (const char* e = std::getenv("KIMA_HOST_THREADS")) nt = std::atoi(e);
         pool = std::make_shared<kima_b200::LanePool>(std::max(1, std::min(nt, 64)));
+        evaluator->set_host_pool(pool);
+    }
+
+    // Sampler::print (SamplerImpl.h:590-612) with the particles formatted by all host threads: RVmodel::print
+    // sets its own format flags before the first number (src/RVmodel.cpp:947-948), so a run of particles
+    // prints the same into a stream of its own; what follows them inherits fixed / precision 8 as it does there.
+    void print_state(std::ostream& out)
+    {
+        const size_t n = this->particles.size();
+        if (n < 4096 || std::getenv("KIMA_SERIAL_STATE")) { this->print(out); return; }
+        out << this->save_to_disk << ' ';
+        out << this->num_threads << ' ';
+        out << this->compression << ' ';
+        out << this->options << ' ';
+        const size_t chunk = 2048, nchunks = (n + chunk - 1) / chunk;
+        std::vector<std::string> parts(nchunks);
+        pool->run(0, (int)nchunks, [&](int a, int b) {
+            for (int c = a; c < b; ++c) {
+                std::ostringstream os;
+                const size_t i1 = std::min(n, ((size_t)c + 1) * chunk);
+                for (size_t i = (size_t)c * chunk; i < i1; ++i) this->particles[i].print(os);
+                parts[c] = os.str();
+            }
+        });
+        for (const std::string& s : parts) out << s;
+        out.setf(std::ios::fixed, std::ios::floatfield);
+        out.precision(8);
+        for (const auto& l : this->log_likelihoods) l.print(out);
+        for (const auto& l : this->level_assignments) out << l << ' ';
+        for (const auto& l : this->levels) l.print(out);
+        out << this->count_saves << ' ';
+        out << this->count_mcmc_steps << ' ';
     }
 
     // update_particle up to its likelihood call, for the lanes [k0, k1) of group g:
@@ -549,6 +581,7 @@ class BatchedSampler : public Sampler<ModelType> {
             tb[i] = this->log_likelihoods[i].get_tiebreaker();
             level[i] = (int32_t)this->level_assignments[i];
         }
+        const double t_created = now();
         evaluator->sampler_upload(this->particles, p0, p1, logl, tb, level);
         kimacuda::Context& ctx = evaluator->sampler_ctx();
         const int max_local = (int)(Tl * this->options.thread_steps), max_pairs = max_local * W;
@@ -640,8 +673,9 @@ class BatchedSampler : public Sampler<ModelType> {
         }
         const double t_loop1 = now();
         if (std::getenv("KIMA_PROFILE"))
-            std::cerr << "# sampling loop " << t_loop1 - t_loop0 << " s (particles to HBM before it: " << t_loop0 - t_begin
-                      << " s)" << std::endl;
+            std::cerr << "# sampling loop " << t_loop1 - t_loop0 << " s (before it: sampler state in HBM allocated "
+                      << t_created - t_begin << " s, particles converted and uploaded " << t_loop0 - t_created << " s)"
+                      << std::endl;
         if (std::getenv("KIMA_PROFILE"))
             std::cerr << "# device proposals: steps + collect " << t_dev << " s, particle arrays back / exchange " << t_xfer
                       << " s, folding counters / above / likelihoods in " << t_fold << " s, bookkeeping " << t_book << " s"
@@ -667,11 +701,15 @@ class BatchedSampler : public Sampler<ModelType> {
                 }
             }
         }
+        const double t_state = now();
         if (rank() == 0) {
             std::fstream fout("sampler_state.txt", std::ios::out);
-            this->print(fout);
+            print_state(fout);
             fout.close();
         }
+        if (std::getenv("KIMA_PROFILE"))
+            std::cerr << "# after the loop: particles back to the host " << t_state - t_loop1 << " s, sampler_state.txt "
+                      << now() - t_state << " s" << std::endl;
         return true;
     }
 

@@ -14,11 +14,14 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <functional>
+#include <memory>
 #include <thread>
 #include <iostream>
 #include <limits>
 #include <vector>
 #include "kima_cuda.hpp"
+#include "LanePool.h"
 #include "PriorTable.h"
 
 // the nine model flags every kima_setup.cpp defines (src/RVmodel.h:16-34)
@@ -279,8 +282,10 @@ public:
         const size_t n = i1 - i0;
         std::vector<double> state((size_t)SL.n_state * n, 0.0);
         std::vector<int32_t> np(n);
-        for (size_t i = 0; i < n; i++)
-            model_to_column(particles[i0 + i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
+        for_range(n, [&](size_t a, size_t b) {
+            for (size_t i = a; i < b; i++)
+                model_to_column(particles[i0 + i], ctx_[0]->layout(), SL, ColRef{state.data() + i, n}, np[i]);
+        });
         ctx_[0]->sampler_upload(state.data(), np.data(), logl.data() + i0, tb.data() + i0, level.data() + i0);
     }
     int sampler_state_rows() const { return ctx_[0]->sampler_layout().n_state; }
@@ -309,13 +314,25 @@ public:
                       const std::vector<int32_t>& np)
     {
         const size_t n = np.size();
-        for (size_t i = 0; i < n; i++)
-            column_to_model(particles[i0 + i], ctx_[0]->layout(), ctx_[0]->sampler_layout(),
-                            ColRef{const_cast<double*>(state.data()) + i, n}, np[i]);
+        for_range(n, [&](size_t a, size_t b) {
+            for (size_t i = a; i < b; i++)
+                column_to_model(particles[i0 + i], ctx_[0]->layout(), ctx_[0]->sampler_layout(),
+                                ColRef{const_cast<double*>(state.data()) + i, n}, np[i]);
+        });
     }
+    // the per-particle conversions above are independent: the sampler lends its host threads
+    void set_host_pool(std::shared_ptr<kima_b200::LanePool> p) { host_pool_ = std::move(p); }
     kimacuda::Context& sampler_ctx() { return *ctx_[0]; }
 
 private:
+    std::shared_ptr<kima_b200::LanePool> host_pool_;
+    void for_range(size_t n, const std::function<void(size_t, size_t)>& f)
+    {
+        if (host_pool_ && n >= 1024)
+            host_pool_->run(0, (int)n, [&](int a, int b) { f((size_t)a, (size_t)b); });
+        else
+            f(0, n);
+    }
     // NCCL's unique id travels through a file in the run directory (all ranks of one node
     // share it): rank 0 writes it atomically, the others wait for it.
     void comm_bootstrap()

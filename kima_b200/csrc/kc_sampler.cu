@@ -69,20 +69,28 @@ struct SamplerState {
 namespace {
 
 constexpr int LANE_THREADS = 32;  // lanes per CTA: small CTAs spread a few thousand lanes over all SMs
+// -DKC_SMP_MIN_CTAS=n compiles the step kernels for n resident CTAs per SM (register cap 64K / 32 / n);
+// measured on B200 (profiles/smp_regcap_r01e.txt): 96 / 80 / 64 registers change nothing at 65 536 lanes, where
+// every warp is resident anyway, and gain up to 10 % at 262 144 lanes; the default stays ptxas' own choice.
+#ifdef KC_SMP_MIN_CTAS
+#define KC_SMP_BOUNDS __launch_bounds__(LANE_THREADS, KC_SMP_MIN_CTAS)
+#else
+#define KC_SMP_BOUNDS __launch_bounds__(LANE_THREADS)
+#endif
 
-__global__ void __launch_bounds__(LANE_THREADS) smp_propose_kernel(SamplerParams sp)
+__global__ void KC_SMP_BOUNDS smp_propose_kernel(SamplerParams sp)
 {
     const int lane = blockIdx.x * LANE_THREADS + threadIdx.x;
     if (lane < sp.lanes) smp::step_propose(sp, lane);
 }
-__global__ void __launch_bounds__(LANE_THREADS) smp_accept_kernel(SamplerParams sp)
+__global__ void KC_SMP_BOUNDS smp_accept_kernel(SamplerParams sp)
 {
     const int lane = blockIdx.x * LANE_THREADS + threadIdx.x;
     if (lane < sp.lanes) smp::step_accept(sp, lane);
 }
 // the second half of step i and the first half of step i+1 of a lane in one launch: both touch
 // only the lane's own particles, proposal column, counters and stream
-__global__ void __launch_bounds__(LANE_THREADS) smp_accept_propose_kernel(SamplerParams sp)
+__global__ void KC_SMP_BOUNDS smp_accept_propose_kernel(SamplerParams sp)
 {
     const int lane = blockIdx.x * LANE_THREADS + threadIdx.x;
     if (lane < sp.lanes) {
