@@ -18,6 +18,7 @@
 // step) -> the likelihood kernels of the context over Q -> smp_accept.  kc_sampler_run enqueues
 // `steps` of them back to back on the context stream; nothing returns to the host before the
 // barrier (kc_sampler_collect).
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -97,6 +98,65 @@ __global__ void KC_SMP_BOUNDS smp_accept_propose_kernel(SamplerParams sp)
         smp::step_accept(sp, lane);
         smp::step_propose(sp, lane);
     }
+}
+
+// Many lanes: CTAs of B lanes that sort their lanes by the move they are about to make (smp::Move, decided
+// by the first draws of the proposal) between the two halves of the proposal, so that the threads of a warp
+// run one branch of RVmodel::perturb instead of up to 32.  A lane's state is addressed by its index, so any
+// thread of the CTA can finish it; which thread does is the only thing the (unordered) counting sort decides.
+template <int B, bool ACCEPT>
+__global__ void __launch_bounds__(B) smp_sorted_propose_kernel(SamplerParams sp)
+{
+    __shared__ int count[smp::MV_COUNT + 1], cursor[smp::MV_COUNT + 1];
+    __shared__ unsigned short perm[B];
+    __shared__ unsigned char moves[B];
+    const int tid = threadIdx.x, lane = blockIdx.x * B + tid;
+    if (tid <= smp::MV_COUNT) count[tid] = 0;
+    __syncthreads();
+    int move = smp::MV_COUNT;  // past the end: sorts behind the live lanes
+    if (lane < sp.lanes) {
+        if (ACCEPT) smp::step_accept(sp, lane);
+        move = smp::step_propose_begin(sp, lane);
+    }
+    moves[tid] = (unsigned char)move;
+    atomicAdd(&count[move], 1);
+    __syncthreads();
+    if (tid == 0) {
+        int o = 0;
+        for (int k = 0; k <= smp::MV_COUNT; k++) { cursor[k] = o; o += count[k]; }
+    }
+    __syncthreads();
+    perm[atomicAdd(&cursor[move], 1)] = (unsigned short)tid;
+    __syncthreads();  // also orders the lanes' global writes of the first half before the second half reads them
+    const int t2 = perm[tid], lane2 = blockIdx.x * B + t2;
+    if (lane2 < sp.lanes) smp::step_propose_finish(sp, lane2, moves[t2]);
+}
+
+// CTA size of the move-sorted kernels for this many lanes; KC_SMP_BLOCK (0, 64, 128, 256) overrides
+int sort_block(const SamplerParams& sp)
+{
+    if (const char* e = std::getenv("KC_SMP_BLOCK")) {
+        const int b = std::atoi(e);
+        return (b == 64 || b == 128 || b == 256) ? b : 0;
+    }
+    // measured (profiles/smp_sorted_r01e.txt, 51Peg shape): the step kernel 0.158 -> 0.070 ms at 65 536 lanes and
+    // 0.65 -> 0.30 ms at 262 144 with B = 256 (128: 0.090, 64: 0.092); 0.078 -> 0.061 ms at 16 384
+    return sp.lanes >= 8192 ? 256 : 0;
+}
+template <bool ACCEPT>
+void launch_propose_t(const SamplerParams& sp, int B, int grid32, cudaStream_t st)
+{
+    const int g = B ? (sp.lanes + B - 1) / B : grid32;
+    if (B == 256) smp_sorted_propose_kernel<256, ACCEPT><<<g, 256, 0, st>>>(sp);
+    else if (B == 128) smp_sorted_propose_kernel<128, ACCEPT><<<g, 128, 0, st>>>(sp);
+    else if (B == 64) smp_sorted_propose_kernel<64, ACCEPT><<<g, 64, 0, st>>>(sp);
+    else if (ACCEPT) smp_accept_propose_kernel<<<grid32, LANE_THREADS, 0, st>>>(sp);
+    else smp_propose_kernel<<<grid32, LANE_THREADS, 0, st>>>(sp);
+}
+void launch_propose(const SamplerParams& sp, int B, bool accept, int grid32, cudaStream_t st)
+{
+    if (accept) launch_propose_t<true>(sp, B, grid32, st);
+    else launch_propose_t<false>(sp, B, grid32, st);
 }
 
 // sum over lanes of one (counter, level) row of cnt: one CTA per row, coalesced
@@ -585,12 +645,13 @@ int kc_sampler_run(kc_ctx* c, int steps)
     CU(cudaSetDevice(c->device));
     const int grid = kc::lane_grid(sp);
     CU(cudaEventRecord(s->ev0, c->stream));
-    kc::smp_propose_kernel<<<grid, kc::LANE_THREADS, 0, c->stream>>>(sp);
+    const int B = kc::sort_block(sp);  // 0: too few lanes to fill the SMs with larger CTAs, one warp per CTA
+    kc::launch_propose(sp, B, false, grid, c->stream);
     c->launches += 1;
     for (int i = 0; i < steps; i++) {
         rc = kc::run_kernels(c, sp.lanes, const_cast<double*>(sp.logl_q), sp.Q, sp.npq);
         if (rc) return rc;
-        if (i + 1 < steps) kc::smp_accept_propose_kernel<<<grid, kc::LANE_THREADS, 0, c->stream>>>(sp);
+        if (i + 1 < steps) kc::launch_propose(sp, B, true, grid, c->stream);
         else kc::smp_accept_kernel<<<grid, kc::LANE_THREADS, 0, c->stream>>>(sp);
         c->launches += 1;
     }

@@ -560,17 +560,29 @@ KS_FN double cond_perturb2(const SamplerParams& sp, const Col& q, int np, Rng& r
 }
 
 // RJObject::perturb, :143-193 (prior_type uniform, hyperparameters = true as kima calls it)
-KS_FN double planets_perturb(const SamplerParams& sp, const Col& q, int& np, Rng& rng)
+// The move a proposal makes is decided by the first draws of RVmodel::perturb and RJObject::perturb; the
+// kernels sort the lanes of a CTA by it before doing the work, so that the threads of a warp run the
+// same branch.  move_choose consumes exactly those selection draws, in the reference's order; move_apply
+// continues on the same stream.
+enum Move : int {
+    MV_NONE = 0,        // npmax == 0: RJObject::perturb returns at once
+    MV_NUM_COMPONENTS,  // RJObjectImpl.h:180-181 (birth / death)
+    MV_COND1,           // :185-186 conditional prior's perturb1
+    MV_COND2,           // :187-188 perturb2
+    MV_COMPONENTS,      // :191
+    MV_ETA1, MV_ETA2, MV_ETA3, MV_ETA4,
+    MV_SIGMA_MA, MV_TAU_MA,
+    MV_JITTER,          // jitters (+ nu, known objects)
+    MV_BACKGROUND,
+    MV_COUNT
+};
+KS_FN int planets_choose(const SamplerParams& sp, Rng& rng)
 {
-    if (sp.L.npmax == 0) return 0.;
-    double logH = 0.;
+    if (sp.L.npmax == 0) return MV_NONE;
     const int which = sp.pri->fix ? (1 + rng.rand_int(2)) : rng.rand_int(3);
-    if (which == 0) logH += perturb_num_components(sp, q, np, rng);
-    else if (which == 1) {
-        if (rng.rand() <= 0.5) logH += cond_perturb1(sp, q, np, rng);
-        else logH += cond_perturb2(sp, q, np, rng);
-    } else logH += perturb_components(sp, q, np, rng);
-    return logH;
+    if (which == 0) return MV_NUM_COMPONENTS;
+    if (which == 1) return rng.rand() <= 0.5 ? MV_COND1 : MV_COND2;
+    return MV_COMPONENTS;
 }
 
 // ---- RVmodel::perturb, src/RVmodel.cpp:435-820 ----------------------------------------------------
@@ -612,48 +624,67 @@ KS_FN void perturb_log_of(const kc_prior& pr, double& x, Rng& rng)  // log_eta =
     x = exp(lx);
 }
 
+KS_FN int move_choose(const SamplerParams& sp, Rng& rng)
+{
+    if (sp.F.GP) {
+        if (rng.rand() <= 0.5) return planets_choose(sp, rng);
+        if (rng.rand() <= 0.5) {
+            if (sp.F.kernel == 0) {  // standard, :458-487
+                if (rng.rand() <= 0.25) return MV_ETA1;
+                if (rng.rand() <= 0.33330) return MV_ETA2;
+                if (rng.rand() <= 0.5) return MV_ETA3;
+                return MV_ETA4;
+            }
+            // celerite, :489-509
+            if (rng.rand() <= 0.33330) return MV_ETA1;
+            if (rng.rand() <= 0.5) return MV_ETA2;
+            return MV_ETA3;
+        }
+        return rng.rand() <= 0.5 ? MV_JITTER : MV_BACKGROUND;
+    }
+    if (sp.F.MA) {
+        if (rng.rand() <= 0.5) return planets_choose(sp, rng);
+        if (rng.rand() <= 0.5) return rng.rand() <= 0.5 ? MV_SIGMA_MA : MV_TAU_MA;
+        return rng.rand() <= 0.5 ? MV_JITTER : MV_BACKGROUND;
+    }
+    if (rng.rand() <= 0.75) return planets_choose(sp, rng);
+    return rng.rand() <= 0.5 ? MV_JITTER : MV_BACKGROUND;
+}
+KS_FN double move_apply(const SamplerParams& sp, int move, const Col& q, int& np, Rng& rng)
+{
+    const int e = sp.L.row_eta;
+    switch (move) {
+    case MV_NUM_COMPONENTS: return perturb_num_components(sp, q, np, rng);
+    case MV_COND1: return cond_perturb1(sp, q, np, rng);
+    case MV_COND2: return cond_perturb2(sp, q, np, rng);
+    case MV_COMPONENTS: return perturb_components(sp, q, np, rng);
+    case MV_ETA1: perturb_log_of(sp.pri->log_eta1_prior, q(e + 0), rng); break;
+    case MV_ETA2: prior_perturb(sp.pri->eta2_prior, q(e + 1), rng); break;
+    case MV_ETA3: prior_perturb(sp.pri->eta3_prior, q(e + 2), rng); break;
+    case MV_ETA4: perturb_log_of(sp.pri->log_eta4_prior, q(e + 3), rng); break;
+    case MV_SIGMA_MA: prior_perturb(sp.pri->sigmaMA_prior, q(sp.L.row_MA + 0), rng); break;
+    case MV_TAU_MA: prior_perturb(sp.pri->tauMA_prior, q(sp.L.row_MA + 1), rng); break;
+    case MV_JITTER:
+        perturb_jitters(sp, q, rng);
+        // the white-noise branch moves nu and the known objects with the jitters, the GP branch the known
+        // objects only, the MA branch neither (the three branches of RVmodel::perturb)
+        if (!sp.F.GP && !sp.F.MA && sp.F.studentt) prior_perturb(sp.pri->nu_prior, q(sp.L.row_nu), rng);
+        if (!sp.F.MA && sp.F.known_object) perturb_known_objects(sp, q, rng);
+        break;
+    case MV_BACKGROUND: perturb_background(sp, q, rng, sp.F.GP || sp.F.MA); break;
+    default: break;
+    }
+    return 0.;
+}
 KS_FN double perturb_model(const SamplerParams& sp, const Col& q, int& np, Rng& rng)
 {
-    double logH = 0.;
-    if (sp.F.GP) {
-        if (rng.rand() <= 0.5) logH += planets_perturb(sp, q, np, rng);
-        else if (rng.rand() <= 0.5) {
-            const int e = sp.L.row_eta;
-            if (sp.F.kernel == 0) {  // standard, :458-487
-                if (rng.rand() <= 0.25) perturb_log_of(sp.pri->log_eta1_prior, q(e + 0), rng);
-                else if (rng.rand() <= 0.33330) prior_perturb(sp.pri->eta2_prior, q(e + 1), rng);
-                else if (rng.rand() <= 0.5) prior_perturb(sp.pri->eta3_prior, q(e + 2), rng);
-                else perturb_log_of(sp.pri->log_eta4_prior, q(e + 3), rng);
-            } else {  // celerite, :489-509
-                if (rng.rand() <= 0.33330) perturb_log_of(sp.pri->log_eta1_prior, q(e + 0), rng);
-                else if (rng.rand() <= 0.5) prior_perturb(sp.pri->eta2_prior, q(e + 1), rng);
-                else prior_perturb(sp.pri->eta3_prior, q(e + 2), rng);
-            }
-        } else if (rng.rand() <= 0.5) {
-            perturb_jitters(sp, q, rng);
-            if (sp.F.known_object) perturb_known_objects(sp, q, rng);
-        } else perturb_background(sp, q, rng, true);
-    } else if (sp.F.MA) {
-        if (rng.rand() <= 0.5) logH += planets_perturb(sp, q, np, rng);
-        else if (rng.rand() <= 0.5) {
-            if (rng.rand() <= 0.5) prior_perturb(sp.pri->sigmaMA_prior, q(sp.L.row_MA + 0), rng);
-            else prior_perturb(sp.pri->tauMA_prior, q(sp.L.row_MA + 1), rng);
-        } else if (rng.rand() <= 0.5) perturb_jitters(sp, q, rng);
-        else perturb_background(sp, q, rng, true);
-    } else {
-        if (rng.rand() <= 0.75) logH += planets_perturb(sp, q, np, rng);
-        else if (rng.rand() <= 0.5) {
-            perturb_jitters(sp, q, rng);
-            if (sp.F.studentt) prior_perturb(sp.pri->nu_prior, q(sp.L.row_nu), rng);
-            if (sp.F.known_object) perturb_known_objects(sp, q, rng);
-        } else perturb_background(sp, q, rng, false);
-    }
-    return logH;
+    const int move = move_choose(sp, rng);
+    return move_apply(sp, move, q, np, rng);
 }
 
 // ---- one MCMC step of a lane, split around the likelihood ---------------------------------------
 // mcmc_thread :146-158 + update_particle :168-190 up to the likelihood call
-KS_FN void step_propose(const SamplerParams& sp, int lane)
+KS_FN int step_propose_begin(const SamplerParams& sp, int lane)
 {
     Rng rng{sp.key0 + (uint64_t)lane, sp.ctr[lane]};
     const int which = lane * sp.P + rng.rand_int(sp.P);
@@ -662,14 +693,30 @@ KS_FN void step_propose(const SamplerParams& sp, int lane)
     const Col q{sp.Q + lane, sp.ldq};
     const double* s = sp.S + which;
     for (int r = 0; r < sp.SL.n_state; r++) q(r) = s[(size_t)r * sp.ldp];
-    int np = sp.np[which];
-    double log_H = perturb_model(sp, q, np, rng);
+    sp.npq[lane] = sp.np[which];
+    const int move = move_choose(sp, rng);
+    sp.which[lane] = which;
+    sp.flags[lane] = particle_first ? 1 : 0;
+    sp.ctr[lane] = rng.ctr;
+    return move;
+}
+// the move itself, the prior-ratio test (:186-190); any thread of the CTA may finish a lane
+KS_FN void step_propose_finish(const SamplerParams& sp, int lane, int move)
+{
+    Rng rng{sp.key0 + (uint64_t)lane, sp.ctr[lane]};
+    const Col q{sp.Q + lane, sp.ldq};
+    int np = sp.npq[lane];
+    double log_H = move_apply(sp, move, q, np, rng);
     sp.npq[lane] = np;
     if (log_H > 0.0) log_H = 0.0;
     const bool scored = rng.rand() <= exp(log_H);
-    sp.which[lane] = which;
-    sp.flags[lane] = (particle_first ? 1 : 0) | (scored ? 2 : 0);
+    sp.flags[lane] |= scored ? 2 : 0;
     sp.ctr[lane] = rng.ctr;
+}
+KS_FN void step_propose(const SamplerParams& sp, int lane)
+{
+    const int move = step_propose_begin(sp, lane);
+    step_propose_finish(sp, lane, move);
 }
 
 // update_particle :191-221, then the level assignment and the `above` list (mcmc_thread :153-163)
