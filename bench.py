@@ -297,7 +297,7 @@ def sampler_device_leg(local: int, lanes: int = 65536, steps: int = 50, reps: in
             "8 levels, blocks of %d lock-step steps" % (lanes, steps), "value": lanes * steps / best * 1e3,
             "ms_per_step": best / steps, "likelihood_kernel_ms_per_step": lk, "gpu_launches": launches,
             "accept_rate": float(cnt[:, 0].sum() / max(1, cnt[:, 1].sum())),
-            "kernels": "smp_accept_propose_kernel + keplerian kernel per step (profiles/launches_sampler_r01e_summary.txt)"}
+            "kernels": "smp_sorted_propose_kernel<256> (accept of step i + move-sorted proposal of step i+1) + keplerian kernel per step (profiles/launches_sampler_r01e_summary.txt)"}
 
 
 def main():

@@ -18,6 +18,8 @@
 // step) -> the likelihood kernels of the context over Q -> smp_accept.  kc_sampler_run enqueues
 // `steps` of them back to back on the context stream; nothing returns to the host before the
 // barrier (kc_sampler_collect).
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -433,6 +435,7 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
         cudaError_t e_ = kc::dalloc(s, &(ptr), (count));                         \
         if (e_ != cudaSuccess) { kc::sampler_free(c); return fail_cuda(e_, "sampler allocation"); } \
     } while (0)
+    const auto t_0 = std::chrono::steady_clock::now();
     DA(s->d_pri, 1);
     DA(sp.S, (size_t)sp.SL.n_state * sp.ldp);
     DA(sp.np, sp.ldp);
@@ -468,6 +471,7 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     CU(cudaMallocHost(&s->h_total, sizeof(int32_t)));
     CU(cudaEventCreate(&s->ev0));
     CU(cudaEventCreate(&s->ev1));
+    const auto t_1 = std::chrono::steady_clock::now();
     if (cfg->pool_reserve > 0) {
         // leftovers of a cut are at most 1/compression of the pool; without a cut the pool stops
         // growing at new_level_interval + one barrier's worth
@@ -498,7 +502,17 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     // the perturb call tree keeps its component vectors on the local stack
     size_t stack = 0;
     CU(cudaDeviceGetLimit(&stack, cudaLimitStackSize));
+    const auto t_2 = std::chrono::steady_clock::now();
     if (stack < 4096) CU(cudaDeviceSetLimit(cudaLimitStackSize, 4096));
+    if (std::getenv("KIMA_PROFILE")) {
+        CU(cudaDeviceSynchronize());
+        const auto t_3 = std::chrono::steady_clock::now();
+        auto sec = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+            return std::chrono::duration<double>(b - a).count();
+        };
+        fprintf(stderr, "# kc_sampler_create: state arrays %.4f s, above pool + sort scratch %.4f s, stack limit %.4f s\n",
+                sec(t_0, t_1), sec(t_1, t_2), sec(t_2, t_3));
+    }
     return KC_OK;
 }
 

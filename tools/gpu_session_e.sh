@@ -13,3 +13,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 tail -5 $OUT/pytest_gpu.log; tail -8 $OUT/smoke.log; cat $OUT/bench.json | head -c 3000
 timeout 300 python tools/dev_devprop_bench2.py > $OUT/devprop_e2e.jsonl 2> $OUT/devprop_e2e.err
 cat $OUT/devprop_e2e.jsonl
+for lanes in 4096 16384 65536 262144; do timeout 300 python tools/dev_sampler_prof.py $lanes 50 3; done > $OUT/dev_sampler_timings.jsonl 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:smp_sorted_propose -c 1 -s 20 \
+   -o $OUT/smp_full -f python tools/dev_sampler_prof.py 65536 30 1 > $OUT/ncu_smp.log 2>&1
+tail -2 $OUT/ncu_smp.log

@@ -79,7 +79,7 @@ def run(kind, name, threads, thread_steps, saves, seed=43, env=None, timeout=120
             # device proposals: barriers only (steps on the GPU + bookkeeping), without the one-off upload
             # of the particles before and the sampler_state.txt of all particles after
             extra.update({"loop_s": loop_s, "steps_per_s_loop": steps / loop_s})
-            extra["one_off"] = [l for l in r.stderr.splitlines() if l.startswith("# sampling loop") or l.startswith("# after the loop")]
+            extra["one_off"] = [l for l in r.stderr.splitlines() if l.startswith(("# sampling loop", "# after the loop", "# kc_sampler_create"))]
         return {"kind": kind, "example": name, "profile": prof[-1] if prof else None, **extra, "threads": threads, "thread_steps": thread_steps, "saves": saves,
                 "mcmc_steps": steps, "wall_s": wall, "steps_per_s": steps / wall}
     finally:
