@@ -60,6 +60,7 @@ struct SamplerState {
     uint32_t *pool_idx[2] = {nullptr, nullptr};
     void* pool_tmp = nullptr;
     size_t pool_tmp_bytes = 0, pool_cap = 0, pool_n = 0;
+    int max_levels = 0;               // of kc_sampler_create; sp.Lcap = rows of cnt allocated so far
     int pool_cur = 0;
     int pool_ranks = 1;                // processes whose lists meet in the pool (the communicator's size at creation)
     int32_t* d_rank_counts = nullptr;  // [pool_ranks]
@@ -425,7 +426,10 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     sp.lanes = T;
     sp.P = P;
     sp.max_steps = cfg->max_steps;
-    sp.Lcap = cfg->max_levels;
+    // the per-lane counter rows grow with the level table (kc_sampler_set_levels): 4 x levels x lanes u32 for
+    // max_levels = 1024 and 65 536 lanes would be 1 GB that a typical run (a few dozen levels) never touches
+    s->max_levels = cfg->max_levels;
+    sp.Lcap = cfg->max_levels < 64 ? cfg->max_levels : 64;
     sp.lambda = cfg->lambda;
     sp.beta = cfg->beta;
     sp.key0 = cfg->seed + (uint64_t)cfg->lane0;
@@ -452,12 +456,12 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     DA(sp.flags, (size_t)T);
     DA(sp.above, (size_t)T * sp.max_steps * 2);
     DA(sp.n_above, (size_t)T);
-    DA(s->d_lv_logl, (size_t)sp.Lcap);
-    DA(s->d_lv_tb, (size_t)sp.Lcap);
-    DA(s->d_lv_logX, (size_t)sp.Lcap);
-    DA(s->d_lv_tries, (size_t)sp.Lcap);
+    DA(s->d_lv_logl, (size_t)s->max_levels);
+    DA(s->d_lv_tb, (size_t)s->max_levels);
+    DA(s->d_lv_logX, (size_t)s->max_levels);
+    DA(s->d_lv_tries, (size_t)s->max_levels);
     DA(sp.cnt, (size_t)4 * sp.Lcap * sp.ldl);
-    DA(s->d_cnt_sum, (size_t)4 * sp.Lcap);
+    DA(s->d_cnt_sum, (size_t)4 * s->max_levels);
     DA(s->d_offsets, (size_t)T + 1);
     DA(s->d_above_compact, (size_t)T * sp.max_steps * 2);
 #undef DA
@@ -467,7 +471,7 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
     sp.lv_logX = s->d_lv_logX;
     sp.lv_tries = s->d_lv_tries;
     CU(cudaMemcpy(s->d_pri, priors, sizeof(kc_prior_table), cudaMemcpyHostToDevice));
-    CU(cudaMallocHost(&s->h_cnt_sum, sizeof(uint64_t) * 4 * sp.Lcap));
+    CU(cudaMallocHost(&s->h_cnt_sum, sizeof(uint64_t) * 4 * s->max_levels));
     CU(cudaMallocHost(&s->h_total, sizeof(int32_t)));
     CU(cudaEventCreate(&s->ev0));
     CU(cudaEventCreate(&s->ev1));
@@ -629,9 +633,22 @@ int kc_sampler_set_levels(kc_ctx* c, int L, const double* logl, const double* ti
     if (rc) return rc;
     SamplerState* s = c->sampler;
     SamplerParams& sp = s->sp;
-    if (L < 1 || L > sp.Lcap) return fail(KC_ERR_ARG, "number of levels outside [1, max_levels of kc_sampler_create]");
+    if (L < 1 || L > s->max_levels) return fail(KC_ERR_ARG, "number of levels outside [1, max_levels of kc_sampler_create]");
     if (!logl || !tiebreaker || !log_X || !tries) return fail(KC_ERR_ARG, "null level array");
     CU(cudaSetDevice(c->device));
+    if (L > sp.Lcap) {
+        // the rows only hold the increments since the last barrier and are cleared below: nothing to carry over
+        int cap = 2 * sp.Lcap > L ? 2 * sp.Lcap : L;
+        if (cap > s->max_levels) cap = s->max_levels;
+        CU(cudaStreamSynchronize(c->stream));
+        uint32_t* grown = nullptr;
+        CU(cudaMalloc(&grown, sizeof(uint32_t) * 4 * (size_t)cap * sp.ldl));
+        for (void*& p : s->allocs)
+            if (p == (void*)sp.cnt) p = grown;
+        CU(cudaFree(sp.cnt));
+        sp.cnt = grown;
+        sp.Lcap = cap;
+    }
     // pageable sources: the copies are staged before the call returns
     CU(cudaMemcpyAsync(s->d_lv_logl, logl, sizeof(double) * L, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(s->d_lv_tb, tiebreaker, sizeof(double) * L, cudaMemcpyHostToDevice, c->stream));

@@ -89,7 +89,8 @@ def test_perturb_on_device_matches_reference(gpu, ref, name):
 @pytest.mark.parametrize("name,P,L_levels,at_max", [
     ("white", 2, 6, False), ("white", 1, 5, True), ("hyper", 2, 4, False), ("studentt_multi", 3, 1, False),
     ("gp", 2, 5, False), ("known_object", 1, 8, True), ("gp_multi_trend", 2, 3, False), ("trend3_ind", 2, 40, False),
-    ("gp_celerite", 1, 4, True), ("fixed_np", 2, 7, False)])
+    ("gp_celerite", 1, 4, True), ("fixed_np", 2, 7, False),
+    ("white", 2, 100, False)])  # more levels than the counter rows allocated at creation: they grow
 def test_mcmc_on_device_matches_reference(gpu, ref, name, P, L_levels, at_max):
     """kc_sampler_run (propose -> likelihood kernels -> accept, all on the GPU) against
     Sampler::mcmc_thread of the reference with its own CPU likelihood."""
@@ -108,7 +109,8 @@ def test_mcmc_on_device_matches_reference(gpu, ref, name, P, L_levels, at_max):
     want = ref.mcmc(T, P, steps, S, nps, logl, tb, level, lv_logl, lv_tb, lv_logX, cnt, 10.0, 100.0,
                     max_num_levels, 43, ctr0)
     with LikelihoodEngine(data, flags, T) as eng:
-        ds = DeviceSampler(eng, pri, SamplerOptions(lanes=T, num_particles=P, thread_steps=steps, max_levels=64))
+        ds = DeviceSampler(eng, pri, SamplerOptions(lanes=T, num_particles=P, thread_steps=steps,
+                                                    max_levels=max(64, 2 * L_levels)))
         ds.upload(S, nps, logl, tb, level)
         ds.set_counters(ctr0)
         ds.set_levels(lv_logl, lv_tb, lv_logX, cnt[:, 1], at_max, at_max)
