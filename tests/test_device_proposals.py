@@ -73,18 +73,20 @@ def test_device_run_is_reproducible_and_keeps_the_file_formats(gpu, tmp_path):
     assert int(st[-1]) == 300 * 16 * 50  # count_mcmc_steps: one save per barrier of lanes x thread steps
 
 
-def test_state_file_written_by_all_host_threads_equals_the_reference_print(gpu, tmp_path):
-    """sampler_state.txt of a many-lane run (4096 lanes x 2 particles) is formatted in chunks by the host
-    threads (BatchedSampler::print_state); KIMA_SERIAL_STATE=1 sends it through Sampler::print
-    (SamplerImpl.h:590-612) instead: the same bytes."""
+def test_many_lanes_sorted_kernels_and_chunked_state_file_change_no_byte(gpu, tmp_path):
+    """8192 lanes x 2 particles: the proposal kernels sort each CTA's lanes by move (the default from 8192
+    lanes on) and sampler_state.txt is formatted in chunks by the host threads (BatchedSampler::print_state).
+    Against the same run with one warp per CTA and no sorting (KC_SMP_BLOCK=0) and the state file through
+    Sampler::print (SamplerImpl.h:590-612, KIMA_SERIAL_STATE=1): every output file equal byte for byte."""
     opts = "2\n20000\n10000\n20\n0\n10\n100\n20\n"
-    a = run("gpu", "51Peg", tmp_path, "par", 4096, 43, True, opts)
-    b = run("gpu", "51Peg", tmp_path, "ser", 4096, 43, True, opts, {"KIMA_SERIAL_STATE": "1"})
+    a = run("gpu", "51Peg", tmp_path, "sorted", 8192, 43, True, opts)
+    b = run("gpu", "51Peg", tmp_path, "plain", 8192, 43, True, opts, {"KIMA_SERIAL_STATE": "1", "KC_SMP_BLOCK": "0"})
     sa, sb = (a / "sampler_state.txt").read_bytes(), (b / "sampler_state.txt").read_bytes()
-    assert len(sa) > 8192 * 40
+    assert len(sa) > 16384 * 40
     assert sa == sb
     for f in ("sample.txt", "sample_info.txt", "levels.txt"):
         assert (a / f).read_bytes() == (b / f).read_bytes(), f
+    assert len(load_sample(a / "sample.txt")[1]) >= 15
 
 
 def test_evidence_matches_the_reference_sampler(gpu, tmp_path):
