@@ -342,6 +342,7 @@ class BatchedSampler : public Sampler<ModelType> {
     unsigned int deletions_dev = 0;
     // one process: all_above stays in HBM (kc_sampler_collect_pool / kc_sampler_pool_select), the host
     // only knows its size; several processes: the lists are gathered on the host as before
+    double book_prof[3] = {0, 0, 0};  // selecting the new level, lagging particles, saving
     bool pool_mode = false;
     int64_t pool_n = 0;
 
@@ -386,36 +387,42 @@ class BatchedSampler : public Sampler<ModelType> {
         std::vector<bool> good(n, true);
         double max_log_push = -std::numeric_limits<double>::max();
         unsigned int num_bad = 0;
-        double kill_probability = 0.0;
+        // log_push and the kill probability depend on the level alone: one evaluation per level instead of
+        // four per particle (log_push walks the level table through enough_levels each time); same values,
+        // same draws from rngs[0] in the same order (SamplerImpl.h:543-558)
+        const size_t L = this->levels.size();
+        std::vector<double> push(L), kill(L);
+        for (size_t j = 0; j < L; ++j) {
+            push[j] = this->log_push((unsigned int)j);
+            kill[j] = pow(1.0 - 1.0 / (1.0 + exp(-push[j] - 4.0)), 3);
+        }
         for (size_t i = 0; i < n; ++i) {
-            if (this->log_push(this->level_assignments[i]) > max_log_push)
-                max_log_push = this->log_push(this->level_assignments[i]);
-            kill_probability = pow(1.0 - 1.0 / (1.0 + exp(-this->log_push(this->level_assignments[i]) - 4.0)), 3);
-            if (this->rngs[0].rand() <= kill_probability) {
+            const unsigned int lv = this->level_assignments[i];
+            if (push[lv] > max_log_push) max_log_push = push[lv];
+            if (this->rngs[0].rand() <= kill[lv]) {
                 good[i] = false;
                 ++num_bad;
             }
         }
         if (num_bad >= n) return;
+        std::vector<double> keep(L);
+        for (size_t j = 0; j < L; ++j) keep[j] = exp(push[j] - max_log_push);
         std::vector<size_t> dst, src;
+        std::ostringstream msg;
         for (size_t i = 0; i < n; ++i) {
             if (good[i]) continue;
             int i_copy;
             do {
                 i_copy = this->rngs[0].rand_int((int)n);
-            } while (!good[i_copy] ||
-                     this->rngs[0].rand() >= exp(this->log_push(this->level_assignments[i_copy]) - max_log_push));
+            } while (!good[i_copy] || this->rngs[0].rand() >= keep[this->level_assignments[i_copy]]);
             dst.push_back(i);
             src.push_back((size_t)i_copy);
             this->log_likelihoods[i] = this->log_likelihoods[i_copy];
             this->level_assignments[i] = this->level_assignments[i_copy];
             ++deletions_dev;
-            if (rank() == 0) {
-                std::cout << "# Replacing lagging particle.";
-                std::cout << " This has happened " << deletions_dev;
-                std::cout << " times." << std::endl;
-            }
+            if (rank() == 0) msg << "# Replacing lagging particle. This has happened " << deletions_dev << " times.\n";
         }
+        if (rank() == 0 && !dst.empty()) std::cout << msg.str() << std::flush;  // the reference's lines, one write
         // sources are good particles and never overwritten: the copies are independent
         std::vector<int32_t> ldst, lsrc;
         std::vector<size_t> cross;
@@ -491,6 +498,7 @@ class BatchedSampler : public Sampler<ModelType> {
             // element and the SET above it matter afterwards (the next creation orders again)
             const int index = static_cast<int>((1. - 1. / this->compression) * n_all);
             LikelihoodType new_level;
+            const double ts = now();
             if (pool_mode) {
                 // ordered and cut on the GPU, where the lists already are: one pair comes back
                 double v = 0, t = 0;
@@ -503,6 +511,7 @@ class BatchedSampler : public Sampler<ModelType> {
                 new_level = this->all_above[index];
                 this->all_above.erase(this->all_above.begin(), this->all_above.begin() + index + 1);
             }
+            book_prof[0] += now() - ts;
             if (rank() == 0) {
                 std::cout << "# Creating level " << this->levels.size() << " with log likelihood = ";
                 std::cout << std::setprecision(12);
@@ -520,17 +529,21 @@ class BatchedSampler : public Sampler<ModelType> {
                 this->options.max_num_levels = this->levels.size();
                 if (rank() == 0) std::cout << "# Done creating levels." << std::endl;
             } else {
+                const double tk = now();
                 kill_lagging_device();
+                book_prof[1] += now() - tk;
             }
             created_level = true;
         }
         Level::recalculate_log_X(this->levels, this->compression,
                                  this->options.new_level_interval * sqrt(this->options.lambda));
         if (created_level) this->save_levels();
+        const double tv = now();
         if (this->count_mcmc_steps_since_save >= this->options.save_interval) {
             save_particle_device();
             if (!created_level) this->save_levels();
         }
+        book_prof[2] += now() - tv;
         // record holder (:433-439)
         size_t best = 0;
         for (size_t i = 1; i < this->log_likelihoods.size(); ++i)
@@ -678,8 +691,9 @@ class BatchedSampler : public Sampler<ModelType> {
                       << std::endl;
         if (std::getenv("KIMA_PROFILE"))
             std::cerr << "# device proposals: steps + collect " << t_dev << " s, particle arrays back / exchange " << t_xfer
-                      << " s, folding counters / above / likelihoods in " << t_fold << " s, bookkeeping " << t_book << " s"
-                      << std::endl;
+                      << " s, folding counters / above / likelihoods in " << t_fold << " s, bookkeeping " << t_book
+                      << " s (new level " << book_prof[0] << ", lagging particles " << book_prof[1] << ", saves "
+                      << book_prof[2] << ")" << std::endl;
         // the end-of-run state file holds every particle: the ranks' columns go to everybody
         {
             std::vector<double> st;
