@@ -109,8 +109,26 @@ class BatchedSampler : public Sampler<ModelType> {
         for (const std::string& s : parts) out << s;
         out.setf(std::ios::fixed, std::ios::floatfield);
         out.precision(8);
-        for (const auto& l : this->log_likelihoods) l.print(out);
-        for (const auto& l : this->level_assignments) out << l << ' ';
+        // the likelihood pairs and the level assignments inherit those flags: chunk streams start from them
+        pool->run(0, (int)nchunks, [&](int a, int b) {
+            for (int c = a; c < b; ++c) {
+                std::ostringstream os;
+                os.copyfmt(out);
+                const size_t i1 = std::min(n, ((size_t)c + 1) * chunk);
+                for (size_t i = (size_t)c * chunk; i < i1; ++i) this->log_likelihoods[i].print(os);
+                parts[c] = os.str();
+            }
+        });
+        for (const std::string& s : parts) out << s;
+        pool->run(0, (int)nchunks, [&](int a, int b) {
+            for (int c = a; c < b; ++c) {
+                std::ostringstream os;
+                const size_t i1 = std::min(n, ((size_t)c + 1) * chunk);
+                for (size_t i = (size_t)c * chunk; i < i1; ++i) os << this->level_assignments[i] << ' ';
+                parts[c] = os.str();
+            }
+        });
+        for (const std::string& s : parts) out << s;
         for (const auto& l : this->levels) l.print(out);
         out << this->count_saves << ' ';
         out << this->count_mcmc_steps << ' ';
