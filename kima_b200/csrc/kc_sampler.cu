@@ -144,7 +144,8 @@ int sort_block(const SamplerParams& sp)
     }
     // measured (profiles/smp_sorted_r01e.txt, 51Peg shape): the step kernel 0.158 -> 0.070 ms at 65 536 lanes and
     // 0.65 -> 0.30 ms at 262 144 with B = 256 (128: 0.090, 64: 0.092); 0.078 -> 0.061 ms at 16 384
-    return sp.lanes >= 8192 ? 256 : 0;
+    // the step is latency-bound, not SM-bound: even 2048 lanes (8 CTAs) gain, 0.101 -> 0.085 ms per step
+    return sp.lanes >= 2048 ? 256 : 0;
 }
 template <bool ACCEPT>
 void launch_propose_t(const SamplerParams& sp, int B, int grid32, cudaStream_t st)

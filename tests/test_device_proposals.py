@@ -74,7 +74,7 @@ def test_device_run_is_reproducible_and_keeps_the_file_formats(gpu, tmp_path):
 
 
 def test_many_lanes_sorted_kernels_and_chunked_state_file_change_no_byte(gpu, tmp_path):
-    """8192 lanes x 2 particles: the proposal kernels sort each CTA's lanes by move (the default from 8192
+    """8192 lanes x 2 particles: the proposal kernels sort each CTA's lanes by move (the default from 2048
     lanes on) and sampler_state.txt is formatted in chunks by the host threads (BatchedSampler::print_state).
     Against the same run with one warp per CTA and no sorting (KC_SMP_BLOCK=0) and the state file through
     Sampler::print (SamplerImpl.h:590-612, KIMA_SERIAL_STATE=1): every output file equal byte for byte."""

@@ -100,7 +100,7 @@ def test_mcmc_on_device_matches_reference(gpu, ref, name, P, L_levels, at_max):
 @pytest.mark.parametrize("block", ["64", "256"])
 @pytest.mark.parametrize("name,P,L_levels", [("white", 2, 6), ("hyper", 2, 4), ("gp", 1, 5), ("known_object", 1, 8)])
 def test_move_sorted_proposal_kernels_match_reference(gpu, ref, monkeypatch, block, name, P, L_levels):
-    """From 8192 lanes on the proposal kernels sort the lanes of a CTA by their move before making it
+    """From 2048 lanes on the proposal kernels sort the lanes of a CTA by their move before making it
     (smp_sorted_propose_kernel); KC_SMP_BLOCK forces them at a size the reference finishes in seconds.
     300 lanes: the last CTA is ragged.  Same decisions, counters and stream positions as the reference."""
     monkeypatch.setenv("KC_SMP_BLOCK", block)
