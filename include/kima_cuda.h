@@ -160,6 +160,27 @@ int kc_eval(kc_ctx* ctx, int B, double* logL_host);
 int kc_eval_async(kc_ctx* ctx, int B, double* logL_host);
 int kc_wait(kc_ctx* ctx);
 int kc_eval_device(kc_ctx* ctx, int B, double* d_logL);
+/* Allocation-free variant of the kernel=celerite likelihood.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two kernels
+ * and the same results as kc_eval_device on a context configured with GP=true, kernel=1, but
+ * the [N][roundup(B,32)] residual scratch is a file-scope `static __device__` array of
+ * KC_NOALLOC_MAX_DOUBLES doubles (4 MiB, held by every GPU that loads the library until the
+ * process exits) instead of the block kc_configure allocates.  The call makes no cudaMalloc /
+ * cudaFree / allocating library call; the context (kc_create, kc_upload_data, kc_configure)
+ * is set up beforehand.  The caller passes the inputs and the output as device pointers:
+ *   d_params  [n_rows][ld] SoA parameter block (kc_get_layout), column b = lane b
+ *   d_np      [B] planets per lane;   d_logL  [B] result
+ * (kc_device_params hands out the context's own block, but any device memory will do).
+ * Asynchronous on the context stream (kc_sync / kc_stream).  Limit: N * roundup(B,32) <=
+ * KC_NOALLOC_MAX_DOUBLES, else KC_ERR_ARG with a message naming the limit.  The first call
+ * on each device resolves the array's address (cudaGetSymbolAddress; B = 0 does only that,
+ * e.g. before a graph capture starts).  All calls on a GPU share the one array: calls that
+ * overlap on that GPU (two contexts, two streams) race; nothing in it needs clearing between
+ * calls (every entry read is written first by the same call). */
+#define KC_NOALLOC_MAX_DOUBLES (1 << 19)
+int kc_eval_celerite_noalloc(kc_ctx* ctx, int B, const double* d_params,
+                             const int32_t* d_np, int ld, double* d_logL);
 int kc_sync(kc_ctx* ctx);
 /* cudaStream_t of the context, as void*. */
 int kc_stream(kc_ctx* ctx, void** stream);

@@ -44,6 +44,7 @@ SIGNATURES = {
     "kc_eval_async": (ctypes.c_int, [_vp, ctypes.c_int, _dp]),
     "kc_wait": (ctypes.c_int, [_vp]),
     "kc_eval_device": (ctypes.c_int, [_vp, ctypes.c_int, _vp]),
+    "kc_eval_celerite_noalloc": (ctypes.c_int, [_vp, ctypes.c_int, _vp, _vp, ctypes.c_int, _vp]),
     "kc_sync": (ctypes.c_int, [_vp]),
     "kc_stream": (ctypes.c_int, [_vp, ctypes.POINTER(_vp)]),
     "kc_set_option": (ctypes.c_int, [_vp, ctypes.c_char_p, ctypes.c_int]),

@@ -185,3 +185,73 @@ cudaError_t launch_gp_celerite(const KParams& p, double* resid, int ldr, int kep
 }
 
 }  // namespace kc
+
+// ---- allocation-free variant (include/kima_cuda.h: kc_eval_celerite_noalloc) ---------------
+// The same two kernels as launch_gp_celerite, with the [N][ldr] residual scratch taken from a
+// file-scope device array instead of the cudaMalloc'ed block kc_configure owns, for callers
+// that cannot allocate (CUDA graph capture, serving loops).  Every GPU that loads the library
+// holds the array (KC_NOALLOC_MAX_DOUBLES * 8 bytes = 4 MiB) until the process exits.
+#include <mutex>
+#include "kc_ctx.h"
+
+namespace {
+
+// In HOST code this name is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, below.
+static __device__ __align__(256) double g_noalloc_resid[KC_NOALLOC_MAX_DOUBLES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+std::mutex g_noalloc_mutex;
+
+}  // namespace
+
+extern "C" int kc_eval_celerite_noalloc(kc_ctx* c, int B, const double* d_params, const int32_t* d_np,
+                                        int ld, double* d_logL)
+{
+    int rc = kc::check_ready(c, 0);  // data uploaded, flags configured
+    if (rc) return rc;
+    if (!(c->F.GP && c->F.kernel == 1))
+        return kc::fail(KC_ERR_ARG, "kc_eval_celerite_noalloc needs GP=true with kernel=celerite");
+    if (B < 0) return kc::fail(KC_ERR_ARG, "B < 0");
+    if (B > 0 && (!d_params || !d_np || !d_logL)) return kc::fail(KC_ERR_ARG, "null device pointer");
+    if (B > 0 && ld < B) return kc::fail(KC_ERR_ARG, "ld < B");
+    if (c->device < 0 || c->device >= NOALLOC_MAX_DEVICES)
+        return kc::fail(KC_ERR_ARG, "device index beyond the scratch table");
+    const size_t ldr = ((size_t)B + 31) & ~(size_t)31;
+    if ((size_t)c->N * ldr > (size_t)KC_NOALLOC_MAX_DOUBLES)
+        return kc::fail(KC_ERR_ARG, "kc_eval_celerite_noalloc: N * roundup(B, 32) = " +
+                                        std::to_string((size_t)c->N * ldr) + " doubles of scratch exceed the static " +
+                                        std::to_string((size_t)KC_NOALLOC_MAX_DOUBLES) +
+                                        " (KC_NOALLOC_MAX_DOUBLES); use kc_eval_device or a smaller batch");
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return kc::fail_cuda(e, "cudaSetDevice");
+    double* scratch;
+    {
+        // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_ptr[c->device]) {
+            double* ptr = nullptr;
+            e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_resid);
+            if (e != cudaSuccess) return kc::fail_cuda(e, "cudaGetSymbolAddress(g_noalloc_resid)");
+            if (!ptr) return kc::fail(KC_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+            g_noalloc_ptr[c->device] = ptr;
+        }
+        scratch = g_noalloc_ptr[c->device];
+    }
+    if (B == 0) return KC_OK;  // set-up only
+    kc::KParams p{};
+    p.t = c->d_t; p.y = c->d_y; p.sig2 = c->d_sig2; p.obsi = c->d_obsi; p.actind = c->d_actind;
+    p.N = c->N; p.n_inst = c->n_inst; p.n_ind = c->n_ind;
+    p.M0_epoch = c->M0_epoch; p.t_middle = c->t_middle;
+    p.F = c->F; p.L = c->L;
+    p.params = d_params; p.np = d_np; p.ld = ld; p.B = B;
+    p.logL = d_logL; p.counter = c->d_counter;
+    // nothing in the scratch has to start at zero: the residual kernel writes every entry
+    // [0,N) x [0,B) that the recursion kernel reads, whatever the last call left behind
+    int n = 0;
+    e = kc::launch_gp_celerite(p, scratch, (int)ldr, c->kepler_mode, c->stream, &n);
+    if (e != cudaSuccess) return kc::fail_cuda(e, "kc_eval_celerite_noalloc launch");
+    c->launches += n;
+    return KC_OK;
+}
