@@ -82,11 +82,11 @@ kc::KParams make_params(kc_ctx* c, int B, double* d_logL, const double* d_params
 }  // namespace
 
 namespace kc {
-int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np)
+int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np, bool timed)
 {
     kc::KParams p = make_params(c, B, d_logL, d_params, d_np);
     int n = 0;
-    CU(cudaEventRecord(c->ev0, c->stream));
+    if (timed) CU(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
     if (c->F.GP && c->F.kernel == 1)
         e = kc::launch_gp_celerite(p, c->d_resid, c->ld, c->kepler_mode, c->stream, &n);
@@ -95,8 +95,10 @@ int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const 
     else if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
     if (e != cudaSuccess) return fail_cuda(e, "kernel launch");
-    CU(cudaEventRecord(c->ev1, c->stream));
-    c->timed = true;
+    if (timed) {
+        CU(cudaEventRecord(c->ev1, c->stream));
+        c->timed = true;
+    }
     c->launches += n;
     return KC_OK;
 }
@@ -166,6 +168,8 @@ int kc_destroy(kc_ctx* c)
     cudaFree(c->d_pred);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    if (c->copy_ev) cudaEventDestroy(c->copy_ev);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     cudaStreamDestroy(c->stream);
     delete c;
     return KC_OK;
@@ -251,7 +255,11 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
         // factor storage for as many lanes in flight as fit the budget; more lanes than
         // slots run in waves
         c->gp.slot_doubles = kc::gpb_slot_doubles(c->N);
-        const size_t cap = (size_t)64 << 30;  // out of 180 GB
+        // budget: 64 GB, or 80% of what the device has free right now if that is less
+        size_t free_b = 0, total_b = 0;
+        CU(cudaMemGetInfo(&free_b, &total_b));
+        size_t cap = (size_t)64 << 30;
+        if (cap > free_b / 5 * 4) cap = free_b / 5 * 4;
         size_t fit = cap / (sizeof(double) * c->gp.slot_doubles);
         if (fit < 1) fit = 1;
         int slots = c->gp_slots_opt > 0 ? c->gp_slots_opt : (int)(fit > (size_t)max_batch ? (size_t)max_batch : fit);
@@ -304,12 +312,40 @@ int kc_eval_async(kc_ctx* c, int B, double* logL_host)
     if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is already in flight");
     CU(cudaSetDevice(c->device));
     if (B == 0) return KC_OK;
-    // one strided copy moves columns [0,B) of every row
-    CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
-                         sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(c->d_np, c->h_np, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
-    rc = run_kernels(c, B, c->d_logL);
-    if (rc) return rc;
+    const int chunk = c->eval_chunk_opt;
+    if (chunk > 0 && B >= 2 * chunk) {
+        // large batches: the columns travel in chunks on a copy stream while the kernels of the
+        // previous chunk run, so that PCIe time hides behind compute (one event, re-recorded:
+        // cudaStreamWaitEvent binds to the record that precedes it)
+        if (!c->copy_stream) {
+            CU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&c->copy_ev, cudaEventDisableTiming));
+        }
+        CU(cudaEventRecord(c->copy_ev, c->stream));       // earlier readers of the device block
+        CU(cudaStreamWaitEvent(c->copy_stream, c->copy_ev, 0));
+        CU(cudaEventRecord(c->ev0, c->stream));
+        for (int c0 = 0; c0 < B; c0 += chunk) {
+            const int nb = B - c0 < chunk ? B - c0 : chunk;
+            CU(cudaMemcpy2DAsync(c->d_params + c0, sizeof(double) * c->ld, c->h_params + c0,
+                                 sizeof(double) * c->ld, sizeof(double) * nb, c->L.n_rows,
+                                 cudaMemcpyHostToDevice, c->copy_stream));
+            CU(cudaMemcpyAsync(c->d_np + c0, c->h_np + c0, sizeof(int32_t) * nb, cudaMemcpyHostToDevice,
+                               c->copy_stream));
+            CU(cudaEventRecord(c->copy_ev, c->copy_stream));
+            CU(cudaStreamWaitEvent(c->stream, c->copy_ev, 0));
+            rc = kc::run_kernels(c, nb, c->d_logL + c0, c->d_params + c0, c->d_np + c0, false);
+            if (rc) return rc;
+        }
+        CU(cudaEventRecord(c->ev1, c->stream));
+        c->timed = true;
+    } else {
+        // one strided copy moves columns [0,B) of every row
+        CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
+                             sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->d_np, c->h_np, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
+        rc = run_kernels(c, B, c->d_logL);
+        if (rc) return rc;
+    }
     CU(cudaMemcpyAsync(c->h_logL, c->d_logL, sizeof(double) * B, cudaMemcpyDeviceToHost, c->stream));
     c->pending_out = logL_host;
     c->pending_B = B;
@@ -373,6 +409,9 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
     } else if (k == "gp_streams") {
         if (value < 1 || value > 4) return fail(KC_ERR_ARG, "gp_streams must be 1..4");
         c->gp_streams_opt = value;  // takes effect at the next kc_configure
+    } else if (k == "eval_chunk") {
+        if (value < 0) return fail(KC_ERR_ARG, "eval_chunk must be >= 0 (0 = one copy, no overlap)");
+        c->eval_chunk_opt = value;
     } else if (k == "gp_slots") {
         if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
         c->gp_slots_opt = value;  // takes effect at the next kc_configure

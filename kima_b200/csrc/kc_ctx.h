@@ -31,6 +31,9 @@ struct kc_ctx {
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
+    int eval_chunk_opt = 32768;  // kc_eval: batches of >= 2 chunks overlap H2D with the kernels (0 = off)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_ev = nullptr;
     int gp_small_opt = 1;   // 1 = shared-memory-resident kernel whenever N fits, 0 = always blocked
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
@@ -58,7 +61,8 @@ namespace kc {
 // np [B]); asynchronous on the context stream.
 int fail(int code, const std::string& msg);
 int fail_cuda(cudaError_t e, const char* what);
-int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np);
+int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np,
+                bool timed = true);
 int check_ready(kc_ctx* c, int B);
 void sampler_free(kc_ctx* c);  // kc_sampler_api.cu
 }  // namespace kc

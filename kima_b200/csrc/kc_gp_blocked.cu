@@ -560,7 +560,8 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
     // latency-bound diagonal blocks (and launch tails) run beside another's update tiles.
     int ng = w.nstreams < 1 ? 1 : w.nstreams;
     while (ng > 1 && (p.B < ng * sm_count || w.slots < ng)) ng--;  // small batches: one group
-    const int gslots = w.slots / ng;
+    // lanes go in gridDim.y of the update kernel (and of kc_predict's mean kernel): at most 65535
+    const int gslots = min(w.slots / ng, 65535);
     const int per_group = (p.B + ng - 1) / ng;
     if (ng > 1) {
         e = cudaEventRecord(w.fork, stream);
@@ -575,8 +576,12 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
         double* ws_g = w.ws + (size_t)g * gslots * w.slot_doubles;
         GpLane* lanes_g = w.lanes + (size_t)g * gslots;
         const int lane_end = min(p.B, (g + 1) * per_group);
-        for (int lane0 = g * per_group; lane0 < lane_end; lane0 += gslots) {
-            const int n = min(gslots, lane_end - lane0);
+        // waves of equal size (342 + 341 + 341 lanes rather than 476 + 476 + 72)
+        const int cnt = lane_end - g * per_group;
+        const int nwaves = (cnt + gslots - 1) / gslots;
+        const int per_wave = nwaves > 0 ? (cnt + nwaves - 1) / nwaves : 0;
+        for (int lane0 = g * per_group; lane0 < lane_end; lane0 += per_wave) {
+            const int n = min(per_wave, lane_end - lane0);
             if (kepler_mode == 0)
                 gpb_prep_kernel<0><<<n, CTA_THREADS, ma_smem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, lane0);
             else

@@ -37,8 +37,13 @@ def flags_dict(f: ModelFlags) -> dict:
     return {k: int(getattr(f, k)) for k in f.__dataclass_fields__}
 
 
+ONLY = set(sys.argv[1:])  # `make_golden.py name ...` regenerates just those fixtures
+
+
 def save_case(ref: Oracle, name: str, flags: ModelFlags, data: RVData, B: int, np_mode: str,
               seed: int, with_cov: bool = False, load_info=None, edge=None):
+    if ONLY and name not in ONLY:
+        return
     ref.set_rvdata(data)
     ref.set_flags(flags)
     P, nps = make_params(flags, data, B, np_mode, seed=seed)
@@ -57,9 +62,7 @@ def save_case(ref: Oracle, name: str, flags: ModelFlags, data: RVData, B: int, n
                                                           int(np.isfinite(logL).sum())))
 
 
-def main():
-    ref = Oracle("reference")
-
+def kepler_vectors(ref):
     # ---- Kepler known answers -------------------------------------------------------
     rng = np.random.default_rng(12345)
     n = 20000
@@ -79,6 +82,13 @@ def main():
     np.savez_compressed(os.path.join(HERE, "kepler.npz"), M=M, e=e, E=E, t=t, P=P, ecc=ee, Tp=Tp, f=f)
     print("kepler.npz: %d (M,e) pairs, %d true anomalies" % (M.size, t.size))
 
+
+
+def main():
+    ref = Oracle("reference")
+
+    if not ONLY or "kepler" in ONLY:
+        kepler_vectors(ref)
     # ---- the example data sets, through the reference's own loaders ------------------
     def ex(path, *a, multi=False, **k):
         d = ref.ref_load_multi(path, *a) if multi else ref.ref_load(path, *a, **k)
@@ -135,6 +145,9 @@ def main():
                                                  trend=True, degree=3, known_object=True,
                                                  n_known_object=2, hyperpriors=True),
               make_data(200, 3, 2), 32, "mix", 56)
+
+    # BASELINE.json configs[4], the scale point: N=4096, QP-GP + Np<=10 (12 s per lane on the CPU)
+    save_case(ref, "synth_gp_N4096", ModelFlags(GP=True, npmax=10), make_data(4096), 4, "mix", 11)
 
     # ---- MA(1) term (src/RVmodel.cpp:378-386) ---------------------------------------------
     save_case(ref, "synth_ma_N200", ModelFlags(npmax=3, MA=True), make_data(200), 16, "mix", 58)

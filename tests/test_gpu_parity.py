@@ -257,6 +257,23 @@ def test_full_size_gp_vs_oracle(gpu, port):
         assert np.array_equal(got2[:64], got) and np.array_equal(got2[64:128], got)
 
 
+def test_scale_point_gp_N4096_vs_reference(gpu):
+    """BASELINE.json configs[4]: N=4096, QP-GP + Np<=10, against the reference's own
+    calculate_mu / calculate_C / log_likelihood (tests/golden/synth_gp_N4096.npz, made by
+    oracle/_ref/libkima_ref.so) at the north-star tolerance, over several waves of the factor
+    storage (134 MB per lane in flight) and both lane-group settings."""
+    g = load_golden("synth_gp_N4096")
+    B = g["nps"].size
+    with LikelihoodEngine(g["data"], g["flags"], 3 * B, gp_slots=3) as eng:   # waves of 3 slots
+        got = eng.evaluate(g["params"], g["nps"])
+        assert relerr(got, g["logL"]).max() <= LOGL_RTOL, relerr(got, g["logL"])
+        # three times the lanes through the same three slots: 4 waves, results unchanged
+        got3 = eng.evaluate(np.tile(g["params"], (1, 3)), np.tile(g["nps"], 3))
+        assert np.array_equal(got3.reshape(3, B), np.tile(got, (3, 1)))
+    with LikelihoodEngine(g["data"], g["flags"], B, gp_streams=1) as eng:     # all lanes in flight, one group
+        assert np.array_equal(eng.evaluate(g["params"], g["nps"]), got)
+
+
 def test_scale_point_gp_N4096_vs_lapack(gpu, port):
     """configs[4] shape: N=4096, QP-GP + Np<=10.  The C oracle supplies mu; LAPACK the factorisation."""
     from oracle.gp_numpy import gp_loglik, qp_cov
@@ -275,6 +292,20 @@ def test_scale_point_gp_N4096_vs_lapack(gpu, port):
         C = qp_cov(d.t, d.sig, np.full(N, P[L["row_jit"], b] ** 2), *P[L["row_eta"]:L["row_eta"] + 4, b])
         ref = gp_loglik(d.y - mu, C)
         assert abs(got[b] - ref) <= 1e-9 * abs(ref)  # LAPACK's own rounding at N=4096, cond ~1e8
+
+
+def test_gp_blocked_more_lanes_in_flight_than_a_grid_dimension(gpu):
+    """The blocked path puts the lanes of a wave in gridDim.y (<= 65535): a batch whose lane
+    groups exceed that must run as several waves, not fail with 'invalid configuration'."""
+    flags = ModelFlags(GP=True, npmax=1)
+    d = make_data(40)
+    nd, B = 1000, 140000   # two lane groups of 70000 > 65535
+    P, nps = make_params(flags, d, nd, "mix")
+    with LikelihoodEngine(d, flags, B) as eng:
+        eng.set_option("gp_small", 0)
+        want = eng.evaluate(P, nps)
+        got = eng.evaluate(np.tile(P, (1, B // nd)), np.tile(nps, B // nd))
+        assert np.array_equal(got.reshape(B // nd, nd), np.tile(want, (B // nd, 1)))
 
 
 def test_non_positive_definite_gives_plus_inf(gpu):

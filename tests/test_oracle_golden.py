@@ -61,6 +61,16 @@ def test_logL_mu_cov_golden(port, name):
         assert np.array_equal(port.cov(g["params"], 0), g["C0"])
 
 
+def test_scale_point_N4096_port_matches_reference(port):
+    """BASELINE.json configs[4] (N=4096, QP-GP): the plain-C port against the reference's values
+    on two lanes (the port's unblocked LLT takes ~6 s per lane here)."""
+    g = load_golden("synth_gp_N4096")
+    port.set_rvdata(g["data"])
+    port.set_flags(g["flags"])
+    logL, _ = port.eval_batch(g["params"][:, :2].copy(), g["nps"][:2], 2)
+    assert relerr(logL, g["logL"][:2]).max() <= 2e-12
+
+
 def test_nonfinite_maps_to_minus_1e300(port):
     # src/RVmodel.cpp:938-941 then DNest4/code/LikelihoodType.cpp:17-24
     g = load_golden("synth_edge")
