@@ -232,6 +232,15 @@ int kc_gp_cov(kc_ctx* ctx, int lane, double* C);
 #define KC_PRED_GP 2
 int kc_predict(kc_ctx* ctx, int B, int nt, const double* t_pred, int what,
                double* model_out, double* gp_out);
+/* The predictive standard deviation of the same GP, GP.predict(..., return_std=True)
+ * (pykima/GP.py:113-131, reached through predict_with_hyperpars(return_std=True), :134-175):
+ *   gp_std_out[b*nt + k] = sqrt(max(0, k(t*,t*) - k(t*,t) C^-1 k(t,t*))),  k(t*,t*) = eta1^2,
+ * by forward substitution of the nt right-hand sides against the Cholesky factor of the
+ * likelihood (pykima forms C^-1 explicitly); NaN where C is not positive definite.
+ * gp_out (the predictive mean, as KC_PRED_GP) may be NULL.  Needs GP=true, standard kernel. */
+#define KC_PRED_GP_STD 4
+int kc_predict_std(kc_ctx* ctx, int B, int nt, const double* t_pred, double* gp_out,
+                   double* gp_std_out);
 
 /* ---- multi-GPU: the level-creation barrier of DNest4 ----------------------
  * (DNest4/code/SamplerImpl.h:306-329).  One rank per GPU. */

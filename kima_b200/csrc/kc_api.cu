@@ -267,6 +267,11 @@ int kc_configure(kc_ctx* c, const kc_model_flags* f, int max_batch)
         c->gp.slots = slots;
         CU(cudaMalloc(&c->gp.ws, sizeof(double) * c->gp.slot_doubles * slots));
         CU(cudaMalloc((void**)&c->gp.lanes, kc::gpb_lane_bytes() * slots));
+        {
+            cudaError_t te = kc::gpb_make_tensor_maps(c->gp, c->N);
+            if (te != cudaSuccess) return fail_cuda(te, "cuTensorMapEncodeTiled over the GP factor storage (TMA descriptors)");
+            c->gp.tma_ok = true;
+        }
         c->gp.nstreams = c->gp_streams_opt;
         CU(cudaEventCreateWithFlags(&c->gp.fork, cudaEventDisableTiming));
         for (int i = 0; i + 1 < c->gp.nstreams; i++) {

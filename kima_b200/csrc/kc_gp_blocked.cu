@@ -20,6 +20,7 @@
 // the tile that consumes it.  HBM traffic per particle is one write of L (4 N^2 B) and
 // N^3/(6 NB) * 8 B of panel re-reads; the FLOPs are the N^3/3 of the factorisation, all
 // of the O(N^3) part on the FP64 tensor cores (mma.sync m8n8k4, SASS DMMA).
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
 #include "kc_model.cuh"
 #include "kc_gp_common.cuh"
 
@@ -32,7 +33,7 @@ constexpr int KC = 16;        // k-chunk per pipeline stage
 constexpr int STAGES = 3;
 constexpr int A_LD = R + 4;   // 132 = 4 mod 16: conflict-free fragment reads (half-warp = 4 k x 4 rows)
 constexpr int B_LD = NB + 4;  // 68  = 4 mod 16
-constexpr int S_LD = NB + 1;  // diag kernel: row-per-lane access
+constexpr int S_LD = NB + 4;  // diag kernel: S_JJ column-major, element (r, c) at Ss[c * S_LD + r]; 68 = 4 mod 16
 constexpr int STAGE_DOUBLES = KC * (A_LD + B_LD);
 constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;
 static_assert(NB * A_LD <= PIPE_DOUBLES, "the S tile aliases the pipeline stages");
@@ -42,30 +43,101 @@ constexpr int D_STAGES = 3;
 constexpr int H_LD = 34;      // 32x32 half-block buffers of the diag kernel
 constexpr int D_STAGE_DOUBLES = KC * B_LD;
 constexpr int D_SMEM_DOUBLES = D_STAGES * D_STAGE_DOUBLES + NB * S_LD;
-static_assert(2 * 32 * H_LD <= D_STAGES * D_STAGE_DOUBLES, "half-block buffers alias the diag pipeline");
+static_assert(32 * H_LD <= D_STAGES * D_STAGE_DOUBLES, "the L21 buffer aliases the diag pipeline");
 constexpr int PAD_DOUBLES = 256;  // tiles may read (never use) up to R rows past the last column
 }  // namespace gpb
 
 // What one block-column launch works on.
 struct GpbStep {
     int j0;         // first column of the block column
+    int slot0;      // first factor-storage slot of the lane group (third coordinate of the tensor maps)
     int n;          // lanes (= slots) in flight
     int first_row;  // update kernel: first row of the first tile
     int ntile;      // update kernel: row tiles per lane
 };
 
 size_t gpb_ld(int N) { return ((size_t)N + 1 + 15) & ~(size_t)15; }
-size_t gpb_slot_doubles(int N) { return gpb_ld(N) * (size_t)N + gpb::PAD_DOUBLES; }
+// a whole number of columns per slot: the slot stride of the tensor maps is then a multiple of the column stride
+size_t gpb_slot_doubles(int N) { return gpb_ld(N) * ((size_t)N + (gpb::PAD_DOUBLES + gpb_ld(N) - 1) / gpb_ld(N)); }
+
+// The two TMA descriptors over the factor storage of a context (see the plumbing comment below).
+cudaError_t gpb_make_tensor_maps(GpWorkspace& w, int N)
+{
+    using namespace gpb;
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess) return e;
+    if (!fn || q != cudaDriverEntryPointSuccess) return cudaErrorNotSupported;
+    const cuuint64_t ld = gpb_ld(N);
+    const cuuint64_t dims[3] = {ld, (cuuint64_t)N, (cuuint64_t)w.slots};
+    const cuuint64_t strides[2] = {ld * sizeof(double), (cuuint64_t)w.slot_doubles * sizeof(double)};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const cuuint32_t rows[2] = {A_LD, B_LD};
+    unsigned char* dst[2] = {w.tmap_a, w.tmap_b};
+    for (int i = 0; i < 2; i++) {
+        alignas(64) CUtensorMap tm;
+        const cuuint32_t box[3] = {rows[i], KC, 1};
+        CUresult r = reinterpret_cast<encode_fn>(fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, w.ws, dims, strides, box, estr,
+                                                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+        static_assert(sizeof(CUtensorMap) == sizeof(w.tmap_a), "CUtensorMap is 128 bytes");
+        memcpy(dst[i], &tm, sizeof(tm));
+    }
+    return cudaSuccess;
+}
 size_t gpb_lane_bytes() { return sizeof(GpLane); }
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+// ---- TMA + mbarrier plumbing (sm_100a: SASS UTMALDG / UBLKCP / SYNCS) ------------------------
+// Panels of L travel from HBM to shared memory as boxes of two tensor maps over the whole factor
+// storage, seen as a (row, column, slot) tensor of doubles with strides (8, 8 ld, 8 slot_doubles)
+// bytes: box A = A_LD rows x KC columns, box B = B_LD rows x KC columns.  The box heights ARE the
+// padded leading dimensions of the shared-memory stages (132 and 68 = 4 mod 16: conflict-free DMMA
+// fragment reads), so a dense box lands in the padded layout; the 4 extra rows are read and
+// ignored, rows past the tensor come back as zeros.  One elected thread issues, consumers wait on
+// the stage's "full" mbarrier and release it through its "empty" mbarrier: no CTA-wide barrier
+// inside the K loop and no per-thread copy instructions.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int count)
 {
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N_>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* tm, uint64_t* bar, int row, int col, int slot)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(row), "r"(col), "r"(slot)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
 
 // Barrier over the 128 threads (warps 0-3) that factor a diagonal block, whether they are
 // the whole diag CTA or half of an update CTA.
@@ -130,8 +202,8 @@ gpb_prep_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
 // K loop of the diag kernel for the warp that owns fragment rows F0 and 7-F0 (all
 // fragment indices compile-time: 9 DMMAs per k-step, no predication), then P -> Ss.
 template <int F0>
-__device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t ld, int j0,
-                                           double* pipe, double* Ss, int tid, int lane)
+__device__ __forceinline__ void diag_kloop(const CUtensorMap* tmB, int slot_g, uint64_t* full, uint64_t* empty,
+                                           int j0, double* pipe, double* Ss, int tid, int lane)
 {
     using namespace gpb;
     constexpr int F1 = 7 - F0;
@@ -141,27 +213,19 @@ __device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t 
 #pragma unroll
     for (int c = 0; c <= F1; c++) acc1[c][0] = acc1[c][1] = 0.0;
     const int nk = j0 / KC;
-    auto load_stage = [&](int s, int it) {
-        double* Bs = pipe + s * D_STAGE_DOUBLES;
-        const double* src = W + (size_t)(it * KC) * ld + j0;
-        // KC x NB doubles = 512 16-byte units, 4 per thread
-#pragma unroll
-        for (int u = tid; u < KC * NB / 2; u += D_THREADS) {
-            int kk = u / (NB / 2), r2 = (u % (NB / 2)) * 2;
-            cp_async16(Bs + kk * B_LD + r2, src + (size_t)kk * ld + r2);
-        }
-    };
-#pragma unroll
-    for (int s = 0; s < D_STAGES - 1; s++) {
-        if (s < nk) load_stage(s, s);
-        cp_async_commit();
-    }
     for (int it = 0; it < nk; it++) {
-        cp_async_wait<D_STAGES - 2>();
-        bar_diag();
-        if (it + D_STAGES - 1 < nk) load_stage((it + D_STAGES - 1) % D_STAGES, it + D_STAGES - 1);
-        cp_async_commit();
-        const double* Bs = pipe + (it % D_STAGES) * D_STAGE_DOUBLES;
+        const int st = it % D_STAGES;
+        if (tid == 0) {
+            const int it2 = it + D_STAGES - 1;
+            if (it2 < nk) {
+                const int s2 = it2 % D_STAGES;
+                if (it2 >= D_STAGES) mbar_wait(empty + s2, ((it2 / D_STAGES) & 1) ^ 1);
+                mbar_expect_tx(full + s2, D_STAGE_DOUBLES * 8);
+                tma_load_3d(pipe + s2 * D_STAGE_DOUBLES, tmB, full + s2, j0, it2 * KC, slot_g);
+            }
+        }
+        mbar_wait(full + st, (it / D_STAGES) & 1);
+        const double* Bs = pipe + st * D_STAGE_DOUBLES;
 #pragma unroll
         for (int k4 = 0; k4 < KC; k4 += 4) {
             const int kk = k4 + (lane & 3);
@@ -173,19 +237,20 @@ __device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t 
 #pragma unroll
             for (int c = 0; c <= F1; c++) dmma(acc1[c][0], acc1[c][1], bf[F1], bf[c]);
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + st);
     }
-    cp_async_wait<0>();
 #pragma unroll
     for (int c = 0; c <= F0; c++) {
         const int r = F0 * 8 + (lane >> 2), cc = c * 8 + 2 * (lane & 3);
-        Ss[r * S_LD + cc] = acc0[c][0];
-        Ss[r * S_LD + cc + 1] = acc0[c][1];
+        Ss[cc * S_LD + r] = acc0[c][0];
+        Ss[(cc + 1) * S_LD + r] = acc0[c][1];
     }
 #pragma unroll
     for (int c = 0; c <= F1; c++) {
         const int r = F1 * 8 + (lane >> 2), cc = c * 8 + 2 * (lane & 3);
-        Ss[r * S_LD + cc] = acc1[c][0];
-        Ss[r * S_LD + cc + 1] = acc1[c][1];
+        Ss[cc * S_LD + r] = acc1[c][0];
+        Ss[(cc + 1) * S_LD + r] = acc1[c][1];
     }
 }
 
@@ -195,25 +260,42 @@ __device__ __forceinline__ void diag_kloop(const double* __restrict__ W, size_t 
 // produced the 64 rows of L the block needs, and folding the (latency-bound) factorisation
 // into the update launch lets the other CTA on the SM keep the FP64 pipe busy meanwhile.
 __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict__ W, size_t ld,
-                                           GpLane& gl, int j0, double* dsm, int tid)
+                                           GpLane& gl, int j0, double* dsm, int tid,
+                                           const CUtensorMap* tmB, int slot_g)
 {
     using namespace gpb;
     double* pipe = dsm;                                // D_STAGES x [KC][B_LD]
-    double* Ss = dsm + D_STAGES * D_STAGE_DOUBLES;     // [NB][S_LD]
-    double* LTs = pipe;                                // after the K loop: [32][H_LD], LTs[c][c2] = L11(c2,c)
-    double* T21 = pipe + 32 * H_LD;                    // [32][H_LD]: L21 row-major
+    double* Ss = dsm + D_STAGES * D_STAGE_DOUBLES;     // [NB][S_LD], column-major
+    double* T21 = pipe;                                // after the K loop: [32][H_LD], L21 row-major
     __shared__ double dinv_s[NB];
-    __shared__ __align__(16) double colbuf_s[CHOL_COLBUF];
     __shared__ int fail_s;
     const int warp = tid >> 5, lane = tid & 31;
     const int N = p.N;
     const int nbc = min(NB, N - j0);
-    if (tid == 0) fail_s = 0;
+    __shared__ __align__(8) uint64_t dbars[2 * D_STAGES];
+    uint64_t* full = dbars;
+    uint64_t* empty = dbars + D_STAGES;
+    if (tid == 0) {
+        fail_s = 0;
+        for (int s = 0; s < D_STAGES; s++) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, D_THREADS / 32);
+        }
+        mbar_fence_init();
+    }
+    bar_diag();
+    if (tid == 0) {
+        const int nk = j0 / KC;
+        for (int s = 0; s < D_STAGES - 1 && s < nk; s++) {
+            mbar_expect_tx(full + s, D_STAGE_DOUBLES * 8);
+            tma_load_3d(pipe + s * D_STAGE_DOUBLES, tmB, full + s, j0, s * KC, slot_g);
+        }
+    }
     switch (warp) {
-        case 0: diag_kloop<0>(W, ld, j0, pipe, Ss, tid, lane); break;
-        case 1: diag_kloop<1>(W, ld, j0, pipe, Ss, tid, lane); break;
-        case 2: diag_kloop<2>(W, ld, j0, pipe, Ss, tid, lane); break;
-        default: diag_kloop<3>(W, ld, j0, pipe, Ss, tid, lane); break;
+        case 0: diag_kloop<0>(tmB, slot_g, full, empty, j0, pipe, Ss, tid, lane); break;
+        case 1: diag_kloop<1>(tmB, slot_g, full, empty, j0, pipe, Ss, tid, lane); break;
+        case 2: diag_kloop<2>(tmB, slot_g, full, empty, j0, pipe, Ss, tid, lane); break;
+        default: diag_kloop<3>(tmB, slot_g, full, empty, j0, pipe, Ss, tid, lane); break;
     }
     bar_diag();
     {
@@ -236,9 +318,9 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
                 } else {
                     v = qp_kernel(g, kadd(__ldg(p.t + j0 + cc), -trow));
                 }
-                v -= Ss[r * S_LD + cc];
+                v -= Ss[cc * S_LD + r];
             }
-            Ss[r * S_LD + cc] = v;
+            Ss[cc * S_LD + r] = v;
         }
     }
     bar_diag();
@@ -249,12 +331,9 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
         const int h0 = 32 * half;
         const int nv = max(0, min(32, nbc - h0));
         if (warp == 0) {
-            double s[32];
-#pragma unroll
-            for (int c = 0; c < 32; c++) s[c] = Ss[(h0 + lane) * S_LD + h0 + c];
-            if (!chol32_rows_in_lanes(s, lane, nv, logdet, dinv_s + h0,
-                                      W + (size_t)(j0 + h0) * ld + j0 + h0, ld,
-                                      half == 0 ? LTs : nullptr, H_LD, colbuf_s) && lane == 0)
+            // L11 / L22 stay in Ss (in place) and go to HBM
+            if (!chol32_panels<false>(Ss + h0 * S_LD + h0, S_LD, lane, nv, logdet, dinv_s + h0,
+                                      W + (size_t)(j0 + h0) * ld + j0 + h0, ld) && lane == 0)
                 fail_s = 1;
         }
         bar_diag();
@@ -263,12 +342,12 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
                 // L21 = S21 L11^-T: row 32+lane, forward substitution
                 double t[32];
 #pragma unroll
-                for (int c = 0; c < 32; c++) t[c] = Ss[(32 + lane) * S_LD + c];
+                for (int c = 0; c < 32; c++) t[c] = Ss[c * S_LD + 32 + lane];
 #pragma unroll
                 for (int c = 0; c < 32; c++) {
                     t[c] *= dinv_s[c];
 #pragma unroll
-                    for (int c2 = c + 1; c2 < 32; c2++) t[c2] = kfma(-t[c], LTs[c * H_LD + c2], t[c2]);
+                    for (int c2 = c + 1; c2 < 32; c2++) t[c2] = kfma(-t[c], Ss[c * S_LD + c2], t[c2]);  // L11(c2, c)
                 }
 #pragma unroll
                 for (int c = 0; c < 32; c++) {
@@ -292,7 +371,7 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
                         a0 = kfma(t[k], o[k], a0);
                         a1 = kfma(t[k + 1], o[k + 1], a1);
                     }
-                    Ss[(32 + lane) * S_LD + 32 + c2] -= a0 + a1;
+                    Ss[(32 + c2) * S_LD + 32 + lane] -= a0 + a1;
                 }
             }
             bar_diag();
@@ -307,24 +386,26 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
 
 __global__ void __launch_bounds__(gpb::D_THREADS, 3)
 gpb_diag_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                GpLane* __restrict__ lanes, const GpbStep w)
+                GpLane* __restrict__ lanes, const GpbStep w, const __grid_constant__ CUtensorMap tmB)
 {
-    extern __shared__ __align__(16) double dsm_k[];
+    extern __shared__ __align__(128) double dsm_k[];
     const int slot = blockIdx.x;
     GpLane& gl = lanes[slot];
     if (gl.fail) return;
     const size_t ld = ((size_t)p.N + 1 + 15) & ~(size_t)15;
-    diag_block(p, ws_all + (size_t)slot * slot_doubles, ld, gl, w.j0, dsm_k, threadIdx.x);
+    diag_block(p, ws_all + (size_t)slot * slot_doubles, ld, gl, w.j0, dsm_k, threadIdx.x, &tmB, w.slot0 + slot);
 }
 
 
 // ---- update: the panel below the diagonal block ----------------------------------------------
 __global__ void __launch_bounds__(CTA_THREADS, 2)
 gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doubles,
-                  GpLane* __restrict__ lanes, const GpbStep w)
+                  GpLane* __restrict__ lanes, const GpbStep w, const __grid_constant__ CUtensorMap tmA,
+                  const __grid_constant__ CUtensorMap tmB)
 {
     using namespace gpb;
-    extern __shared__ __align__(16) double usm[];
+    extern __shared__ __align__(128) double usm[];
+    __shared__ __align__(8) uint64_t ubars[2 * STAGES + 1];
     const int j0 = w.j0, first_row = w.first_row;
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
@@ -346,47 +427,52 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         for (int c = 0; c < 4; c++) acc[a][c][0] = acc[a][c][1] = 0.0;
 
     // L_JJ (as stored: LT[c][c2] = L_JJ(c2, c), only c2 > c is ever read) and 1/diag ride in
-    // as the oldest cp.async group, hidden behind the K loop
+    // on their own mbarrier, hidden behind the K loop
     double* LT = usm + PIPE_DOUBLES;     // [NB][B_LD]
     double* dinv = LT + NB * B_LD;       // [NB]
-    for (int u = tid; u < nbc * (NB / 2); u += CTA_THREADS) {
-        const int c = u / (NB / 2), c2 = (u % (NB / 2)) * 2;
-        cp_async16(LT + c * B_LD + c2, W + (size_t)(j0 + c) * ld + j0 + c2);
-    }
-    if (tid < NB / 2) cp_async16(dinv + 2 * tid, &gl.dinv[(j0 / NB) & 1][2 * tid]);
-    cp_async_commit();
-
+    uint64_t* full = ubars;
+    uint64_t* empty = ubars + STAGES;
+    uint64_t* aux = ubars + 2 * STAGES;
     const int nk = j0 / KC;
+    const int slot_g = w.slot0 + slot;
     const bool warp_rows_live = r0 + wr * 32 <= N;
-    auto load_stage = [&](int s, int it) {
+    constexpr uint32_t STAGE_BYTES = STAGE_DOUBLES * 8;
+    auto issue_stage = [&](int s, int it) {
         double* As = usm + s * STAGE_DOUBLES;
-        double* Bs = As + KC * A_LD;
-        const double* col0 = W + (size_t)(it * KC) * ld;
-        // A: KC x R doubles = 1024 16-byte units (4 per thread); B: KC x NB = 512 (2 per thread)
-#pragma unroll
-        for (int u = tid; u < KC * R / 2; u += CTA_THREADS) {
-            int kk = u / (R / 2), r2 = (u % (R / 2)) * 2;
-            cp_async16(As + kk * A_LD + r2, col0 + (size_t)kk * ld + r0 + r2);
-        }
-#pragma unroll
-        for (int u = tid; u < KC * NB / 2; u += CTA_THREADS) {
-            int kk = u / (NB / 2), c2 = (u % (NB / 2)) * 2;
-            cp_async16(Bs + kk * B_LD + c2, col0 + (size_t)kk * ld + j0 + c2);
-        }
+        mbar_expect_tx(full + s, STAGE_BYTES);
+        tma_load_3d(As, &tmA, full + s, r0, it * KC, slot_g);            // A_LD rows x KC columns of the row tile
+        tma_load_3d(As + KC * A_LD, &tmB, full + s, j0, it * KC, slot_g);  // B_LD rows x KC columns of block row J
     };
-#pragma unroll
-    for (int s = 0; s < STAGES - 1; s++) {
-        if (s < nk) load_stage(s, s);
-        cp_async_commit();
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, CTA_WARPS);
+        }
+        mbar_init(aux, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        mbar_expect_tx(aux, (NB / KC) * KC * B_LD * 8 + NB * 8);
+        for (int q = 0; q < NB / KC; q++) tma_load_3d(LT + q * KC * B_LD, &tmB, aux, j0, j0 + q * KC, slot_g);
+        bulk_load(dinv, &gl.dinv[(j0 / NB) & 1][0], NB * 8, aux);
+        for (int s = 0; s < STAGES - 1 && s < nk; s++) issue_stage(s, s);
     }
     for (int it = 0; it < nk; it++) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        if (it + STAGES - 1 < nk) load_stage((it + STAGES - 1) % STAGES, it + STAGES - 1);
-        cp_async_commit();
-        const double* As = usm + (it % STAGES) * STAGE_DOUBLES;
+        const int st = it % STAGES;
+        if (tid == 0) {
+            // refill the stage every warp released at the end of iteration it - 1
+            const int it2 = it + STAGES - 1;
+            if (it2 < nk) {
+                const int s2 = it2 % STAGES;
+                if (it2 >= STAGES) mbar_wait(empty + s2, ((it2 / STAGES) & 1) ^ 1);
+                issue_stage(s2, it2);
+            }
+        }
+        mbar_wait(full + st, (it / STAGES) & 1);
+        const double* As = usm + st * STAGE_DOUBLES;
         const double* Bs = As + KC * A_LD;
-        // a warp whose 32 rows are all past row N (partial last tile): loads and barriers only
+        // a warp whose 32 rows are all past row N (partial last tile): waits and releases only
 #pragma unroll
         for (int k4 = 0; k4 < (warp_rows_live ? KC : 0); k4 += 4) {
             const int kk = k4 + (lane & 3);
@@ -400,8 +486,10 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
 #pragma unroll
                 for (int c = 0; c < 4; c++) dmma(acc[a][c][0], acc[a][c][1], af[a], bf[c]);
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + st);
     }
-    cp_async_wait<0>();
+    mbar_wait(aux, 0);
     __syncthreads();  // every warp is done with the stages: the epilogue buffers alias them
 
     double* SsT = usm;                   // [NB][A_LD]: the tile, column-major (S, then X in place)
@@ -423,25 +511,28 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         const int row = r0 + rl;
         const bool row_ok = row >= row_lo && row <= N;
         const double trow = (row_ok && row < N) ? __ldg(p.t + row) : 0.0;
-        // two columns per pass (cl, cl + 2): two independent chains per thread
-        for (int cl = tid >> 7; cl < NB; cl += 2 * CTA_THREADS / R) {
-            const int cl1 = cl + CTA_THREADS / R;
-            const int col = j0 + cl, col1 = j0 + cl1;
-            double v0 = 0.0, v1 = 0.0;
+        // four columns per pass (cl, cl + 2, cl + 4, cl + 6): four independent chains per thread
+        constexpr int CS = CTA_THREADS / R;  // 2
+        for (int cl = tid >> 7; cl < NB; cl += 4 * CS) {
+            double v[4] = {0.0, 0.0, 0.0, 0.0};
             if (row_ok) {
                 if (row == N) {
-                    if (cl < nbc) v0 = W[(size_t)col * ld + N];
-                    if (cl1 < nbc) v1 = W[(size_t)col1 * ld + N];
+#pragma unroll
+                    for (int q = 0; q < 4; q++)
+                        if (cl + q * CS < nbc) v[q] = W[(size_t)(j0 + cl + q * CS) * ld + N];
                 } else {
                     // t[i]-t[j], i<j (:193); columns past a partial block are generated and dropped
-                    const double tc0 = __ldg(p.t + min(col, N - 1)), tc1 = __ldg(p.t + min(col1, N - 1));
-                    qp_kernel2(g, kadd(tc0, -trow), kadd(tc1, -trow), v0, v1);
+                    double tc[4];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) tc[q] = __ldg(p.t + min(j0 + cl + q * CS, N - 1));
+                    qp_kernel2(g, kadd(tc[0], -trow), kadd(tc[1], -trow), v[0], v[1]);
+                    qp_kernel2(g, kadd(tc[2], -trow), kadd(tc[3], -trow), v[2], v[3]);
                 }
-                v0 = cl < nbc ? v0 - SsT[cl * A_LD + rl] : 0.0;
-                v1 = cl1 < nbc ? v1 - SsT[cl1 * A_LD + rl] : 0.0;
+#pragma unroll
+                for (int q = 0; q < 4; q++) v[q] = cl + q * CS < nbc ? v[q] - SsT[(cl + q * CS) * A_LD + rl] : 0.0;
             }
-            SsT[cl * A_LD + rl] = v0;
-            SsT[cl1 * A_LD + rl] = v1;
+#pragma unroll
+            for (int q = 0; q < 4; q++) SsT[(cl + q * CS) * A_LD + rl] = v[q];
         }
     }
     __syncthreads();
@@ -538,6 +629,10 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
 {
     using namespace gpb;
     if (p.B <= 0) return cudaSuccess;
+    if (!w.tma_ok) return cudaErrorNotReady;  // kc_configure builds the tensor maps
+    CUtensorMap tmA, tmB;
+    memcpy(&tmA, w.tmap_a, sizeof(tmA));
+    memcpy(&tmB, w.tmap_b, sizeof(tmB));
     const size_t usmem = sizeof(double) * U_SMEM_DOUBLES;
     const size_t dsmem = sizeof(double) * D_SMEM_DOUBLES;
     cudaError_t e;
@@ -590,13 +685,14 @@ cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler
             for (int J = 0; J < nblk; J++) {
                 GpbStep st;
                 st.j0 = J * NB;
+                st.slot0 = g * gslots;
                 st.n = n;
                 const int nbc = min(NB, N - st.j0);
                 // rows below the diagonal block, up to and including the residual row N
                 st.first_row = nbc == NB ? st.j0 + NB : st.j0;
                 st.ntile = (N + 1 - st.first_row + R - 1) / R;
-                gpb_diag_kernel<<<n, D_THREADS, dsmem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, st);
-                gpb_update_kernel<<<dim3(st.ntile, n), CTA_THREADS, usmem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, st);
+                gpb_diag_kernel<<<n, D_THREADS, dsmem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, st, tmB);
+                gpb_update_kernel<<<dim3(st.ntile, n), CTA_THREADS, usmem, st_g>>>(p, ws_g, w.slot_doubles, lanes_g, st, tmA, tmB);
                 *n_launches += 2;
             }
             gpb_finish_kernel<<<(n + 127) / 128, 128, 0, st_g>>>(p, lanes_g, lane0, n);

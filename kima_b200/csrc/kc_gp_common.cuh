@@ -106,32 +106,6 @@ __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-// Unblocked Cholesky of a 32x32 block (LLT.h:313-337) by one warp, row `lane` of the block
-// in s[0..lane].  Rolled loops over the columns: every step consumes s[0] and writes the
-// updated row shifted down by one (s[k-1] <- s[k] - L(r,c) L(c+k,c)), so all register
-// indices are static and the body stays in the instruction cache; the window of live
-// entries narrows every 8 columns (31, 23, 15, 7).  The finished column goes to Lout
-// (Lout(c, r) = L(r, c), column-major; HBM or shared) and, transposed, to LT if wanted.
-// `progress` (shared memory, may be null): set to progress_base + c + 1 once column c and
-// 1/L(c,c) are visible, so that other warps can follow the factorisation column by column.
-// CTA-scope release store / acquire load for flags in shared memory (a __threadfence_block()
-// is a sequentially consistent MEMBAR.SC.CTA, far more than a producer/consumer flag needs).
-__device__ __forceinline__ void st_release_cta(int* p, int v)
-{
-    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
-}
-__device__ __forceinline__ int ld_acquire_cta(const int* p)
-{
-    int v;
-    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
-    return v;
-}
-
-struct Chol32State {
-    double d, inv, l, lmine;
-    bool ok;
-};
-
 // 1/sqrt(d) from the MUFU seed + two Newton steps, sqrt(d) = d/sqrt(d) + one Heron step
 __device__ __forceinline__ void chol_pivot(double d, double& inv, double& l)
 {
@@ -147,102 +121,130 @@ __device__ __forceinline__ void chol_pivot(double d, double& inv, double& l)
     inv = y;
 }
 
-// Column broadcast buffer of chol32: two parity halves of CHOL_CB_STRIDE doubles.  The lanes
-// read L(c+1..c+W, c) of the finished column as 16-byte pairs, so the column is stored with
-// a shift of one element for even c (element c+1 then sits at an even index either way).
-constexpr int CHOL_CB_STRIDE = 72;
-constexpr int CHOL_COLBUF = 2 * CHOL_CB_STRIDE;
-
-template <int W>
-__device__ __forceinline__ void chol32_steps(double (&s)[32], Chol32State& st, int c_lo, int c_hi, int lane,
-                                             int nvalid, double* dinv_out, double* __restrict__ Lout,
-                                             size_t ld, double* LT, int lt_ld, double* colbuf,
-                                             int* progress, int progress_base)
+// Cholesky of a 32x32 diagonal block (LLT.h:313-337) by ONE warp, the block resident in shared
+// memory, column-major: element (r, c) at S[c * ldS + r], lower triangle valid, ldS = 4 mod 16.
+// Blocked by panels of 8 columns:
+//   panel   rows in lanes, the 8 columns of row `lane` in registers; per column the loop-carried
+//           chain is scale -> square -> shuffle -> rsqrt (MUFU seed + 2 Newton steps), and the
+//           rest of the step is <= 7 shuffle + FMA pairs: the warp is bound by that chain
+//           (about 120 cycles per column), not by its issue slots (the unblocked variant of
+//           round 1 updated a 31-wide register window per column: 380 cycles, 230 of them issue)
+//   update  the 8-column panel goes back to shared memory and the trailing part of the block is
+//           updated on the FP64 tensor cores (two DMMA.8x8x4 per 8x8 fragment, read-modify-write
+//           of the fragment in shared memory); the columns of the next panel first.
+// L overwrites S (rows < nvalid); dinv_out[c] = 1 / L(c, c); L also goes to Lout (column-major,
+// leading dimension ld; HBM) when Lout is not null.  Rows / columns >= nvalid of a partial block
+// are treated as identity.  MASK: rows >= nvalid of S belong to other warps (the shared-memory
+// resident path keeps the residual row and the rows other warps substitute there): they are
+// neither read as data nor written.  `progress` (shared memory, may be null) is set to
+// progress_base + c + 8 once the panel that starts at column c and its 1/L(c,c) are visible, so
+// that other warps can follow the factorisation panel by panel.
+// CTA-scope release store / acquire load for flags in shared memory (a __threadfence_block()
+// is a sequentially consistent MEMBAR.SC.CTA, far more than a producer/consumer flag needs).
+__device__ __forceinline__ void st_release_cta(int* p, int v)
 {
-    constexpr int NP2 = (W + 1) / 2;
-#pragma unroll 1
-    for (int c = c_lo; c < c_hi; c++) {
-        if (!(st.d > 0.0)) st.ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
-        if (lane == c) st.lmine = st.l;
-        if (lane == 0) dinv_out[c] = st.inv;
-        const double lrc = s[0] * st.inv;
-        const double lcc = st.l;
-        // The next pivot is known to lane c+1 before the column is broadcast:
-        // s'[0] = s[1] - L(c+1,c)^2, the same FMA the update below performs.  Its
-        // rsqrt chain (latency-bound) then overlaps the loads + FMAs (issue-bound).
-        st.d = __shfl_sync(0xffffffffu, kfma(-lrc, lrc, s[1]), (c + 1) & 31);
-        const double dn = st.d;
-        const int shift = (c & 1) ^ 1;
-        double* cb = colbuf + (c & 1) * CHOL_CB_STRIDE + shift;
-        cb[lane] = lrc;
-        cb[lane + 32] = lrc;
-        if (lane >= c && lane < nvalid) Lout[(size_t)c * ld + lane] = (lane == c) ? lcc : lrc;
-        if (LT) LT[c * lt_ld + lane] = (lane > c) ? lrc : 0.0;
-        __syncwarp();
-        if (progress && lane == 0) st_release_cta(progress, progress_base + c + 1);
-        // col2[j] = { L(c+1+2j, c), L(c+2+2j, c) }: c + 1 + shift is even
-        const double2* col2 = reinterpret_cast<const double2*>(cb + c + 1);
-        double2 cv[NP2];
-#pragma unroll
-        for (int j = 0; j < NP2; j++) cv[j] = col2[j];
-        // A warp issues in order: the pivot chain (chol_pivot, ~10 dependent FP64 operations)
-        // is written out here stage by stage with a group of the W independent update FMAs
-        // after every stage, so that its latency is covered by them instead of preceding them.
-        constexpr int G = (W + 7) / 8;
-#define CHOL_FMAS(g)                                                                            \
-        _Pragma("unroll") for (int k = 1 + (g) * G; k <= W && k <= ((g) + 1) * G; k++) {        \
-            const double v = ((k - 1) & 1) ? cv[(k - 1) >> 1].y : cv[(k - 1) >> 1].x;           \
-            s[k - 1] = kfma(-lrc, v, s[k]);                                                     \
-        }                                                                                       \
-        asm volatile("" : "+d"(y), "+d"(e), "+d"(l), "+d"(s[(g) * G]));
-        double y = rsqrt_seed(dn), e = 0.0, l = 0.0;
-        CHOL_FMAS(0)
-        double hy = 0.5 * y;
-        e = kfma(-dn * y, hy, 0.5);
-        CHOL_FMAS(1)
-        y = kfma(y, e, y);
-        CHOL_FMAS(2)
-        hy = 0.5 * y;
-        l = dn * y;
-        CHOL_FMAS(3)
-        e = kfma(-l, hy, 0.5);
-        CHOL_FMAS(4)
-        y = kfma(y, e, y);
-        CHOL_FMAS(5)
-        e = kfma(-l, l, dn);
-        CHOL_FMAS(6)
-        l = kfma(e, 0.5 * y, l);
-        CHOL_FMAS(7)
-#undef CHOL_FMAS
-        st.inv = y;
-        st.l = l;
-        s[W] = 0.0;
-    }
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_cta(const int* p)
+{
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
 }
 
-__device__ __forceinline__ bool chol32_rows_in_lanes(double (&s)[32], int lane, int nvalid,
-                                                     double& logdet, double* dinv_out,
-                                                     double* __restrict__ Lout, size_t ld,
-                                                     double* LT, int lt_ld, double* colbuf,
-                                                     int* progress = nullptr, int progress_base = 0)
+constexpr int CHOL_PANEL = 8;
+
+template <bool MASK>
+__device__ __forceinline__ bool chol32_panels(double* S, int ldS, int lane, int nvalid, double& logdet,
+                                              double* dinv_out, double* __restrict__ Lout, size_t ld,
+                                              int* progress = nullptr, int progress_base = 0)
 {
-    // colbuf: CHOL_COLBUF doubles of 16-byte-aligned shared memory; the finished column is
-    // broadcast through it (written twice, 32 apart, so that L(c+k, c) is read without
-    // wrap-around; double-buffered by the parity of c: one __syncwarp per column)
-    Chol32State st;
-    st.ok = true;
-    st.lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant
-    st.d = __shfl_sync(0xffffffffu, s[0], 0);
-    chol_pivot(st.d, st.inv, st.l);
-    chol32_steps<31>(s, st, 0, 8, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
-    chol32_steps<23>(s, st, 8, 16, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
-    chol32_steps<15>(s, st, 16, 24, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
-    chol32_steps<7>(s, st, 24, 32, lane, nvalid, dinv_out, Lout, ld, LT, lt_ld, colbuf, progress, progress_base);
-    double lg = lane < nvalid ? log(st.lmine) : 0.0;
+    constexpr unsigned FULL = 0xffffffffu;
+    const int fr = lane >> 2, fk = lane & 3;
+    bool ok = true;
+    double lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant
+    double d = 1.0, inv = 1.0, l = 1.0;
+#pragma unroll 1
+    for (int p = 0; p < 4; p++) {
+        const int c0 = CHOL_PANEL * p;
+        // ---- the panel: 8 columns of row `lane` ----
+        double a[CHOL_PANEL];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, o);
+        for (int k = 0; k < CHOL_PANEL; k++) {
+            const int c = c0 + k;
+            double v = (lane == c) ? 1.0 : 0.0;  // identity padding of a partial block; zeros above the diagonal
+            if (lane < nvalid && c <= lane) v = S[c * ldS + lane];
+            a[k] = v;
+        }
+        d = __shfl_sync(FULL, a[0], c0);
+        chol_pivot(d, inv, l);
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++) {
+            const int c = c0 + k;
+            if (!(d > 0.0)) ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
+            if (lane == c) lmine = l;
+            if (lane == k) dinv_out[c] = inv;
+            const double lrc = a[k] * inv;  // L(lane, c) below the diagonal
+            const double lcc = l;
+            if (k + 1 < CHOL_PANEL) {
+                // The next pivot is known to lane c+1 before the column is passed round:
+                // S(c+1,c+1) - L(c+1,c)^2, the same FMA the update below performs.  Its rsqrt
+                // chain (latency-bound) overlaps the shuffles + FMAs of the rest of the panel.
+                d = __shfl_sync(FULL, kfma(-lrc, lrc, a[k + 1]), c + 1);
+                chol_pivot(d, inv, l);
+#pragma unroll
+                for (int k2 = k + 1; k2 < CHOL_PANEL; k2++)
+                    a[k2] = kfma(-lrc, __shfl_sync(FULL, lrc, c0 + k2), a[k2]);
+            }
+            a[k] = (lane == c) ? lcc : lrc;
+        }
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++) {
+            const int c = c0 + k;
+            if (lane >= c && lane < nvalid) {
+                S[c * ldS + lane] = a[k];
+                if (Lout) Lout[(size_t)c * ld + lane] = a[k];
+            }
+        }
+        __syncwarp();
+        if (progress && lane == 0) st_release_cta(progress, progress_base + c0 + CHOL_PANEL);
+        // ---- trailing update of the block on the tensor cores: S(i,j) -= sum_k L(i,k) L(j,k) ----
+        if (p < 3) {
+            double af[4][2];  // fragments of L[8I .. 8I+7, panel]: A operand of row block I, B operand of column block I
+#pragma unroll
+            for (int I = 1; I < 4; I++) {
+                af[I][0] = af[I][1] = 0.0;
+                const int row = 8 * I + fr;
+                if (I > p && (!MASK || row < nvalid)) {
+                    af[I][0] = S[(c0 + fk) * ldS + row];
+                    af[I][1] = S[(c0 + 4 + fk) * ldS + row];
+                }
+            }
+#pragma unroll
+            for (int J = 1; J < 4; J++) {
+#pragma unroll
+                for (int I = J; I < 4; I++) {
+                    if (J > p) {  // warp-uniform
+                        double u0 = 0.0, u1 = 0.0;
+                        dmma(u0, u1, af[I][0], af[J][0]);
+                        dmma(u0, u1, af[I][1], af[J][1]);
+                        const int row = 8 * I + fr;
+                        double* q = S + (8 * J + 2 * fk) * ldS + row;
+                        if (!MASK || row < nvalid) {
+                            q[0] -= u0;
+                            q[ldS] -= u1;
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    double lg = lane < nvalid ? log(lmine) : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(FULL, lg, o);
     logdet += lg;
-    return st.ok;
+    return ok;
 }
 
 }  // namespace kc

@@ -11,13 +11,14 @@
 // column-major [32][ld_J] over rows 32J .. N, where row N is the residual r = y - mu (so
 // z = L^-1 r falls out of the factorisation as row N of L and r^T C^-1 r = |z|^2).
 //
-// Warp roles (12 warps in one CTA per SM; 6 or 4 warps in 2 or 3 CTAs per SM when the factor is
-// small enough, so that the serial chains of several particles overlap):
-//   warp 0      "diag": the 32x32 Cholesky of each diagonal block, rows in lanes
-//               (chol32_rows_in_lanes) -- a serial chain of N column steps, the critical path
+// Warp roles (16 warps in one CTA per SM; 8, 5 or 4 warps in 2, 3 or 4 CTAs per SM when the factor
+// is small enough, so that the serial chains of several particles overlap):
+//   warp 0      "diag": the 32x32 Cholesky of each diagonal block (chol32_panels: 8-column panels
+//               with the rows in lanes, trailing update on the tensor cores) -- a serial chain of
+//               N column steps, the critical path
 //   warps 1..   "workers", left-looking per block column J:
 //       U_J  S[:,J] = C[:,J] - L[:,0:j0] L[J,0:j0]^T   8x32 strips on the FP64 tensor cores
-//       T_J  X = S L_JJ^-T                              a row per lane, forward substitution
+//       T_J  X = S L_JJ^-T                              a row per lane, 8-column panels + DMMA
 //     and, whenever they would wait for the diag warp, they generate covariance entries of
 //     later block columns from a shared work queue: the generation (the largest consumer of
 //     issue slots at this size) hides under the factorisation chain.
@@ -31,7 +32,7 @@ namespace kc {
 
 namespace gps {
 constexpr int T = 32;
-constexpr int REGS_PER_THREAD = 168;  // 1 x 12, 2 x 6 or 3 x 4 warps fill the register file
+constexpr int WARPS_PER_SM = 16;      // 128 registers per thread: 1 x 16, 2 x 8, 3 x 5 or 4 x 4 warps fill the register file
 constexpr int MAXBLK = 8;
 constexpr int GW = 4;              // columns per generation item: two qp_kernel2 calls, four independent chains per lane
 constexpr int GQ = T / GW;         // generation items per 32x32 tile
@@ -43,7 +44,6 @@ struct Hdr {
     ParticleScalars sc;
     GpConsts g;
     double dinv[T];
-    alignas(16) double colbuf[CHOL_COLBUF];
     double quad;
     int base[MAXBLK];
     int ld[MAXBLK];
@@ -161,10 +161,12 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
     }
 }
 
-// T_J for 32 rows below the diagonal block: row per lane, X L_JJ^T = S in place.  Rolled
-// loops over the columns with a rotating register window (x[k] holds element c+k at step c),
-// so register indices stay static and the body stays in the instruction cache; the window
-// narrows from 31 to 15 for the second half of the columns.
+// T_J for 32 rows below the diagonal block: X L_JJ^T = S in place, a row per lane, following the
+// diag warp panel by panel (8 columns).  Within a panel: plain substitution on the 8 columns of
+// the lane's row in registers (L_JJ read as shared-memory broadcasts); the columns to the right
+// of the panel are then updated on the tensor cores, X[:, rest] -= X[:, panel] L_JJ[rest, panel]^T,
+// fragments read-modify-written in shared memory: 4x fewer issue slots than a 31-wide register
+// window per column.
 #ifndef KC_GPS_SLEEP_T
 #define KC_GPS_SLEEP_T 20
 #endif
@@ -174,58 +176,84 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
 #ifndef KC_GPS_SLEEP_F
 #define KC_GPS_SLEEP_F 40
 #endif
-#ifndef KC_GPS_TBATCH
-#define KC_GPS_TBATCH 1
-#endif
-template <int W>
-__device__ __forceinline__ void trsm_steps(double (&x)[T], const double* S, int ldj, int c_lo, int c_hi,
-                                           const double* dinv, double* mine, bool ok, double& q,
-                                           const int* col_done, int need0, int& seen, int lane)
-{
-#pragma unroll 1
-    for (int c = c_lo; c < c_hi; c++) {
-        // follow the diag warp column by column: column c of L_JJ and 1/L(c,c) are published
-        if (seen < need0 + c + 1) {
-            const int want = need0 + min((c / KC_GPS_TBATCH + 1) * KC_GPS_TBATCH, c_hi);
-            while ((seen = ld_uniform(col_done, lane)) < want) __nanosleep(KC_GPS_SLEEP_T);
-        }
-        const double x0 = x[0] * dinv[c];
-        if (ok) mine[(size_t)c * ldj] = x0;
-        q = kfma(x0, x0, q);
-        const double* lc = S + (size_t)c * ldj + c;  // lc[k] = L_JJ(c+k, c)
-        double lv[W + 1];
-#pragma unroll
-        for (int k = 1; k <= W; k++) lv[k] = lc[k];
-#pragma unroll
-        for (int k = 1; k <= W; k++) x[k - 1] = kfma(-x0, lv[k], x[k]);
-        x[W] = 0.0;
-    }
-}
-
 __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int nbc, int tile, int lane)
 {
     const int j0 = T * J;
-    const int row = j0 + nbc + T * tile + lane;
+    const int row0 = nbc + T * tile;  // first row of the tile, relative to j0
+    const int row = j0 + row0 + lane;
     const bool ok = row <= N;
     const int ldj = H.ld[J];
     double* S = M + H.base[J];
-    double* mine = S + (ok ? row - j0 : nbc);
-    double x[T];
-#pragma unroll
-    for (int c = 0; c < T; c++) x[c] = mine[(size_t)c * ldj];
+    double* mine = S + (ok ? row0 + lane : nbc);
+    double* tileS = S + row0;
+    const int fr = lane >> 2, fk = lane & 3;
     double q = 0.0;
-    int seen = 0;
-    trsm_steps<31>(x, S, ldj, 0, min(nbc, 8), H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
-    trsm_steps<23>(x, S, ldj, 8, min(nbc, 16), H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
-    trsm_steps<15>(x, S, ldj, 16, min(nbc, 24), H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
-    trsm_steps<7>(x, S, ldj, 24, nbc, H.dinv, mine, ok, q, &H.col_done, j0, seen, lane);
+#pragma unroll 1
+    for (int c0 = 0; c0 < nbc; c0 += CHOL_PANEL) {
+        const int want = j0 + min(c0 + CHOL_PANEL, nbc);
+        while (ld_uniform(&H.col_done, lane) < want) __nanosleep(KC_GPS_SLEEP_T);
+        double x[CHOL_PANEL];
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++) x[k] = mine[(size_t)min(c0 + k, nbc - 1) * ldj];
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++) {
+            const int c = c0 + k;
+            if (c < nbc) {  // warp-uniform
+                const double x0 = x[k] * H.dinv[c];
+                x[k] = x0;
+                q = kfma(x0, x0, q);
+                const double* lc = S + (size_t)c * ldj + c0;  // lc[k2] = L_JJ(c0 + k2, c)
+#pragma unroll
+                for (int k2 = k + 1; k2 < CHOL_PANEL; k2++) x[k2] = kfma(-x0, lc[k2], x[k2]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++)
+            if (ok && c0 + k < nbc) mine[(size_t)(c0 + k) * ldj] = x[k];
+        __syncwarp();
+        if (c0 + CHOL_PANEL < nbc) {
+            // A fragments: X(tile row 8 Ir + fr, panel column 4 h + fk); columns past a partial block are zero
+            double af[4][2];
+#pragma unroll
+            for (int Ir = 0; Ir < 4; Ir++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int c = c0 + 4 * h + fk;
+                    af[Ir][h] = c < nbc ? tileS[(size_t)c * ldj + 8 * Ir + fr] : 0.0;
+                }
+#pragma unroll 1
+            for (int cb = c0 + CHOL_PANEL; cb < nbc; cb += 8) {
+                // B fragment: L_JJ(cb + fr, panel column 4 h + fk)
+                double bf[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int c = c0 + 4 * h + fk;
+                    bf[h] = (c < nbc && cb + fr < nbc) ? S[(size_t)c * ldj + cb + fr] : 0.0;
+                }
+#pragma unroll
+                for (int Ir = 0; Ir < 4; Ir++) {
+                    double u0 = 0.0, u1 = 0.0;
+                    dmma(u0, u1, af[Ir][0], bf[0]);
+                    dmma(u0, u1, af[Ir][1], bf[1]);
+                    const int col = cb + 2 * fk;
+                    const int r = j0 + row0 + 8 * Ir + fr;
+                    double* qd = tileS + (size_t)col * ldj + 8 * Ir + fr;
+                    if (r <= N) {
+                        if (col < nbc) qd[0] -= u0;
+                        if (col + 1 < nbc) qd[ldj] -= u1;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
     if (ok && row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
 }
 
-// NW warps per CTA (1 diag + NW-1 workers); 12 / NW CTAs share an SM when the factor is small
+// NW warps per CTA (1 diag + NW-1 workers); 16 / NW CTAs share an SM when the factor is small
 // enough, so that the serial chains of several particles overlap.
 template <int MODE, int NW>
-__global__ void __launch_bounds__(NW * 32, 12 / NW) gps_kernel(const KParams p)
+__global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const KParams p)
 {
     constexpr int THREADS = NW * 32;
     constexpr int WORKERS = NW - 1;
@@ -321,17 +349,8 @@ __global__ void __launch_bounds__(NW * 32, 12 / NW) gps_kernel(const KParams p)
             while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(KC_GPS_SLEEP_D);
             PROF(0);
             const int nv = min(T, N - j0);
-            const int ldj = H.ld[J];
-            double* S = M + H.base[J];
-            double s[T];
-#pragma unroll
-            for (int c = 0; c < T; c++) {
-                double v = (c == lane) ? 1.0 : 0.0;  // identity padding of a partial block
-                if (lane < nv && c <= lane) v = S[(size_t)c * ldj + lane];
-                s[c] = v;
-            }
-            if (!chol32_rows_in_lanes(s, lane, nv, logdet, H.dinv, S, (size_t)ldj, nullptr, 0, H.colbuf,
-                                      &H.col_done, T * J))
+            if (!chol32_panels<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv, nullptr, 0,
+                                     &H.col_done, T * J))
                 ok = false;
             __syncwarp();
             if (lane == 0) st_release_cta(&H.d_done, J + 1);
@@ -414,9 +433,10 @@ cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stre
     const size_t per_sm = 228 * 1024;
     const int fit = (int)(per_sm / (smem + 1024));
     cudaError_t e;
-    if (fit >= 3) e = kepler_mode == 0 ? launch_one<0, 4>(p, smem, stream) : launch_one<1, 4>(p, smem, stream);
-    else if (fit == 2) e = kepler_mode == 0 ? launch_one<0, 6>(p, smem, stream) : launch_one<1, 6>(p, smem, stream);
-    else e = kepler_mode == 0 ? launch_one<0, 12>(p, smem, stream) : launch_one<1, 12>(p, smem, stream);
+    if (fit >= 4) e = kepler_mode == 0 ? launch_one<0, 4>(p, smem, stream) : launch_one<1, 4>(p, smem, stream);
+    else if (fit == 3) e = kepler_mode == 0 ? launch_one<0, 5>(p, smem, stream) : launch_one<1, 5>(p, smem, stream);
+    else if (fit == 2) e = kepler_mode == 0 ? launch_one<0, 8>(p, smem, stream) : launch_one<1, 8>(p, smem, stream);
+    else e = kepler_mode == 0 ? launch_one<0, 16>(p, smem, stream) : launch_one<1, 16>(p, smem, stream);
     *n_launches += 1;
     return e;
 }

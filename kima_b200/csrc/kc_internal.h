@@ -52,6 +52,11 @@ struct GpWorkspace {
     int nstreams;               // groups (1..4)
     cudaStream_t aux[3];
     cudaEvent_t fork, join[3];
+    // TMA descriptors (CUtensorMap, 128 bytes each) over ws as a (row, column, slot) tensor: boxes of
+    // the update kernel's A and B panels (kc_gp_blocked.cu: gpb_make_tensor_maps)
+    alignas(64) unsigned char tmap_a[128];
+    alignas(64) unsigned char tmap_b[128];
+    bool tma_ok;
 };
 // posterior-predictive GP mean, computed wave by wave while the factors are still in HBM
 // (kc_predict.cu)
@@ -64,6 +69,7 @@ struct GpPredict {
 size_t gpb_ld(int N);
 size_t gpb_slot_doubles(int N);
 size_t gpb_lane_bytes();
+cudaError_t gpb_make_tensor_maps(GpWorkspace& w, int N);
 cudaError_t launch_gp_blocked(const KParams& p, const GpWorkspace& w, int kepler_mode, int sm_count,
                               cudaStream_t stream, int* n_launches, const GpPredict* pred = nullptr);
 cudaError_t launch_gp_predict_wave(const KParams& p, const double* ws, size_t slot_doubles,

@@ -2,8 +2,8 @@
 
 Restates, for one parameter vector at a time,
   KimaResults.model()          /root/reference/pykima/results.py:723-797
-  GP.predict(y - model, t)     /root/reference/pykima/GP.py:96-112 (mean only), with the
-                               kernel of pykima/GP.py:36-55
+  GP.predict(y - model, t)     /root/reference/pykima/GP.py:96-131 (mean, and the standard
+                               deviation of return_std=True), with the kernel of pykima/GP.py:36-55
 on top of the reference's C++ arithmetic as the oracle exposes it: the Keplerians use
 kepler::true_anomaly (src/RVmodel.cpp:1457-1475) through ``Oracle.true_anomaly``, the
 covariance is calculate_C's (``Oracle.cov``: sig^2 + jitter^2 on the diagonal,
@@ -19,7 +19,7 @@ Parity pinned: against pykima's keplerian() and GP.predict() run in the build co
 from __future__ import annotations
 
 import numpy as np
-from scipy.linalg import cho_factor, cho_solve
+from scipy.linalg import cho_factor, cho_solve, cholesky, solve_triangular
 
 from kima_b200.flags import ModelFlags
 from .oracle import Oracle
@@ -77,3 +77,20 @@ def gp_mean(orc: Oracle, flags: ModelFlags, data, P, b: int, np_b: int, t=None) 
         return np.full(tt.size, np.nan)
     eta = [P[L["row_eta"] + k, b] for k in range(4)]
     return qp_kernel(eta, tt, data.t) @ alpha
+
+
+def gp_std(orc: Oracle, flags: ModelFlags, data, P, b: int, np_b: int, t=None) -> np.ndarray:
+    """GP.py:113-131 (return_std=True): sqrt(k(t*,t*) - k(t*,t) C^-1 k(t,t*)), negative variances
+    set to zero; NaN where C is not positive definite.  pykima forms C^-1 explicitly; here
+    |L^-1 k(t,t*)|^2 by forward substitution (the same number, better conditioned)."""
+    L = orc.layout()
+    tt = data.t if t is None else np.asarray(t, np.float64)
+    C = orc.cov(P, b)
+    try:
+        Lc = cholesky(C, lower=True)
+    except np.linalg.LinAlgError:
+        return np.full(tt.size, np.nan)
+    eta = [P[L["row_eta"] + k, b] for k in range(4)]
+    v = solve_triangular(Lc, qp_kernel(eta, data.t, tt), lower=True)
+    var = eta[0] ** 2 - np.einsum("ij,ij->j", v, v)
+    return np.sqrt(np.maximum(var, 0.0))

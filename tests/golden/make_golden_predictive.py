@@ -53,6 +53,7 @@ def main():
         model_grid = np.zeros((B, nt))
         model_data = np.zeros((B, N))
         gp_grid = np.zeros((B, nt))
+        gp_std = np.zeros((B, nt))
         for b in range(B):
             v = np.zeros(nt)
             vd = np.zeros(N)
@@ -77,8 +78,9 @@ def main():
                 jit = P[L["row_jit"], b]
                 g = gpm.GP(gpm.QPkernel(*eta), d.t, d.sig ** 2 + jit ** 2, white_noise=0.0)
                 gp_grid[b] = g.predict(d.y - vd, tg, return_std=False)
+                gp_std[b] = g.predict(d.y - vd, tg, return_std=True)[1]   # GP.py:113-131
         np.savez_compressed(os.path.join(HERE, name + ".npz"), t=d.t, y=d.y, sig=d.sig, params=P, nps=nps,
-                            tgrid=tg, model_grid=model_grid, model_data=model_data, gp_grid=gp_grid,
+                            tgrid=tg, model_grid=model_grid, model_data=model_data, gp_grid=gp_grid, gp_std=gp_std,
                             flags=json.dumps({k: int(getattr(flags, k)) for k in flags.__dataclass_fields__}))
         print(name, "N=%d B=%d nt=%d  max|model|=%.3g max|gp|=%.3g" % (N, B, nt, np.abs(model_grid).max(), np.abs(gp_grid).max()))
 

@@ -119,6 +119,72 @@ def run_rank(name, d, threads, rank, world, local, port, host_threads, seed=43, 
     return {"wall_s": wall, "mcmc_steps": steps, "run_s": _run_seconds(r.stderr)}
 
 
+PARITY_OPTS = "2\n50\n10\n5\n0\n1\n100\n600\n"  # lambda = 1: lagging particles get replaced early and often
+PARITY_FILES = ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt")
+
+
+def chains_equal_check(rank, world, local, port, exch, name="BL2009", lanes=16, seed=43):
+    """The parity bit of the multi-GPU sampler leg (every rank calls this): `world` ranks x lanes/world
+    lanes must write, byte for byte, the files of one process x `lanes` lanes, with host proposals
+    (the reference's mt19937 chains) and with device proposals (per-lane Philox streams).  Rank 0
+    runs the single-process twin and compares."""
+    import torch.distributed as dist
+    exe = os.path.join(BUILD, "kima_gpu_%s" % name)
+    out = {"example": name, "lanes": lanes, "ranks": world, "seed": seed, "files": list(PARITY_FILES)}
+    for mode, extra in (("host_proposals", {}), ("device_proposals", {"KIMA_DEVICE_PROPOSALS": "1"})):
+        box = [None]
+        if rank == 0:
+            dirs = []
+            for tag in ("one", "ranks"):
+                d = tempfile.mkdtemp(prefix="kima_parity_%s_%s_" % (mode, tag))
+                for f in DATA[name]:
+                    shutil.copy(os.path.join(E2E, f), d)
+                with open(os.path.join(d, "OPTIONS"), "w") as fh:
+                    fh.write(PARITY_OPTS)
+                dirs.append(d)
+            e = dict(os.environ, KIMA_CUDA_DEVICE=str(local))
+            for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+                e.pop(k, None)
+            e.update(extra)
+            r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=dirs[0], capture_output=True,
+                               text=True, timeout=300, env=e)
+            if r.returncode != 0:
+                out[mode] = {"error": "single process: " + (r.stdout[-300:] + r.stderr[-300:])}
+                dirs = None
+            box = [dirs]
+        dist.broadcast_object_list(box, src=0)
+        dirs = box[0]
+        if dirs is None:
+            continue
+        dist.barrier()
+        e = dict(os.environ, RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(local),
+                 MASTER_PORT=str(port + (1 if extra else 0)))
+        e.pop("KIMA_CUDA_DEVICE", None)
+        e.update(extra)
+        bad = 0.0
+        try:
+            r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=dirs[1], capture_output=True,
+                               text=True, timeout=300, env=e)
+            bad = 0.0 if r.returncode == 0 else 1.0
+        except subprocess.TimeoutExpired:
+            bad = 1.0
+        bad = exch.max_float(bad)
+        if rank == 0:
+            if bad:
+                out[mode] = {"error": "a rank failed"}
+            else:
+                eq = {f: open(os.path.join(dirs[0], f), "rb").read() == open(os.path.join(dirs[1], f), "rb").read()
+                      for f in PARITY_FILES}
+                rows = sum(1 for _ in open(os.path.join(dirs[1], "sample.txt"))) - 1
+                out[mode] = {"chains_equal": all(eq.values()), "per_file": eq, "saved_particles": rows}
+            for d in dirs:
+                shutil.rmtree(d, ignore_errors=True)
+    if rank == 0:
+        out["chains_equal"] = all(isinstance(out.get(m), dict) and out[m].get("chains_equal") is True
+                                  for m in ("host_proposals", "device_proposals"))
+    return out
+
+
 def compare(name, lanes, cores, gpu_saves=20, cpu_saves=20, thread_steps=100, env=None):
     cpu = run("cpu", name, cores, thread_steps, cpu_saves)
     gpu = run("gpu", name, lanes, thread_steps, gpu_saves, env=env)
