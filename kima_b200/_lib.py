@@ -9,11 +9,12 @@ from .flags import CLayout, CModelFlags
 from .sampler_types import SAMPLER_SIGNATURES
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libkima_cuda.so")
+# KIMA_CUDA_LIB: a developer build of the same library (e.g. with the in-kernel phase profile)
+LIB_PATH = os.environ.get("KIMA_CUDA_LIB") or os.path.join(HERE, "libkima_cuda.so")
 
 KC_OK = 0
 KC_ERR_ARG, KC_ERR_CUDA, KC_ERR_UNSUPPORTED, KC_ERR_COMM = 1, 2, 3, 4
-KC_PRED_MODEL, KC_PRED_GP = 1, 2
+KC_PRED_MODEL, KC_PRED_GP, KC_PRED_GP_STD = 1, 2, 4
 
 
 class KimaCudaError(RuntimeError):
@@ -58,6 +59,7 @@ SIGNATURES = {
     "kc_model_mu": (ctypes.c_int, [_vp, ctypes.c_int, _dp]),
     "kc_gp_cov": (ctypes.c_int, [_vp, ctypes.c_int, _dp]),
     "kc_predict": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _dp, ctypes.c_int, _dp, _dp]),
+    "kc_predict_std": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _dp, _dp, _dp]),
     "kc_comm_unique_id": (ctypes.c_int, [_vp]),
     "kc_comm_init": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _vp]),
     "kc_allgather_above": (ctypes.c_int, [_vp, _dp, ctypes.c_int, _dp, ctypes.c_int,

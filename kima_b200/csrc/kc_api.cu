@@ -544,25 +544,29 @@ int kc_gp_cov(kc_ctx* c, int lane, double* C)
     return KC_OK;
 }
 
-int kc_predict(kc_ctx* c, int B, int nt, const double* t_pred, int what, double* model_out,
-               double* gp_out)
+static int predict_impl(kc_ctx* c, int B, int nt, const double* t_pred, int what, double* model_out,
+                        double* gp_out, double* std_out)
 {
     int rc = check_ready(c, B);
     if (rc) return rc;
     const bool want_model = (what & KC_PRED_MODEL) != 0, want_gp = (what & KC_PRED_GP) != 0;
-    if (!want_model && !want_gp) return fail(KC_ERR_ARG, "what must name KC_PRED_MODEL and/or KC_PRED_GP");
-    if (what & ~(KC_PRED_MODEL | KC_PRED_GP)) return fail(KC_ERR_ARG, "unknown bits in what");
+    const bool want_std = (what & KC_PRED_GP_STD) != 0;
+    if (!want_model && !want_gp && !want_std)
+        return fail(KC_ERR_ARG, "what must name KC_PRED_MODEL, KC_PRED_GP and/or KC_PRED_GP_STD");
+    if (what & ~(KC_PRED_MODEL | KC_PRED_GP | KC_PRED_GP_STD)) return fail(KC_ERR_ARG, "unknown bits in what");
     if (nt <= 0) return fail(KC_ERR_ARG, "nt <= 0");
     if (!t_pred && nt != c->N) return fail(KC_ERR_ARG, "t_pred is null (the data epochs) but nt != N");
     if (want_model && !model_out) return fail(KC_ERR_ARG, "model_out is null");
     if (want_gp && !gp_out) return fail(KC_ERR_ARG, "gp_out is null");
-    if (want_gp && !(c->F.GP && c->F.kernel == 0))
-        return fail(KC_ERR_UNSUPPORTED, "KC_PRED_GP needs GP=true with the standard kernel");
+    if (want_std && !std_out) return fail(KC_ERR_ARG, "gp_std_out is null");
+    if ((want_gp || want_std) && !(c->F.GP && c->F.kernel == 0))
+        return fail(KC_ERR_UNSUPPORTED, "KC_PRED_GP / KC_PRED_GP_STD need GP=true with the standard kernel");
     if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is in flight");
     CU(cudaSetDevice(c->device));
     if (B == 0) return KC_OK;
     const size_t out_d = (size_t)B * nt;
-    const size_t need = (size_t)nt + (want_model ? out_d : 0) + (want_gp ? out_d + (size_t)B * c->N : 0);
+    const size_t need = (size_t)nt + (want_model ? out_d : 0) + (want_gp ? out_d + (size_t)B * c->N : 0) +
+                        (want_std ? out_d : 0);
     if (need > c->pred_doubles) {
         CU(cudaStreamSynchronize(c->stream));
         cudaFree(c->d_pred);
@@ -575,6 +579,7 @@ int kc_predict(kc_ctx* c, int B, int nt, const double* t_pred, int what, double*
     double* d_model = d_t + nt;
     double* d_gp = d_model + (want_model ? out_d : 0);
     double* d_alpha = d_gp + (want_gp ? out_d : 0);
+    double* d_std = d_alpha + (want_gp ? (size_t)B * c->N : 0);
     if (t_pred) CU(cudaMemcpyAsync(d_t, t_pred, sizeof(double) * nt, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
                          sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
@@ -585,8 +590,8 @@ int kc_predict(kc_ctx* c, int B, int nt, const double* t_pred, int what, double*
     cudaError_t e = cudaSuccess;
     if (want_model)
         e = kc::launch_predict_model(p, c->kepler_mode, t_pred ? d_t : nullptr, nt, d_model, c->stream, &n);
-    if (e == cudaSuccess && want_gp) {
-        kc::GpPredict pr{t_pred ? d_t : nullptr, nt, d_alpha, d_gp};
+    if (e == cudaSuccess && (want_gp || want_std)) {
+        kc::GpPredict pr{t_pred ? d_t : nullptr, nt, d_alpha, want_gp ? d_gp : nullptr, want_std ? d_std : nullptr};
         e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n, &pr);
     }
     if (e != cudaSuccess) return fail_cuda(e, "predict launch");
@@ -595,8 +600,21 @@ int kc_predict(kc_ctx* c, int B, int nt, const double* t_pred, int what, double*
     c->launches += n;
     if (want_model) CU(cudaMemcpyAsync(model_out, d_model, sizeof(double) * out_d, cudaMemcpyDeviceToHost, c->stream));
     if (want_gp) CU(cudaMemcpyAsync(gp_out, d_gp, sizeof(double) * out_d, cudaMemcpyDeviceToHost, c->stream));
+    if (want_std) CU(cudaMemcpyAsync(std_out, d_std, sizeof(double) * out_d, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     return KC_OK;
+}
+
+int kc_predict(kc_ctx* c, int B, int nt, const double* t_pred, int what, double* model_out,
+               double* gp_out)
+{
+    if (what & KC_PRED_GP_STD) return fail(KC_ERR_ARG, "KC_PRED_GP_STD goes through kc_predict_std");
+    return predict_impl(c, B, nt, t_pred, what, model_out, gp_out, nullptr);
+}
+
+int kc_predict_std(kc_ctx* c, int B, int nt, const double* t_pred, double* gp_out, double* gp_std_out)
+{
+    return predict_impl(c, B, nt, t_pred, (gp_out ? KC_PRED_GP : 0) | KC_PRED_GP_STD, nullptr, gp_out, gp_std_out);
 }
 
 }  // extern "C"

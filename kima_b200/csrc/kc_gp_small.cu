@@ -49,6 +49,7 @@ struct Hdr {
     int ld[MAXBLK];
     int gen_end[MAXBLK];
     int gen_next, u_done, d_done, col_done;
+    int tile_cnt[MAXBLK + 1];  // block column 0: finished generation items per 32-row tile
 };
 
 __host__ __device__ inline int ld_for(int rows) { return ((rows + 11) & ~15) + 4; }  // >= rows, = 4 mod 16
@@ -72,8 +73,22 @@ namespace {
 
 using namespace gps;
 
-template <int NW>
-__device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"((NW - 1) * 32) : "memory"); }
+// switches of the schedule (each measured on a B200, profiles/gps_variants_r02.txt)
+#ifndef KC_GPS_ISOLATE
+#define KC_GPS_ISOLATE 0    // 16-warp CTAs: warps 4, 8, 12 (the diag warp's scheduler) stay idle
+#endif
+#ifndef KC_GPS_LOOKAHEAD
+#define KC_GPS_LOOKAHEAD 1  // U_J: the strips of the diagonal block first, then the diag warp starts
+#endif
+#ifndef KC_GPS_TILEGEN
+#define KC_GPS_TILEGEN 0    // block column 0: factorisation / substitution start per generated tile
+#endif
+template <int WORKERS>
+__device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"(WORKERS * 32) : "memory"); }
+__device__ __forceinline__ void red_release_add(int* p, int v)
+{
+    asm volatile("red.release.cta.shared.add.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
 // warp-uniform read of a flag / counter in shared memory
 __device__ __forceinline__ int ld_uniform(const int* p, int lane)
 {
@@ -113,6 +128,12 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
             if (cb <= row && cb < N) dst[(size_t)(cc + 1) * ldj] = vb;
         }
     }
+#if KC_GPS_TILEGEN
+    if (J == 0) {
+        __syncwarp();
+        if (lane == 0) red_release_add(&H.tile_cnt[I], 1);
+    }
+#endif
 }
 
 __device__ __forceinline__ int claim(Hdr& H, int lane)
@@ -256,7 +277,8 @@ template <int MODE, int NW>
 __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const KParams p)
 {
     constexpr int THREADS = NW * 32;
-    constexpr int WORKERS = NW - 1;
+    constexpr bool ISO = KC_GPS_ISOLATE && NW == 16;
+    constexpr int WORKERS = ISO ? NW - 4 : NW - 1;
     extern __shared__ __align__(16) unsigned char gps_smem[];
     Hdr& H = *reinterpret_cast<Hdr*>(gps_smem);
     const int N = p.N;
@@ -282,6 +304,7 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             }
             H.gen_next = 0; H.u_done = 0; H.d_done = 0; H.col_done = 0;
             H.quad = 0.0;
+            for (int I = 0; I <= MAXBLK; I++) H.tile_cnt[I] = 0;
         }
     }
     __syncthreads();
@@ -346,6 +369,10 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
         // ---- diag role ----
         for (int J = 0; J < nb; J++) {
             const int j0 = T * J;
+#if KC_GPS_TILEGEN
+            if (J == 0) while (ld_uniform(&H.tile_cnt[0], lane) < GQ) __nanosleep(KC_GPS_SLEEP_D);
+            else
+#endif
             while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(KC_GPS_SLEEP_D);
             PROF(0);
             const int nv = min(T, N - j0);
@@ -356,9 +383,9 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             if (lane == 0) st_release_cta(&H.d_done, J + 1);
             PROF(1);
         }
-    } else {
+    } else if (!(ISO && (warp & 3) == 0)) {
         // ---- worker role ----
-        const int wid = warp - 1;
+        const int wid = ISO ? warp - 1 - (warp >> 2) : warp - 1;
         for (int J = 0; J < nb; J++) {
             const int j0 = T * J;
             const int nbc = min(T, N - j0);
@@ -367,12 +394,26 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
                 const int it = claim(H, lane);
                 if (it < total_items) gen_item(H, tS, nS, M, N, it, nb, lane);
             }
-            worker_bar<NW>();
+#if KC_GPS_TILEGEN
+            if (J > 0)   // block column 0 is followed tile by tile (tile_cnt), not as a whole
+#endif
+            worker_bar<WORKERS>();
             PROF(0);
             if (J > 0) {
                 const int nstrips = (N + 1 - j0 + 7) / 8;
+#if KC_GPS_LOOKAHEAD
+                // the four strips of the diagonal block first: the diag warp starts while the
+                // rows below are still being updated
+                const int ndiag = min(4, nstrips);
+                for (int s = wid; s < ndiag; s += WORKERS) update_strip(H, M, N, J, s, lane);
+                worker_bar<WORKERS>();
+                if (wid == 0 && lane == 0) st_release_cta(&H.u_done, J + 1);
+                for (int s = ndiag + wid; s < nstrips; s += WORKERS) update_strip(H, M, N, J, s, lane);
+                worker_bar<WORKERS>();
+#else
                 for (int s = wid; s < nstrips; s += WORKERS) update_strip(H, M, N, J, s, lane);
-                worker_bar<NW>();
+                worker_bar<WORKERS>();
+#endif
             }
             PROF(1);
             if (wid == 0 && lane == 0) st_release_cta(&H.u_done, J + 1);
@@ -381,7 +422,14 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             const int first = j0 + nbc;
             const int ntiles = (N + 1 - first + T - 1) / T;
             if (wid < ntiles) {
-                for (int tl = wid; tl < ntiles; tl += WORKERS) trsm_tile(H, M, N, J, nbc, tl, lane);
+                for (int tl = wid; tl < ntiles; tl += WORKERS) {
+#if KC_GPS_TILEGEN
+                    // every item of block column 0 has been claimed by now: the tile completes without us
+                    if (J == 0 && tl + 1 < nb)
+                        while (ld_uniform(&H.tile_cnt[tl + 1], lane) < GQ) __nanosleep(KC_GPS_SLEEP_T);
+#endif
+                    trsm_tile(H, M, N, J, nbc, tl, lane);
+                }
             } else {
                 while (ld_uniform(&H.d_done, lane) < J + 1) {
                     if (ld_uniform(&H.gen_next, lane) < total_items) {
@@ -393,7 +441,7 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
                 }
             }
             PROF(2);
-            worker_bar<NW>();
+            worker_bar<WORKERS>();
             PROF(3);
         }
     }

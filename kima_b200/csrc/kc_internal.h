@@ -64,7 +64,8 @@ struct GpPredict {
     const double* t_pred;  // device [nt], null = the data epochs
     int nt;
     double* alpha;         // device [B][N]: C^-1 r per lane
-    double* gp_out;        // device [B][nt]
+    double* gp_out;        // device [B][nt], null = no mean
+    double* std_out;       // device [B][nt], null = no predictive standard deviation
 };
 size_t gpb_ld(int N);
 size_t gpb_slot_doubles(int N);

@@ -153,6 +153,19 @@ class LikelihoodEngine:
                                        None if m is None else _d(m), None if g is None else _d(g)))
         return m, g
 
+    def predict_std(self, params: np.ndarray, nps: np.ndarray, t: Optional[np.ndarray] = None,
+                    mean: bool = True):
+        """GP predictive mean and standard deviation, pykima's ``GP.predict(y, t, return_std=True)``
+        (pykima/GP.py:113-131) for every parameter vector.  Returns ``(mean[B, nt] | None, std[B, nt])``."""
+        B = self.set_params(params, nps)
+        tt = None if t is None else np.ascontiguousarray(t, np.float64)
+        nt = self.data.N() if tt is None else tt.size
+        g = np.empty((B, nt)) if mean else None
+        sd = np.empty((B, nt))
+        _lib.check(self.lib.kc_predict_std(self._ctx, B, nt, None if tt is None else _d(tt),
+                                           None if g is None else _d(g), _d(sd)))
+        return g, sd
+
     @staticmethod
     def likelihood_type_value(logL: np.ndarray) -> np.ndarray:
         """What DNest4's LikelihoodType stores (LikelihoodType.cpp:17-24)."""

@@ -141,6 +141,21 @@ class PosteriorPredictive:
             return np.zeros((S.shape[0], self.data.N() if t is None else np.asarray(t).size))
         return self._run(samples, t, False, True)[1]
 
+    def model_stochastic_std(self, samples, t: Optional[np.ndarray] = None):
+        """GP predictive mean and standard deviation, ``GP.predict_with_hyperpars(..., return_std=True)``
+        (pykima/GP.py:134-175, :113-131), one row per sample: ``(mean, std)``."""
+        if not self.flags.GP:
+            raise ValueError("model_stochastic_std needs a GP model")
+        P, nps = params_from_samples(samples, self.flags, self.data.number_instruments,
+                                     self.data.number_indicators)
+        B = P.shape[1]
+        nt = self.data.N() if t is None else np.asarray(t).size
+        g, sd = np.empty((B, nt)), np.empty((B, nt))
+        for lo in range(0, B, self.max_batch):
+            hi = min(B, lo + self.max_batch)
+            g[lo:hi], sd[lo:hi] = self.engine.predict_std(P[:, lo:hi], nps[lo:hi], t)
+        return g, sd
+
     def full_model(self, samples, t: Optional[np.ndarray] = None) -> np.ndarray:
         """Deterministic part + GP predictive mean (results.py:832-855)."""
         m, g = self._run(samples, t, True, bool(self.flags.GP))

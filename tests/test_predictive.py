@@ -50,6 +50,10 @@ def test_oracle_predictive_against_pykima(name):
         if flags.GP:
             g = opred.gp_mean(orc, flags, data, P, b, nps[b], z["tgrid"])
             assert np.max(np.abs(g - z["gp_grid"][b])) <= 1e-8 * (np.abs(z["gp_grid"][b]).max() + 1.0)
+            # return_std=True (GP.py:113-131): pykima forms C^-1 explicitly, which costs it digits
+            sd = opred.gp_std(orc, flags, data, P, b, nps[b], z["tgrid"])
+            eta1 = P[orc.layout()["row_eta"], b]
+            assert np.max(np.abs(sd ** 2 - z["gp_std"][b] ** 2)) <= 1e-7 * eta1 ** 2
 
 
 @pytest.mark.parametrize("example,flags,n_inst", [
@@ -110,6 +114,54 @@ def test_gpu_predict_against_pykima_and_oracle(gpu, name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name", ["predictive_gp_N60", "predictive_gp_N300_trend"])
+def test_gpu_predict_std_against_pykima_and_oracle(gpu, name):
+    """kc_predict_std: GP.predict(return_std=True), pykima/GP.py:113-131."""
+    z, flags, data = load_case(name)
+    P, nps = z["params"], z["nps"]
+    B = nps.size
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    eta1 = P[orc.layout()["row_eta"]]
+    with LikelihoodEngine(data, flags, B) as eng:
+        g, sd = eng.predict_std(P, nps, z["tgrid"])
+        _, sdd = eng.predict_std(P, nps, None, mean=False)
+        _, g0 = eng.predict(P, nps, z["tgrid"], model=False)
+    assert np.array_equal(g, g0)   # the mean of kc_predict_std is kc_predict's
+    for b in range(B):
+        var = eta1[b] ** 2
+        want = opred.gp_std(orc, flags, data, P, b, nps[b], z["tgrid"])
+        assert np.max(np.abs(sd[b] ** 2 - want ** 2)) <= 1e-8 * var, b
+        assert np.max(np.abs(sd[b] ** 2 - z["gp_std"][b] ** 2)) <= 1e-7 * var, b
+        wd = opred.gp_std(orc, flags, data, P, b, nps[b])
+        assert np.max(np.abs(sdd[b] ** 2 - wd ** 2)) <= 1e-8 * var, b
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,B,nt,slots", [(1000, 6, 333, 4), (97, 40, 50, 7), (2100, 2, 21, 0)])
+def test_gpu_predict_std_sizes_and_waves(gpu, N, B, nt, slots):
+    """N=1000 (16 right-hand sides per tile), N=2100 (8 per tile), waves of the factor storage,
+    grid sizes that are no multiple of the tile, a lane whose C is not positive definite."""
+    flags = ModelFlags(GP=True, npmax=1)
+    data = make_data(N)
+    P, nps = make_params(flags, data, B, "mix", seed=5)
+    L = None
+    tg = np.linspace(data.t.min() - 3.0, data.t.max() + 3.0, nt)
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    L = orc.layout()
+    P[L["row_jit"], 1] = np.nan
+    with LikelihoodEngine(data, flags, B, gp_slots=slots) as eng:
+        g, sd = eng.predict_std(P, nps, tg)
+    assert np.all(np.isnan(sd[1])) and np.all(np.isnan(g[1]))
+    for b in {0, B - 1} - {1}:
+        want = opred.gp_std(orc, flags, data, P, b, nps[b], tg)
+        assert np.max(np.abs(sd[b] ** 2 - want ** 2)) <= 1e-8 * P[L["row_eta"], b] ** 2
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("flags,N,n_inst,n_ind", [
     (ModelFlags(GP=True, npmax=2, multi_instrument=True), 97, 3, 0),
     (ModelFlags(GP=True, npmax=1, known_object=True, n_known_object=2, trend=True, degree=3), 130, 1, 1),
@@ -157,6 +209,11 @@ def test_gpu_posterior_predictive_from_sample_rows(gpu):
         s = pp.model_stochastic(rows, tg)
         f = pp.full_model(rows, tg)
         res = pp.residuals(rows, full=True)
+        s2, sd = pp.model_stochastic_std(rows, tg)
+    assert np.array_equal(s2, s)
+    for b in range(rows.shape[0]):
+        want = opred.gp_std(orc, flags, data, P, b, nps[b], tg)
+        assert np.max(np.abs(sd[b] ** 2 - want ** 2)) <= 1e-8 * P[orc.layout()["row_eta"], b] ** 2
     assert m.shape == (rows.shape[0], 400)
     np.testing.assert_allclose(f, m + s, rtol=0, atol=1e-9)
     for b in range(rows.shape[0]):
