@@ -8,6 +8,8 @@
 // is still an RVmodel object held by the Sampler; `stage` copies its parameters into one
 // column of libkima_cuda's pinned SoA block (include/kima_cuda.h, kc_layout).
 #pragma once
+#include <sys/stat.h>
+#include <ctime>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -334,15 +336,25 @@ private:
             f(0, n);
     }
     // NCCL's unique id travels through a file in the run directory (all ranks of one node
-    // share it): rank 0 writes it atomically, the others wait for it.
+    // share it): rank 0 writes it atomically, the others wait for it.  A file left behind by a
+    // killed run must not be taken for this run's: the name carries the launcher's run id when
+    // there is one (KIMA_RUN_NONCE, else TORCHELASTIC_RUN_ID), rank 0 unlinks before it writes,
+    // and the other ranks only accept a file written after their own start (minus a margin for
+    // ranks that start late).
     void comm_bootstrap()
     {
         const char* tag = std::getenv("KIMA_COMM_ID_FILE");
         std::string path = tag ? tag : ".kima_nccl_id";
-        if (!tag)
+        if (!tag) {
             if (const char* port = std::getenv("MASTER_PORT")) path += std::string(".") + port;
+            const char* nonce = std::getenv("KIMA_RUN_NONCE");
+            if (!nonce) nonce = std::getenv("TORCHELASTIC_RUN_ID");
+            if (nonce) path += std::string(".") + nonce;
+        }
+        const time_t started = std::time(nullptr);
         unsigned char id[128];
         if (rank_ == 0) {
+            std::remove(path.c_str());
             kimacuda::Context::unique_id(id);
             const std::string tmp = path + ".tmp";
             {
@@ -352,8 +364,11 @@ private:
             std::rename(tmp.c_str(), path.c_str());
         } else {
             for (int tries = 0;; tries++) {
-                std::ifstream f(path, std::ios::binary);
-                if (f && f.read((char*)id, 128)) break;
+                struct stat sb;
+                if (::stat(path.c_str(), &sb) == 0 && sb.st_mtime + 300 >= started) {
+                    std::ifstream f(path, std::ios::binary);
+                    if (f && f.read((char*)id, 128)) break;
+                }
                 if (tries > 6000) throw std::runtime_error("timed out waiting for " + path);
                 std::this_thread::sleep_for(std::chrono::milliseconds(10));
             }

@@ -1,6 +1,7 @@
-// Test set-up (ours): MA(1) term + cubic trend, no planets.  With npmax = 0 the reference
-// never takes the incremental-update branch of calculate_mu (src/RVmodel.cpp:296), so its
-// MA term is the from-scratch one (:378-386) and the chains are comparable.
+// Test set-up (ours): MA(1) term + cubic trend, no planets.  The reference's perturb() still
+// patches mu incrementally for vsys / trend moves without redoing the MA term
+// (src/RVmodel.cpp:548-604), so its chain depends on each particle's history and is NOT expected
+// to equal a stateless evaluator's: the test checks files, columns and the first saved particle.
 #include "kima.h"
 
 const bool GP = false;

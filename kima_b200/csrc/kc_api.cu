@@ -143,13 +143,18 @@ int kc_create(int device, kc_ctx** out)
     CU(cudaSetDevice(device));
     kc_ctx* c = new kc_ctx();
     c->device = device;
+    // a failure half-way leaves nothing behind: kc_destroy tolerates the null members
+    auto bail = [&](cudaError_t err, const char* what) {
+        kc_destroy(c);
+        return fail_cuda(err, what);
+    };
     cudaDeviceProp prop;
-    CU(cudaGetDeviceProperties(&prop, device));
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
     c->sm_count = prop.multiProcessorCount;
-    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU(cudaEventCreate(&c->ev0));
-    CU(cudaEventCreate(&c->ev1));
-    CU(cudaMalloc(&c->d_counter, 64));
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaMalloc(&c->d_counter, 64)) != cudaSuccess) return bail(e, "cudaMalloc");
     *out = c;
     return KC_OK;
 }
@@ -158,7 +163,7 @@ int kc_destroy(kc_ctx* c)
 {
     if (!c) return KC_OK;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    if (c->stream) cudaStreamSynchronize(c->stream);
     kc_comm_destroy(c);
     free_model(c);
     free_data(c);
@@ -166,11 +171,11 @@ int kc_destroy(kc_ctx* c)
     cudaFree(c->d_comm_buf);
     cudaFree(c->d_flush);
     cudaFree(c->d_pred);
-    cudaEventDestroy(c->ev0);
-    cudaEventDestroy(c->ev1);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->copy_ev) cudaEventDestroy(c->copy_ev);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
-    cudaStreamDestroy(c->stream);
+    if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return KC_OK;
 }

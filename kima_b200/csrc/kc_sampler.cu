@@ -375,7 +375,16 @@ int kc_prior_make(int type, const double* p, int n_p, kc_prior* out)
     return KC_OK;
 }
 
+static int sampler_create_impl(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_config* cfg);
+
 int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_config* cfg)
+{
+    const int rc = sampler_create_impl(c, priors, cfg);
+    if (rc != KC_OK && c) kc::sampler_free(c);  // no half-built sampler behind a failed call
+    return rc;
+}
+
+static int sampler_create_impl(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_config* cfg)
 {
     if (!c || !priors || !cfg) return fail(KC_ERR_ARG, "null argument");
     int rc = kc::check_ready(c, 0);

@@ -128,15 +128,17 @@ class NcclBarrierExchange:
         return c
 
 
-def merge_above_and_create_level(all_above: np.ndarray, new_level_interval: int):
+def merge_above_and_create_level(all_above: np.ndarray, new_level_interval: int,
+                                 compression: float = float(np.e)):
     """The level-creation rule of do_bookkeeping (SamplerImpl.h:382-399): once
     `all_above` holds at least new_level_interval entries, sort them by
-    (value, tiebreaker), cut the new level at index (1 - 1/e) * size and keep
+    (value, tiebreaker), cut the new level at index (1 - 1/compression) * size
+    (`compression` is the run's -c option, e by default, SamplerImpl.h:389) and keep
     the entries above it.  Returns (new_level or None, remaining above)."""
     a = np.asarray(all_above, np.float64).reshape(-1, 2)
     if a.shape[0] < new_level_interval:
         return None, a
     order = np.lexsort((a[:, 1], a[:, 0]))
     a = a[order]
-    idx = int((1.0 - 1.0 / np.e) * a.shape[0])
+    idx = int((1.0 - 1.0 / compression) * a.shape[0])
     return a[idx].copy(), a[idx + 1:].copy()

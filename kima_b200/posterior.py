@@ -131,7 +131,14 @@ class PosteriorPredictive:
         return m, g
 
     def model(self, samples, t: Optional[np.ndarray] = None) -> np.ndarray:
-        """Deterministic part (results.py:723-797), one row per sample."""
+        """Deterministic part (results.py:723-797), one row per sample.
+
+        Deviation from pykima at the data epochs (``t=None``): this is the C++ likelihood's
+        ``calculate_mu`` without the MA term, so it also holds the indicator (beta) terms and the
+        known-object Keplerians, and the instrument offsets whenever ``multi_instrument`` is set;
+        pykima's ``model()`` adds neither betas nor known objects and adds offsets only for
+        multi-file data.  On a grid ``t`` the two agree except for known objects (included here).
+        ``residuals`` inherits the difference: it is y minus what the likelihood subtracts."""
         return self._run(samples, t, True, False)[0]
 
     def model_stochastic(self, samples, t: Optional[np.ndarray] = None) -> np.ndarray:

@@ -178,6 +178,20 @@ class Oracle:
         getattr(self.lib, self.p + "cov")(params.shape[1], _d(params), b, 0, _d(C))
         return C.T.copy()  # column-major -> C[i, j]
 
+    def celerite_predict(self, params, b: int, np_b: int, x):
+        """kernel=celerite: the reference solver's own conditional mean at the sorted times x
+        (CholeskySolver::predict, celerite/.../solver/cholesky.h:590-690).  Reference kind only."""
+        if self.kind != "reference":
+            raise RuntimeError("celerite_predict calls the reference's solver: Oracle('reference') only")
+        params = np.ascontiguousarray(params, np.float64)
+        x = np.ascontiguousarray(x, np.float64)
+        out = np.zeros(x.size)
+        fn = self.lib.ref_celerite_predict
+        fn.restype = ctypes.c_int
+        rc = fn(ctypes.c_int(params.shape[1]), _d(params), ctypes.c_int(b), ctypes.c_int(int(np_b)),
+                ctypes.c_int(x.size), _d(x), _d(out))
+        return out if rc == 0 else np.full(x.size, np.nan)
+
     def kepler(self, M, ecc):
         M = np.ascontiguousarray(M, np.float64)
         ecc = np.ascontiguousarray(ecc, np.float64)

@@ -94,3 +94,147 @@ def gp_std(orc: Oracle, flags: ModelFlags, data, P, b: int, np_b: int, t=None) -
     v = solve_triangular(Lc, qp_kernel(eta, data.t, tt), lower=True)
     var = eta[0] ** 2 - np.einsum("ij,ij->j", v, v)
     return np.sqrt(np.maximum(var, 0.0))
+
+
+# ---- kernel = celerite ----------------------------------------------------------------------------
+def celerite_terms(eta):
+    """The three complex terms of kima's quasi-periodic approximation (src/RVmodel.cpp:231-250):
+    (a_comp, b_comp, c_comp, d_comp); the kernel has no eta4."""
+    wbeat, wrot, amp = 1.0 / eta[1], 2.0 * np.pi / eta[2], eta[0] * eta[0]
+    c, d = wbeat, wrot
+    x = c / d
+    a, b, e, f = amp / 2, amp * x / 2, amp / 8, amp * x / 4
+    g = amp * (3.0 / 8.0 + 0.001)
+    return (np.array([a, e, g]), np.array([b, f, 0.0]), np.array([c, c, c]), np.array([d, 2 * d, 0.0]))
+
+
+def celerite_factor(terms, t, diag):
+    """CholeskySolver::compute (celerite/cpp/include/celerite/solver/cholesky.h:95-190) for J = 6
+    complex-term columns: D[N], W[6][N], u[6][N-1], phi[6][N-1]; None if a pivot goes negative."""
+    a_c, b_c, c_c, d_c = terms
+    N, J = t.size, 6
+    D = diag + a_c.sum()
+    W = np.zeros((J, N))
+    u = np.zeros((J, N - 1))
+    phi = np.zeros((J, N - 1))
+    Dn = D[0]
+    for j in range(3):
+        W[2 * j, 0] = np.cos(d_c[j] * t[0]) / Dn
+        W[2 * j + 1, 0] = np.sin(d_c[j] * t[0]) / Dn
+    S = np.zeros((J, J))
+    D = D.copy()
+    for n in range(1, N):
+        dx = t[n] - t[n - 1]
+        for j in range(3):
+            cd, sd = np.cos(d_c[j] * t[n]), np.sin(d_c[j] * t[n])
+            phi[2 * j, n - 1] = phi[2 * j + 1, n - 1] = np.exp(-c_c[j] * dx)
+            u[2 * j, n - 1] = a_c[j] * cd + b_c[j] * sd
+            u[2 * j + 1, n - 1] = a_c[j] * sd - b_c[j] * cd
+            W[2 * j, n], W[2 * j + 1, n] = cd, sd
+        for j in range(J):
+            xj = Dn * W[j, n - 1]
+            for k in range(j + 1):
+                S[k, j] = phi[j, n - 1] * (phi[k, n - 1] * (S[k, j] + xj * W[k, n - 1]))
+        Dn = D[n]
+        for j in range(J):
+            uj, xj = u[j, n - 1], W[j, n]
+            for k in range(j):
+                tmp = u[k, n - 1] * S[k, j]
+                Dn -= 2.0 * (uj * tmp)
+                xj -= tmp
+                W[k, n] -= uj * S[k, j]
+            tmp = uj * S[j, j]
+            Dn -= uj * tmp
+            W[j, n] = xj - tmp
+        if Dn < 0:
+            return None
+        D[n] = Dn
+        W[:, n] /= Dn
+    return D, W, u, phi
+
+
+def celerite_solve(fac, b):
+    """CholeskySolver::solve (cholesky.h:217-262): forward and backward sweep."""
+    D, W, u, phi = fac
+    N, J = b.size, 6
+    x = b.astype(np.float64).copy()
+    f = np.zeros(J)
+    for n in range(1, N):
+        f = phi[:, n - 1] * (f + W[:, n - 1] * x[n - 1])
+        x[n] = b[n] - u[:, n - 1] @ f
+    x /= D
+    f = np.zeros(J)
+    for n in range(N - 2, -1, -1):
+        f = phi[:, n] * (f + u[:, n] * x[n + 1])
+        x[n] -= W[:, n] @ f
+    return x
+
+
+def celerite_predict(terms, t, alpha, xs):
+    """CholeskySolver::predict (cholesky.h:598-690): O(N + M) forward and backward pass over the
+    sorted prediction times xs."""
+    a_c, b_c, c_c, d_c = terms
+    N, M = t.size, xs.size
+    pred = np.zeros(M)
+    Q = np.zeros(6)
+    m = 0
+    while m < M and xs[m] <= t[0]:
+        m += 1
+    for n in range(N):
+        tref = t[n + 1] if n < N - 1 else t[N - 1]
+        tn = t[n]
+        dt = tref - tn
+        for j in range(3):
+            tmp = np.exp(-c_c[j] * dt)
+            Q[2 * j] = (Q[2 * j] + alpha[n] * np.cos(d_c[j] * tn)) * tmp
+            Q[2 * j + 1] = (Q[2 * j + 1] + alpha[n] * np.sin(d_c[j] * tn)) * tmp
+        while m < M and (n == N - 1 or xs[m] <= tref):
+            xm = xs[m]
+            dt = xm - tref
+            pm = 0.0
+            for j in range(3):
+                cd, sd = np.cos(d_c[j] * xm), np.sin(d_c[j] * xm)
+                tmp = np.exp(-c_c[j] * dt)
+                pm += (a_c[j] * cd + b_c[j] * sd) * tmp * Q[2 * j]
+                pm += (a_c[j] * sd - b_c[j] * cd) * tmp * Q[2 * j + 1]
+            pred[m] = pm
+            m += 1
+    m = M - 1
+    while m >= 0 and xs[m] > t[N - 1]:
+        m -= 1
+    Q = np.zeros(6)
+    for n in range(N - 1, -1, -1):
+        tref = t[n - 1] if n > 0 else t[0]
+        tn = t[n]
+        dt = tn - tref
+        for j in range(3):
+            cd, sd = np.cos(d_c[j] * tn), np.sin(d_c[j] * tn)
+            tmp = np.exp(-c_c[j] * dt)
+            Q[2 * j] = (Q[2 * j] + alpha[n] * (a_c[j] * cd + b_c[j] * sd)) * tmp
+            Q[2 * j + 1] = (Q[2 * j + 1] + alpha[n] * (a_c[j] * sd - b_c[j] * cd)) * tmp
+        while m >= 0 and (n == 0 or xs[m] > tref):
+            xm = xs[m]
+            dt = tref - xm
+            pm = 0.0
+            for j in range(3):
+                tmp = np.exp(-c_c[j] * dt)
+                pm += np.cos(d_c[j] * xm) * tmp * Q[2 * j]
+                pm += np.sin(d_c[j] * xm) * tmp * Q[2 * j + 1]
+            pred[m] += pm
+            m -= 1
+    return pred
+
+
+def gp_mean_celerite(orc: Oracle, flags: ModelFlags, data, P, b: int, np_b: int, t=None) -> np.ndarray:
+    """GP_celerite.predict (pykima/GP.py:349-355) with the C++ likelihood's set-up of the solver
+    (src/RVmodel.cpp:218-266: jitter^2 and sig^2 on the diagonal) and residual y - calculate_mu:
+    K_* (K + sigma)^-1 r through celerite's O(N) recursions; NaN where a pivot goes negative."""
+    L = orc.layout()
+    tt = data.t if t is None else np.asarray(t, np.float64)
+    eta = [P[L["row_eta"] + k, b] for k in range(3)]
+    terms = celerite_terms(eta)
+    fac = celerite_factor(terms, data.t, data.sig ** 2 + P[L["row_jit"], b] ** 2)
+    if fac is None or not np.all(np.isfinite(fac[0])):
+        return np.full(tt.size, np.nan)
+    alpha = celerite_solve(fac, data.y - orc.mu(P, b, np_b))
+    return celerite_predict(terms, data.t, alpha, tt)

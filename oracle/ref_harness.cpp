@@ -295,6 +295,30 @@ int ref_cov(int ld, const double* params, int b, int np, double* C)
     return (int)N;
 }
 
+// kernel=celerite: the conditional mean K_* (K + sigma)^-1 (y - mu) of the reference's own solver,
+// celerite::solver::CholeskySolver::predict (celerite/cpp/include/celerite/solver/cholesky.h:590-690),
+// after calculate_mu / calculate_C have set it up as log_likelihood's celerite branch does
+// (src/RVmodel.cpp:218-266, 875-877).  x must be sorted.  Returns 0, or 1 if the solver threw.
+int ref_celerite_predict(int ld, const double* params, int b, int np, int nt, const double* x, double* out)
+{
+    RVmodel m;
+    set_lane(m, params, ld, b, np);
+    m.calculate_mu();
+    m.calculate_C();
+    const std::vector<double>& y = Data::get_instance().get_y();
+    const int N = (int)y.size();
+    Eigen::VectorXd r(N), xs(nt);
+    for (int i = 0; i < N; i++) r(i) = y[i] - (double)m.mu[i];
+    for (int k = 0; k < nt; k++) xs(k) = x[k];
+    try {
+        Eigen::VectorXd pr = m.solver.predict(r, xs);
+        for (int k = 0; k < nt; k++) out[k] = pr(k);
+    } catch (...) {
+        return 1;
+    }
+    return 0;
+}
+
 int ref_get_layout(kc_layout* out) { *out = g_layout; return 0; }
 
 // What DNest4 does with the value (LikelihoodType.cpp:17-24).

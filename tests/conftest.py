@@ -36,7 +36,7 @@ _build_once()
 def golden_cases():
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
                   if not p.endswith("kepler.npz") and not os.path.basename(p).startswith("predictive_")
-                  and "N4096" not in p)  # the scale point has its own tests (12 s per lane on the CPU)
+                  and "N4096" not in p and not os.path.basename(p).startswith("tail_"))  # the scale point has its own tests (12 s per lane on the CPU)
 
 
 def load_golden(name):

@@ -131,6 +131,25 @@ def test_evidence_at_many_lanes_matches_host_proposals(gpu, tmp_path):
     assert abs(dev.mean() - (-146.0)) < 5.0, z   # the reference's CPU runs give -143.6 ... -147
 
 
+def test_evidence_corot7_gp_matches_host_proposals(gpu, tmp_path):
+    """The GP example (CoRoT7: N=177, hyperpriors, Np <= 5) with device proposals against the
+    host-proposal GPU path at the same -t, which is the reference's own chain
+    (tests/test_host_cpp.py): log Z and the information over two seeds each."""
+    opts = "2\n1000\n500\n100\n0\n10\n100\n600\n"
+    z, H = {True: [], False: []}, {True: [], False: []}
+    for seed in (7, 8):
+        for device in (True, False):
+            d = run("gpu", "CoRoT7", tmp_path, "%s%d" % ("dev" if device else "host", seed), 128, seed, device, opts)
+            zz, _, hh = log_evidence(d)
+            z[device].append(zz)
+            H[device].append(hh)
+    print("CoRoT7 log Z device %s host %s; H device %s host %s" % (z[True], z[False], H[True], H[False]))
+    dev, host = np.array(z[True]), np.array(z[False])
+    spread = max(np.ptp(dev), np.ptp(host))
+    assert abs(dev.mean() - host.mean()) < 2.0 + 2.0 * spread, z
+    assert abs(np.mean(H[True]) - np.mean(H[False])) < 5.0 + 2.0 * max(np.ptp(H[True]), np.ptp(H[False])), H
+
+
 @pytest.mark.parametrize("host_above", ["0", "1"])
 def test_two_ranks_reproduce_the_single_process_device_chain(gpu, tmp_path, host_above):
     """One process per GPU with device proposals: each rank keeps its lanes' particles in its own

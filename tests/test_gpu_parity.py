@@ -50,6 +50,25 @@ def test_golden_logL_mu(gpu, name, mode):
             np.testing.assert_allclose(C, g["C0"], rtol=4e-15, atol=1e-300)
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_ill_conditioned_tail_within_the_reference_bound(gpu, mode):
+    """The 48 worst-conditioned lanes of 65 536 prior draws (e -> 1 with an epoch at periastron:
+    the reference's acos, src/RVmodel.cpp:1467, loses up to 8 digits of f there).  The GPU must
+    stay within 1e-10 |logL| plus the bound derived from the reference's own f, mu and variances
+    (tests/golden/make_golden_tail.py); three of the lanes have a bound above 1e-10 |logL|."""
+    import json
+    z = np.load(os.path.join(GOLDEN, "tail_kep_N200_np5_hyper.npz"))
+    flags = ModelFlags(**{k: (bool(v) if isinstance(getattr(ModelFlags(), k), bool) else int(v))
+                          for k, v in json.loads(str(z["flags"])).items()})
+    d = make_data(200)
+    with LikelihoodEngine(d, flags, z["nps"].size, kepler_mode=mode) as eng:
+        got = eng.evaluate(z["params"], z["nps"])
+    assert (z["bound"] > 1e-10 * np.abs(z["logL"])).sum() >= 3
+    assert np.all(np.abs(got - z["logL"]) <= LOGL_RTOL * np.abs(z["logL"]) + z["bound"])
+    # and the tail is a tail: the median lane of this worst-of-65536 set is still far inside 1e-10
+    assert np.median(relerr(got, z["logL"])) <= 1e-12
+
+
 FLAG_CASES = [
     ("plain_np0", ModelFlags(npmax=0), 57, 1, 0),
     ("np7", ModelFlags(npmax=7), 300, 1, 0),

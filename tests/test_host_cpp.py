@@ -36,7 +36,17 @@ CASES = {
 OWN_SETUPS = {
     "celerite_CoRoT7": ["corot7.txt"],   # kernel = celerite (src/RVmodel.cpp:218-266, 875-882)
     "MA_trend": ["d1.txt"],              # MA(1) term (src/RVmodel.cpp:378-386), cubic trend
+    # BASELINE.json's many_planets variant: npmax 10, hyperpriors, Student-t, four instruments
+    "many_planets_studentt_multi": ["HD106252_ELODIE.txt", "HD106252_HET.txt", "HD106252_HJS.txt",
+                                    "HD106252_Lick.txt"],
+    "activity_indicators": ["simulated2.txt"],   # two indicator columns through Data::load (betas)
+    "BL2009_np5": ["BL2009_dataset2.kms.rv"],    # BASELINE.json: "variable Np up to 5"
+    # shipped examples without a CI fixture (a file of another name in e2e/ is copied as `dst`)
+    "many_planets": ["HD10180.kms.rv"],          # npmax 10, hyperpriors
+    "trends": [("trends_d1.txt", "d1.txt")],     # cubic trend, no planets
 }
+# GPU chain == chain of the reference's CPU binary built from the same set-up, byte for byte
+CHAIN_EQUALITY = ["many_planets", "trends", "many_planets_studentt_multi", "activity_indicators", "BL2009_np5"]
 
 
 def run_example(kind, name, tmp_path, lanes=4, seed=43):
@@ -46,7 +56,8 @@ def run_example(kind, name, tmp_path, lanes=4, seed=43):
     d = tmp_path / ("%s_%s" % (kind, name))
     d.mkdir()
     for f in (CASES[name][0] if name in CASES else OWN_SETUPS[name]) + ["OPTIONS"]:
-        shutil.copy(os.path.join(E2E, f), d)
+        src, dst = f if isinstance(f, tuple) else (f, f)
+        shutil.copy(os.path.join(E2E, src), d / dst)
     r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, capture_output=True,
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
@@ -98,6 +109,21 @@ def test_gpu_chain_equals_cpu_chain_on_this_box(gpu, tmp_path):
     assert np.max(np.abs(ia[:, 1] - ib[:, 1]) / np.abs(ia[:, 1])) <= 1e-10  # its log-likelihood
 
 
+@pytest.mark.parametrize("name", CHAIN_EQUALITY)
+def test_more_setups_gpu_chain_equals_reference_chain(gpu, tmp_path, name):
+    """The BASELINE configs beyond the CI fixtures, through the whole C++ host side: the chain of the
+    batched GPU sampler equals, byte for byte, the chain of the reference's CPU sampler built from
+    the same set-up file (`-t 4 -s 43`, the CI OPTIONS)."""
+    a = run_example("cpu", name, tmp_path)
+    b = run_example("gpu", name, tmp_path)
+    assert (a / "sample.txt").read_bytes() == (b / "sample.txt").read_bytes()
+    assert (a / "levels.txt").read_bytes() == (b / "levels.txt").read_bytes()
+    ia = np.loadtxt(a / "sample_info.txt", ndmin=2)
+    ib = np.loadtxt(b / "sample_info.txt", ndmin=2)
+    assert ia.shape == ib.shape and np.array_equal(ia[:, 0], ib[:, 0])
+    assert np.max(np.abs(ia[:, 1] - ib[:, 1]) / np.abs(ia[:, 1])) <= 1e-10
+
+
 def test_celerite_setup_gpu_chain_equals_reference_chain(gpu, tmp_path):
     """kernel=celerite through the whole C++ host side: same chain as the reference's CPU
     sampler built from the same set-up file."""
@@ -141,7 +167,8 @@ def run_ranks(name, tmp_path, world, lanes, seed=43, port=29541):
     d = tmp_path / ("ranks%d_%s" % (world, name))
     d.mkdir()
     for f in (CASES[name][0] if name in CASES else OWN_SETUPS[name]) + ["OPTIONS"]:
-        shutil.copy(os.path.join(E2E, f), d)
+        src, dst = f if isinstance(f, tuple) else (f, f)
+        shutil.copy(os.path.join(E2E, src), d / dst)
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK=str(r), MASTER_PORT=str(port))

@@ -200,3 +200,17 @@ def test_device_sincos_accuracy(hc):
         rs = np.array([math.sin(v) for v in x])
         rc = np.array([math.cos(v) for v in x])
         assert np.max(np.abs(s - rs)) <= 3e-16 and np.max(np.abs(c - rc)) <= 3e-16
+
+
+def test_dnest_post_is_pykimas_postprocess():
+    """tests/dnest_post.py against pykima.classic.postprocess (/root/reference/pykima/classic.py:20-135)
+    on a committed run of the reference's CPU sampler (tests/golden/make_golden_postprocess.py)."""
+    import dnest_post
+    run = os.path.join(GOLDEN, "postprocess_run")
+    z = np.load(os.path.join(run, "pykima_postprocess.npz"))
+    logz, P, H = dnest_post.log_evidence(run)
+    assert abs(logz - float(z["logz"])) <= 1e-10 and abs(H - float(z["H"])) <= 1e-10
+    lv = np.loadtxt(os.path.join(run, "levels.txt"), ndmin=2)
+    si = np.loadtxt(os.path.join(run, "sample_info.txt"), ndmin=2)
+    assert np.max(np.abs(dnest_post.postprocess(lv, si)[2] - z["logx"])) <= 1e-12
+    assert abs(P.sum() - 1.0) <= 1e-12

@@ -71,6 +71,22 @@ def test_scale_point_N4096_port_matches_reference(port):
     assert relerr(logL, g["logL"][:2]).max() <= 2e-12
 
 
+def test_tail_case_port_is_the_reference_bit_for_bit(port):
+    """The ill-conditioned lanes (tests/golden/tail_kep_N200_np5_hyper.npz): the plain-C port follows the
+    reference's acos chain operation by operation, so even here it reproduces the reference exactly."""
+    import json
+    import os
+    from kima_b200.flags import ModelFlags
+    from kima_b200.synthetic import make_data
+    z = np.load(os.path.join(GOLDEN, "tail_kep_N200_np5_hyper.npz"))
+    flags = ModelFlags(**{k: (bool(v) if isinstance(getattr(ModelFlags(), k), bool) else int(v))
+                          for k, v in json.loads(str(z["flags"])).items()})
+    port.set_rvdata(make_data(200))
+    port.set_flags(flags)
+    logL, _ = port.eval_batch(z["params"], z["nps"])
+    assert np.array_equal(logL, z["logL"])
+
+
 def test_nonfinite_maps_to_minus_1e300(port):
     # src/RVmodel.cpp:938-941 then DNest4/code/LikelihoodType.cpp:17-24
     g = load_golden("synth_edge")
