@@ -226,7 +226,11 @@ int kc_gp_cov(kc_ctx* ctx, int lane, double* C);
  *            indicator terms, i.e. calculate_mu without the MA term
  *            KC_PRED_GP: gp_out[b*nt + k] = K(t_pred[k], t) C^-1 (y - mu), C and mu those of
  *            the C++ likelihood (src/RVmodel.cpp:186-216, 286-375); NaN where C is not
- *            positive definite.  Needs GP=true with the standard kernel.
+ *            positive definite.  Needs GP=true.  With kernel=celerite this is
+ *            GP_celerite.predict (pykima/GP.py:349-355): the solver's own O(N + nt) recursions,
+ *            CholeskySolver::solve / predict (celerite/cpp/include/celerite/solver/
+ *            cholesky.h:217-262, 598-690) on the solver set up as in src/RVmodel.cpp:218-266;
+ *            t_pred must then be sorted ascending (KC_ERR_ARG otherwise).
  * Outputs are host arrays of B*nt doubles (either may be NULL when not asked for). */
 #define KC_PRED_MODEL 1
 #define KC_PRED_GP 2

@@ -564,13 +564,20 @@ static int predict_impl(kc_ctx* c, int B, int nt, const double* t_pred, int what
     if (want_model && !model_out) return fail(KC_ERR_ARG, "model_out is null");
     if (want_gp && !gp_out) return fail(KC_ERR_ARG, "gp_out is null");
     if (want_std && !std_out) return fail(KC_ERR_ARG, "gp_std_out is null");
-    if ((want_gp || want_std) && !(c->F.GP && c->F.kernel == 0))
-        return fail(KC_ERR_UNSUPPORTED, "KC_PRED_GP / KC_PRED_GP_STD need GP=true with the standard kernel");
+    if ((want_gp || want_std) && !c->F.GP) return fail(KC_ERR_UNSUPPORTED, "KC_PRED_GP / KC_PRED_GP_STD need GP=true");
+    const bool cel = c->F.GP && c->F.kernel == 1;
+    if (want_std && cel)
+        return fail(KC_ERR_UNSUPPORTED, "KC_PRED_GP_STD needs the standard kernel (kernel=celerite predicts the mean only)");
+    if (want_gp && cel && t_pred)  // celerite's predict walks the grid and the epochs together (cholesky.h:613-687)
+        for (int k = 1; k < nt; k++)
+            if (!(t_pred[k] >= t_pred[k - 1])) return fail(KC_ERR_ARG, "kernel=celerite: t_pred must be sorted ascending");
     if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is in flight");
     CU(cudaSetDevice(c->device));
     if (B == 0) return KC_OK;
     const size_t out_d = (size_t)B * nt;
-    const size_t need = (size_t)nt + (want_model ? out_d : 0) + (want_gp ? out_d + (size_t)B * c->N : 0) +
+    // GP scratch: the standard kernel keeps alpha [B][N]; celerite its factor [N][8][ld]
+    const size_t gp_scratch = cel ? (size_t)8 * c->N * c->ld : (size_t)B * c->N;
+    const size_t need = (size_t)nt + (want_model ? out_d : 0) + (want_gp ? out_d + gp_scratch : 0) +
                         (want_std ? out_d : 0);
     if (need > c->pred_doubles) {
         CU(cudaStreamSynchronize(c->stream));
@@ -584,7 +591,7 @@ static int predict_impl(kc_ctx* c, int B, int nt, const double* t_pred, int what
     double* d_model = d_t + nt;
     double* d_gp = d_model + (want_model ? out_d : 0);
     double* d_alpha = d_gp + (want_gp ? out_d : 0);
-    double* d_std = d_alpha + (want_gp ? (size_t)B * c->N : 0);
+    double* d_std = d_alpha + (want_gp ? gp_scratch : 0);
     if (t_pred) CU(cudaMemcpyAsync(d_t, t_pred, sizeof(double) * nt, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
                          sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
@@ -595,7 +602,10 @@ static int predict_impl(kc_ctx* c, int B, int nt, const double* t_pred, int what
     cudaError_t e = cudaSuccess;
     if (want_model)
         e = kc::launch_predict_model(p, c->kepler_mode, t_pred ? d_t : nullptr, nt, d_model, c->stream, &n);
-    if (e == cudaSuccess && (want_gp || want_std)) {
+    if (e == cudaSuccess && want_gp && cel) {
+        e = kc::launch_celerite_predict(p, c->d_resid, d_alpha, c->ld, c->kepler_mode, t_pred ? d_t : nullptr, nt, d_gp,
+                                        c->stream, &n);
+    } else if (e == cudaSuccess && (want_gp || want_std)) {
         kc::GpPredict pr{t_pred ? d_t : nullptr, nt, d_alpha, want_gp ? d_gp : nullptr, want_std ? d_std : nullptr};
         e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n, &pr);
     }

@@ -161,7 +161,240 @@ celerite_kernel(const KParams p, const double* __restrict__ resid, int ldr)
     p.logL[b] = logL;
 }
 
+// ---- conditional mean on a time grid (pykima's GP_celerite.predict, GP.py:349-355) ----
+// K_* (K + sigma)^-1 r by the solver's own O(N + M) recursions: CholeskySolver::compute (cholesky.h:95-190),
+// solve (:217-262: forward sweep, division by D, backward sweep) and predict (:598-690: a forward and a
+// backward pass over the sorted prediction times).  One thread per particle again; what the backward sweep
+// needs of the factor (D, the six W and the forward-solved x of every epoch) goes through HBM scratch laid out
+// [N][8][ldr] (coalesced over particles); u and phi are recomputed from the epochs.
+constexpr int CF = 8;  // D, W[6], x
+
+__global__ void __launch_bounds__(32)
+celerite_predict_kernel(const KParams p, const double* __restrict__ resid, int ldr, double* __restrict__ fac,
+                        const double* __restrict__ tpred, int M, double* __restrict__ out)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.B) return;
+    const int N = p.N;
+    const kc_layout& L = p.L;
+    const double eta1 = ldp(p, L.row_eta, b), eta2 = ldp(p, L.row_eta + 1, b), eta3 = ldp(p, L.row_eta + 2, b);
+    const double extra_sigma = ldp(p, L.row_jit, b);
+    const double wbeat = kdiv(1.0, eta2), wrot = kdiv(kmul(2.0, PI), eta3), amp = kmul(eta1, eta1);
+    const double c = wbeat, d = wrot, x = kdiv(c, d);
+    const double a = kdiv(amp, 2.0), bq = kdiv(kmul(amp, x), 2.0), e = kdiv(amp, 8.0), f = kdiv(kmul(amp, x), 4.0);
+    const double g = kmul(amp, kadd(3. / 8., 0.001));
+    const double a_comp[3] = {a, e, g}, b_comp[3] = {bq, f, 0.0}, d_comp[3] = {d, kmul(2.0, d), 0.0};
+    const double jitter = kmul(extra_sigma, extra_sigma);
+    const double asum = kadd(kadd(a, e), g);
+    auto F = [&](int n, int k) -> double& { return fac[((size_t)n * CF + k) * ldr + b]; };
+    const double* tp = tpred ? tpred : p.t;
+    double* row = out + (size_t)b * M;
+    const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+
+    // ---- compute + forward sweep (as celerite_kernel), keeping D, W and x of every epoch ----
+    double S[CJ][CJ];
+#pragma unroll
+    for (int j = 0; j < CJ; j++)
+#pragma unroll
+        for (int k = 0; k < CJ; k++) S[k][j] = 0.0;
+    double W0[CJ], W1[CJ], u[CJ], fv[CJ];
+    bool fail = false;
+    double t_prev = __ldg(p.t);
+    double Dn = kadd(kadd(__ldg(p.sig2), asum), jitter);
+    {
+        const double value = kdiv(1.0, Dn);
+#pragma unroll
+        for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+            double sd, cd;
+            sincos(kmul(d_comp[j], t_prev), &sd, &cd);
+            W0[k] = kmul(cd, value);
+            W0[k + 1] = kmul(sd, value);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < CJ; j++) fv[j] = 0.0;
+    double xm1 = resid[b];
+    F(0, 0) = Dn;
+#pragma unroll
+    for (int j = 0; j < CJ; j++) F(0, 1 + j) = W0[j];
+    F(0, 7) = xm1;
+    for (int n = 1; n < N; ++n) {
+        const double t = __ldg(p.t + n);
+        const double dx = kadd(t, -t_prev);
+        t_prev = t;
+        const double phi = exp(kmul(-c, dx));
+#pragma unroll
+        for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+            double sd, cd;
+            sincos(kmul(d_comp[j], t), &sd, &cd);
+            u[k] = kadd(kmul(a_comp[j], cd), kmul(b_comp[j], sd));
+            u[k + 1] = kadd(kmul(a_comp[j], sd), -kmul(b_comp[j], cd));
+            W1[k] = cd;
+            W1[k + 1] = sd;
+        }
+#pragma unroll
+        for (int j = 0; j < CJ; ++j) {
+            const double xj = kmul(Dn, W0[j]);
+#pragma unroll
+            for (int k = 0; k <= j; ++k) S[k][j] = kmul(phi, kmul(phi, kadd(S[k][j], kmul(xj, W0[k]))));
+        }
+        Dn = kadd(kadd(__ldg(p.sig2 + n), asum), jitter);
+#pragma unroll
+        for (int j = 0; j < CJ; ++j) {
+            const double uj = u[j];
+            double xj = W1[j];
+#pragma unroll
+            for (int k = 0; k < j; ++k) {
+                const double tmp = kmul(u[k], S[k][j]);
+                Dn = kadd(Dn, -kmul(2.0, kmul(uj, tmp)));
+                xj = kadd(xj, -tmp);
+                W1[k] = kadd(W1[k], -kmul(uj, S[k][j]));
+            }
+            const double tmp = kmul(uj, S[j][j]);
+            Dn = kadd(Dn, -kmul(uj, tmp));
+            W1[j] = kadd(xj, -tmp);
+        }
+        if (Dn < 0) fail = true;
+#pragma unroll
+        for (int j = 0; j < CJ; ++j) W1[j] = kdiv(W1[j], Dn);
+        double xv = resid[(size_t)n * ldr + b];
+#pragma unroll
+        for (int j = 0; j < CJ; ++j) {
+            const double value = kmul(phi, kadd(fv[j], kmul(W0[j], xm1)));
+            fv[j] = value;
+            xv = kadd(xv, -kmul(u[j], value));
+        }
+        xm1 = xv;
+        F(n, 0) = Dn;
+#pragma unroll
+        for (int j = 0; j < CJ; ++j) {
+            F(n, 1 + j) = W1[j];
+            W0[j] = W1[j];
+        }
+        F(n, 7) = xv;
+    }
+    if (fail || !(Dn == Dn)) {
+        for (int m = 0; m < M; m++) row[m] = qnan;
+        return;
+    }
+    // ---- x /= D, backward sweep (cholesky.h:245-255): alpha overwrites x ----
+    {
+        double xn1 = kdiv(F(N - 1, 7), F(N - 1, 0));
+        F(N - 1, 7) = xn1;
+#pragma unroll
+        for (int j = 0; j < CJ; j++) fv[j] = 0.0;
+        for (int n = N - 2; n >= 0; --n) {
+            const double t1 = __ldg(p.t + n + 1);
+            const double phi = exp(kmul(-c, kadd(t1, -__ldg(p.t + n))));
+#pragma unroll
+            for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+                double sd, cd;
+                sincos(kmul(d_comp[j], t1), &sd, &cd);
+                u[k] = kadd(kmul(a_comp[j], cd), kmul(b_comp[j], sd));
+                u[k + 1] = kadd(kmul(a_comp[j], sd), -kmul(b_comp[j], cd));
+            }
+            double xv = kdiv(F(n, 7), F(n, 0));
+#pragma unroll
+            for (int j = 0; j < CJ; ++j) {
+                const double value = kmul(phi, kadd(fv[j], kmul(u[j], xn1)));
+                fv[j] = value;
+                xv = kadd(xv, -kmul(F(n, 1 + j), value));
+            }
+            F(n, 7) = xv;
+            xn1 = xv;
+        }
+    }
+    // ---- predict: forward pass (cholesky.h:613-647) ----
+    double Q[CJ];
+#pragma unroll
+    for (int j = 0; j < CJ; j++) Q[j] = 0.0;
+    const double t0 = __ldg(p.t), tN = __ldg(p.t + N - 1);
+    int m = 0;
+    while (m < M && __ldg(tp + m) <= t0) row[m++] = 0.0;  // pred.setZero(): only the backward pass reaches these
+    for (int n = 0; n < N; ++n) {
+        const double alphan = F(n, 7);
+        const double tref = n < N - 1 ? __ldg(p.t + n + 1) : tN;
+        const double tn = __ldg(p.t + n);
+        const double tmp = exp(kmul(-c, kadd(tref, -tn)));
+#pragma unroll
+        for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+            double sd, cd;
+            sincos(kmul(d_comp[j], tn), &sd, &cd);
+            Q[k] = kmul(kadd(Q[k], kmul(alphan, cd)), tmp);
+            Q[k + 1] = kmul(kadd(Q[k + 1], kmul(alphan, sd)), tmp);
+        }
+        while (m < M && (n == N - 1 || __ldg(tp + m) <= tref)) {
+            const double xm = __ldg(tp + m);
+            const double tq = exp(kmul(-c, kadd(xm, -tref)));
+            double pm = 0.0;
+#pragma unroll
+            for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+                double sd, cd;
+                sincos(kmul(d_comp[j], xm), &sd, &cd);
+                pm = kadd(pm, kmul(kmul(kadd(kmul(a_comp[j], cd), kmul(b_comp[j], sd)), tq), Q[k]));
+                pm = kadd(pm, kmul(kmul(kadd(kmul(a_comp[j], sd), -kmul(b_comp[j], cd)), tq), Q[k + 1]));
+            }
+            row[m] = pm;
+            ++m;
+        }
+    }
+    // ---- predict: backward pass (cholesky.h:649-687) ----
+    m = M - 1;
+    while (m >= 0 && __ldg(tp + m) > tN) --m;
+#pragma unroll
+    for (int j = 0; j < CJ; j++) Q[j] = 0.0;
+    for (int n = N - 1; n >= 0; --n) {
+        const double alphan = F(n, 7);
+        const double tref = n > 0 ? __ldg(p.t + n - 1) : t0;
+        const double tn = __ldg(p.t + n);
+        const double tmp = exp(kmul(-c, kadd(tn, -tref)));
+#pragma unroll
+        for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+            double sd, cd;
+            sincos(kmul(d_comp[j], tn), &sd, &cd);
+            Q[k] = kmul(kadd(Q[k], kmul(alphan, kadd(kmul(a_comp[j], cd), kmul(b_comp[j], sd)))), tmp);
+            Q[k + 1] = kmul(kadd(Q[k + 1], kmul(alphan, kadd(kmul(a_comp[j], sd), -kmul(b_comp[j], cd)))), tmp);
+        }
+        while (m >= 0 && (n == 0 || __ldg(tp + m) > tref)) {
+            const double xm = __ldg(tp + m);
+            const double tq = exp(kmul(-c, kadd(tref, -xm)));
+            double pm = 0.0;
+#pragma unroll
+            for (int j = 0, k = 0; j < 3; ++j, k += 2) {
+                double sd, cd;
+                sincos(kmul(d_comp[j], xm), &sd, &cd);
+                pm = kadd(pm, kmul(kmul(cd, tq), Q[k]));
+                pm = kadd(pm, kmul(kmul(sd, tq), Q[k + 1]));
+            }
+            row[m] = kadd(row[m], pm);
+            --m;
+        }
+    }
+}
+
 }  // namespace
+
+// resid: [N][ldr] doubles, fac: [N][8][ldr] doubles of scratch; d_tpred (null = the data epochs) sorted ascending
+cudaError_t launch_celerite_predict(const KParams& p, double* resid, double* fac, int ldr, int kepler_mode,
+                                    const double* d_tpred, int nt, double* d_out, cudaStream_t stream, int* n_launches)
+{
+    if (p.B <= 0 || nt <= 0) return cudaSuccess;
+    const size_t ma_smem = p.F.MA ? 2 * sizeof(double) * (size_t)p.N : 0;
+    if (ma_smem > 160 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e;
+    if (kepler_mode == 0) {
+        e = cudaFuncSetAttribute(celerite_resid_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ma_smem);
+        if (e != cudaSuccess) return e;
+        celerite_resid_kernel<0><<<p.B, CTA_THREADS, ma_smem, stream>>>(p, resid, ldr);
+    } else {
+        e = cudaFuncSetAttribute(celerite_resid_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ma_smem);
+        if (e != cudaSuccess) return e;
+        celerite_resid_kernel<1><<<p.B, CTA_THREADS, ma_smem, stream>>>(p, resid, ldr);
+    }
+    celerite_predict_kernel<<<(p.B + 31) / 32, 32, 0, stream>>>(p, resid, ldr, fac, d_tpred, nt, d_out);
+    *n_launches += 2;
+    return cudaGetLastError();
+}
 
 cudaError_t launch_gp_celerite(const KParams& p, double* resid, int ldr, int kepler_mode,
                                cudaStream_t stream, int* n_launches)

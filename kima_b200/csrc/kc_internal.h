@@ -84,6 +84,9 @@ cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stre
 // kernel = celerite (kc_celerite.cu): resid is [N][ldr] doubles of scratch
 cudaError_t launch_gp_celerite(const KParams& p, double* resid, int ldr, int kepler_mode,
                                cudaStream_t stream, int* n_launches);
+cudaError_t launch_celerite_predict(const KParams& p, double* resid, double* fac, int ldr, int kepler_mode,
+                                    const double* d_tpred, int nt, double* d_out, cudaStream_t stream,
+                                    int* n_launches);
 cudaError_t launch_gp_cov(const KParams& p, int lane, double* C, cudaStream_t s);
 
 // The communicator state of a context, as kc_comm.cu sees it.

@@ -143,7 +143,7 @@ class LikelihoodEngine:
         ``t`` (None = the data epochs).  Returns ``(model[B, nt] | None, gp[B, nt] | None)``."""
         B = self.set_params(params, nps)
         if gp is None:
-            gp = bool(self.flags.GP) and self.flags.kernel == 0
+            gp = bool(self.flags.GP)  # kernel=celerite: the solver's own predict (sorted grid)
         tt = None if t is None else np.ascontiguousarray(t, np.float64)
         nt = self.data.N() if tt is None else tt.size
         what = (_lib.KC_PRED_MODEL if model else 0) | (_lib.KC_PRED_GP if gp else 0)

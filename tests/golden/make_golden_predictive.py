@@ -85,5 +85,29 @@ def main():
         print(name, "N=%d B=%d nt=%d  max|model|=%.3g max|gp|=%.3g" % (N, B, nt, np.abs(model_grid).max(), np.abs(gp_grid).max()))
 
 
+def celerite_case():
+    """kernel=celerite: the conditional mean of the reference's OWN solver (CholeskySolver::predict through
+    oracle/_ref/libkima_ref.so, oracle/ref_harness.cpp: ref_celerite_predict) -- pykima's GP_celerite wraps the
+    Python celerite package, which is not installed here; the C++ solver is the code the likelihood runs."""
+    from oracle.oracle import Oracle
+    ref = Oracle("reference")
+    for name, flags, N, B, nt in (("predictive_celerite_N200", ModelFlags(GP=True, kernel=1, npmax=2), 200, 6, 450),
+                                  ("predictive_celerite_N90_trend", ModelFlags(GP=True, kernel=1, npmax=1, trend=True, degree=1),
+                                   90, 4, 77)):
+        d = make_data(N)
+        P, nps = make_params(flags, d, B, "mix", seed=9)
+        ref.set_rvdata(d)
+        ref.set_flags(flags)
+        tg = np.linspace(d.t.min() - 25.0, d.t.max() + 25.0, nt)
+        gp_grid = np.array([ref.celerite_predict(P, b, int(nps[b]), tg) for b in range(B)])
+        gp_data = np.array([ref.celerite_predict(P, b, int(nps[b]), d.t) for b in range(B)])
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), t=d.t, y=d.y, sig=d.sig, params=P, nps=nps, tgrid=tg,
+                            gp_grid=gp_grid, gp_data=gp_data,
+                            flags=json.dumps({k: int(getattr(flags, k)) for k in flags.__dataclass_fields__}))
+        print(name, "N=%d B=%d nt=%d  max|gp|=%.3g" % (N, B, nt, np.abs(gp_grid).max()))
+
+
 if __name__ == "__main__":
-    main()
+    if "celerite" not in sys.argv[1:]:
+        main()
+    celerite_case()

@@ -56,6 +56,76 @@ def test_oracle_predictive_against_pykima(name):
             assert np.max(np.abs(sd ** 2 - z["gp_std"][b] ** 2)) <= 1e-7 * eta1 ** 2
 
 
+CELERITE_CASES = ["predictive_celerite_N200", "predictive_celerite_N90_trend"]
+
+
+@pytest.mark.parametrize("name", CELERITE_CASES)
+def test_oracle_celerite_predict_against_the_reference_solver(name):
+    """oracle.predictive.gp_mean_celerite (numpy restatement of CholeskySolver::compute / solve / predict)
+    against vectors made by the reference's own solver (make_golden_predictive.py: celerite_case)."""
+    z, flags, data = load_case(name)
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    P, nps = z["params"], z["nps"]
+    for b in range(nps.size):
+        g = opred.gp_mean_celerite(orc, flags, data, P, b, nps[b], z["tgrid"])
+        assert np.max(np.abs(g - z["gp_grid"][b])) <= 1e-11 * (np.abs(z["gp_grid"][b]).max() + 1.0)
+        gd = opred.gp_mean_celerite(orc, flags, data, P, b, nps[b])
+        assert np.max(np.abs(gd - z["gp_data"][b])) <= 1e-11 * (np.abs(z["gp_data"][b]).max() + 1.0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CELERITE_CASES)
+def test_gpu_celerite_predict_against_the_reference_solver(gpu, name):
+    """kc_predict with kernel=celerite (GP_celerite.predict, pykima/GP.py:349-355)."""
+    z, flags, data = load_case(name)
+    P, nps = z["params"], z["nps"]
+    B = nps.size
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    with LikelihoodEngine(data, flags, B) as eng:
+        m, g = eng.predict(P, nps, z["tgrid"])
+        md, gd = eng.predict(P, nps, None)
+        with pytest.raises(KimaCudaError):
+            eng.predict(P, nps, z["tgrid"][::-1].copy())       # celerite walks a sorted grid
+        with pytest.raises(KimaCudaError):
+            eng.predict_std(P, nps, z["tgrid"])                 # no predictive variance for celerite
+    for b in range(B):
+        gs = np.abs(z["gp_grid"][b]).max() + 1.0
+        assert np.max(np.abs(g[b] - z["gp_grid"][b])) <= 1e-8 * gs
+        assert np.max(np.abs(gd[b] - z["gp_data"][b])) <= 1e-8 * gs
+        assert np.max(np.abs(g[b] - opred.gp_mean_celerite(orc, flags, data, P, b, nps[b], z["tgrid"]))) <= 1e-8 * gs
+        scale = np.abs(m[b]).max() + 1.0
+        assert np.max(np.abs(m[b] - opred.model(orc, flags, data, P, b, nps[b], z["tgrid"]))) <= 1e-10 * scale
+
+
+@pytest.mark.gpu
+def test_gpu_celerite_predict_many_lanes_and_failures(gpu):
+    """More lanes than a warp, MA residuals, a lane whose factorisation fails (NaN row)."""
+    flags = ModelFlags(GP=True, kernel=1, npmax=2, MA=True)
+    data = make_data(120)
+    B = 200
+    P, nps = make_params(flags, data, B, "mix", seed=21)
+    orc = Oracle("port")
+    orc.set_rvdata(data)
+    orc.set_flags(flags)
+    L = orc.layout()
+    P[L["row_jit"], 5] = np.nan
+    tg = np.linspace(data.t.min() - 2.0, data.t.max() + 2.0, 301)
+    with LikelihoodEngine(data, flags, B) as eng:
+        _, g = eng.predict(P, nps, tg, model=False)
+    assert np.all(np.isnan(g[5]))
+    for b in (0, 17, 64, B - 1):
+        fac = opred.celerite_factor(opred.celerite_terms([P[L["row_eta"] + k, b] for k in range(3)]), data.t,
+                                    data.sig ** 2 + P[L["row_jit"], b] ** 2)
+        # MA residuals: y - mu with the MA(1) term, as the likelihood's celerite branch uses them
+        alpha = opred.celerite_solve(fac, data.y - orc.mu(P, b, nps[b]))
+        want = opred.celerite_predict(opred.celerite_terms([P[L["row_eta"] + k, b] for k in range(3)]), data.t, alpha, tg)
+        assert np.max(np.abs(g[b] - want)) <= 1e-8 * (np.abs(want).max() + 1.0)
+
+
 @pytest.mark.parametrize("example,flags,n_inst", [
     ("51Peg", ModelFlags(npmax=1), 1),
     ("CoRoT7", ModelFlags(GP=True, hyperpriors=True, npmax=5), 1),
@@ -240,4 +310,4 @@ def test_gpu_predict_errors(gpu):
     Pc, npc = make_params(fc, d, 2, "mix")
     with LikelihoodEngine(d, fc, 2) as eng:
         with pytest.raises(KimaCudaError):
-            eng.predict(Pc, npc, np.arange(5.0), gp=True)         # celerite: not built
+            eng.predict_std(Pc, npc, np.arange(5.0))              # celerite: the mean only
