@@ -593,25 +593,37 @@ def multi_gpu_sampler_leg(rank, world, local, threads, exch):
     import sampler_bench
     runs = []
     port0 = int(os.environ.get("MASTER_PORT", "29500")) + 11
-    # (example, lanes per GPU, saves, device proposals?): host proposals as in the 1-GPU leg, and the
-    # 51Peg example with the whole step on the GPUs (each rank keeps its lanes' particles in HBM)
-    for i, (name, lpg, saves, dev) in enumerate((("CoRoT7", 4096, 80, False), ("51Peg", 16384, 20, True))):
+    # (example, lanes per GPU, saves, device proposals?): host proposals as in the 1-GPU leg (the
+    # reference's byte-identical chains: perturb on the host cores, which the ranks share), and the
+    # whole step on the GPUs (each rank keeps its lanes' particles in HBM) for both examples.
+    # `scaling` = steps/s over run() at `world` ranks / (world x the same binary at the same lanes
+    # per GPU in ONE process, which rank 0 runs first while the others wait).
+    legs = (("CoRoT7", 4096, 80, False), ("CoRoT7", 16384, 10, True), ("51Peg", 16384, 20, True))
+    for i, (name, lpg, saves, dev) in enumerate(legs):
+        env = {"KIMA_DEVICE_PROPOSALS": "1"} if dev else None
+        one = None
+        if rank == 0:
+            one = sampler_bench.run("gpu", name, lpg, 100, saves,
+                                    env=dict(env or {}, KIMA_CUDA_DEVICE=str(local), RANK="0", WORLD_SIZE="1",
+                                             LOCAL_RANK=str(local), KIMA_HOST_THREADS=str(max(1, threads // world))))
         box = [sampler_bench.prepare_dir(name, lpg * world, 100, saves) if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
         dist.barrier()
         r = sampler_bench.run_rank(name, box[0], lpg * world, rank, world, local, port0 + i,
-                                   max(1, threads // world),
-                                   env={"KIMA_DEVICE_PROPOSALS": "1"} if dev else None)
+                                   max(1, threads // world), env=env)
         wall = exch.max_float(float(r.get("wall_s", 0.0)))
         bad = exch.max_float(1.0 if "error" in r else 0.0)
         if rank == 0:
             if bad or not r.get("mcmc_steps"):
-                runs.append({"example": name, "error": r.get("error", "a rank failed")})
+                runs.append({"example": name, "device_proposals": dev, "error": r.get("error", "a rank failed")})
             else:
+                sps_run = r["mcmc_steps"] / r["run_s"] if r.get("run_s") else None
+                one_run = (one or {}).get("steps_per_s_run")
                 runs.append({"example": name, "lanes": lpg * world, "lanes_per_gpu": lpg, "device_proposals": dev,
                              "mcmc_steps": r["mcmc_steps"], "wall_s": wall, "steps_per_s": r["mcmc_steps"] / wall,
-                             "run_s": r.get("run_s"),
-                             "steps_per_s_run": r["mcmc_steps"] / r["run_s"] if r.get("run_s") else None})
+                             "run_s": r.get("run_s"), "steps_per_s_run": sps_run,
+                             "one_process_steps_per_s_run": one_run, "one_process_steps_per_s": (one or {}).get("steps_per_s"),
+                             "scaling": sps_run / (world * one_run) if sps_run and one_run else None})
             shutil.rmtree(box[0], ignore_errors=True)
     out = {"unit": "MCMC steps/s", "ranks": world, "host_threads_per_rank": max(1, threads // world), "runs": runs}
     # parity bit: BL2009, 16 lanes over `world` ranks against the same run in one process (rank 0)

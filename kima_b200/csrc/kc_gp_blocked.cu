@@ -30,14 +30,17 @@ namespace gpb {
 constexpr int NB = 64;        // block-column width
 constexpr int R = 128;        // rows per update tile
 constexpr int KC = 16;        // k-chunk per pipeline stage
-constexpr int STAGES = 3;
+constexpr int STAGES = 4;
 constexpr int A_LD = R + 4;   // 132 = 4 mod 16: conflict-free fragment reads (half-warp = 4 k x 4 rows)
 constexpr int B_LD = NB + 4;  // 68  = 4 mod 16
 constexpr int S_LD = NB + 4;  // diag kernel: S_JJ column-major, element (r, c) at Ss[c * S_LD + r]; 68 = 4 mod 16
 constexpr int STAGE_DOUBLES = KC * (A_LD + B_LD);
 constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;
 static_assert(NB * A_LD <= PIPE_DOUBLES, "the S tile aliases the pipeline stages");
-constexpr int U_SMEM_DOUBLES = PIPE_DOUBLES + NB * B_LD + NB;  // + L_JJ^T + 1/diag, prefetched
+// the epilogue's buffers (the S tile, then L_JJ^T and 1/diag behind it) alias the pipeline stages:
+// L_JJ is fetched once the K loop has drained them, its latency hidden behind the covariance generation
+constexpr int EPI_DOUBLES = NB * A_LD + NB * B_LD + NB;
+constexpr int U_SMEM_DOUBLES = PIPE_DOUBLES > EPI_DOUBLES ? PIPE_DOUBLES : EPI_DOUBLES;
 constexpr int D_THREADS = 128;
 constexpr int D_STAGES = 3;
 constexpr int H_LD = 34;      // 32x32 half-block buffers of the diag kernel
@@ -427,8 +430,8 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         for (int c = 0; c < 4; c++) acc[a][c][0] = acc[a][c][1] = 0.0;
 
     // L_JJ (as stored: LT[c][c2] = L_JJ(c2, c), only c2 > c is ever read) and 1/diag ride in
-    // on their own mbarrier, hidden behind the K loop
-    double* LT = usm + PIPE_DOUBLES;     // [NB][B_LD]
+    // on their own mbarrier after the K loop, hidden behind the covariance generation
+    double* LT = usm + NB * A_LD;        // [NB][B_LD], behind the S tile
     double* dinv = LT + NB * B_LD;       // [NB]
     uint64_t* full = ubars;
     uint64_t* empty = ubars + STAGES;
@@ -452,12 +455,8 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         mbar_fence_init();
     }
     __syncthreads();
-    if (tid == 0) {
-        mbar_expect_tx(aux, (NB / KC) * KC * B_LD * 8 + NB * 8);
-        for (int q = 0; q < NB / KC; q++) tma_load_3d(LT + q * KC * B_LD, &tmB, aux, j0, j0 + q * KC, slot_g);
-        bulk_load(dinv, &gl.dinv[(j0 / NB) & 1][0], NB * 8, aux);
+    if (tid == 0)
         for (int s = 0; s < STAGES - 1 && s < nk; s++) issue_stage(s, s);
-    }
     for (int it = 0; it < nk; it++) {
         const int st = it % STAGES;
         if (tid == 0) {
@@ -489,8 +488,12 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         __syncwarp();
         if (lane == 0) mbar_arrive(empty + st);
     }
-    mbar_wait(aux, 0);
     __syncthreads();  // every warp is done with the stages: the epilogue buffers alias them
+    if (tid == 0) {
+        mbar_expect_tx(aux, (NB / KC) * KC * B_LD * 8 + NB * 8);
+        for (int q = 0; q < NB / KC; q++) tma_load_3d(LT + q * KC * B_LD, &tmB, aux, j0, j0 + q * KC, slot_g);
+        bulk_load(dinv, &gl.dinv[(j0 / NB) & 1][0], NB * 8, aux);
+    }
 
     double* SsT = usm;                   // [NB][A_LD]: the tile, column-major (S, then X in place)
 
@@ -535,6 +538,7 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
             for (int q = 0; q < 4; q++) SsT[(cl + q * CS) * A_LD + rl] = v[q];
         }
     }
+    mbar_wait(aux, 0);  // L_JJ^T and 1/diag have landed (issued before the generation)
     __syncthreads();
 
     // ---- X L_JJ^T = S: each warp owns 16 rows.  Blocked forward substitution over four

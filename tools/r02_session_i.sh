@@ -1,0 +1,19 @@
+#!/bin/bash
+# r02 session i: chol32_panels with the 8x8 diagonal block factored redundantly in every lane
+OUT=gpurun_out/r02i; mkdir -p $OUT
+timeout 60 tools/_build/chol_bench | tee $OUT/chol_bench.txt
+timeout 300 python tools/dev_gp.py parity > $OUT/dev_gp_parity.jsonl 2>&1; rc=$?; echo "parity rc=$rc" >> $OUT/dev_gp_parity.jsonl
+python - <<'PY'
+import json
+mx=0
+for l in open("gpurun_out/r02i/dev_gp_parity.jsonl"):
+    if l.startswith("{"):
+        d=json.loads(l); mx=max(mx,d["max"])
+        if d["max"]>1e-10 or not d["inf_match"]: print("BAD", d)
+print("parity worst", mx)
+PY
+tail -1 $OUT/dev_gp_parity.jsonl
+if [ $rc -ne 0 ]; then echo "GATE FAILED"; tail -20 $OUT/dev_gp_parity.jsonl; exit 1; fi
+timeout 300 python tools/dev_small.py > $OUT/dev_small.jsonl 2>&1; cat $OUT/dev_small.jsonl
+timeout 300 python tools/dev_gp.py timing > $OUT/dev_gp_timing.jsonl 2>&1; cat $OUT/dev_gp_timing.jsonl
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q > $OUT/pytest.log 2>&1; echo "pytest rc=$?" >> $OUT/pytest.log; tail -3 $OUT/pytest.log
