@@ -23,7 +23,7 @@ namespace kima_b200 {
 using PriorMake = int (*)(int type, const double* p, int n_p, kc_prior* out);
 
 // One ContinuousDistribution -> kc_prior; false when the class has no device counterpart
-// (Empirical, mixGaussianLogUniform, Gaussian_from_Tc, Jeffreys).
+// (Empirical: a table of samples, and its log_pdf throws).  Jeffreys is an alias of LogUniform.
 inline bool extract_prior(const DNest4::ContinuousDistribution* d, kc_prior& out, PriorMake make)
 {
     using namespace DNest4;
@@ -54,6 +54,12 @@ inline bool extract_prior(const DNest4::ContinuousDistribution* d, kc_prior& out
         return mk(KC_PRIOR_TRUNC_RAYLEIGH, {q->scale, q->lower, q->upper});
     if (auto* q = dynamic_cast<const Triangular*>(d)) return mk(KC_PRIOR_TRIANGULAR, {q->lower, q->centre, q->upper});
     if (auto* q = dynamic_cast<const Pareto*>(d)) return mk(KC_PRIOR_PARETO, {q->min, q->alpha});
+    // kima's own classes (src/distributions/): the Gaussian for phi built from a transit time is the
+    // Gaussian(m, s) it wraps (every virtual forwards to it; its perturb is not virtual and never reached
+    // through the base pointer); the Gaussian + log-uniform mixture has its own table form
+    if (auto* q = dynamic_cast<const Gaussian_from_Tc*>(d)) return mk(KC_PRIOR_GAUSSIAN, {q->m, q->s});
+    if (auto* q = dynamic_cast<const mixGaussianLogUniform*>(d))
+        return mk(KC_PRIOR_MIX_GAUSS_LOGUNIFORM, {q->mean, q->sigma, q->lower, q->upper});
     return false;
 }
 

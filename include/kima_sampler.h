@@ -58,7 +58,12 @@ enum {
     KC_PRIOR_TRUNC_RAYLEIGH = 13,  /* TruncatedRayleigh(scale, lower, upper); k0 = lcdf, k1 = tp, k2 = logtp */
     KC_PRIOR_TRIANGULAR = 14,      /* Triangular(lower, centre, upper)                  */
     KC_PRIOR_PARETO = 15,          /* Pareto(min, alpha)                                */
-    KC_PRIOR_N_TYPES = 16
+    KC_PRIOR_MIX_GAUSS_LOGUNIFORM = 16, /* mixGaussianLogUniform(mean, sigma, lower, upper), src/distributions/
+                                      mixGaussianLogUniform.cpp; k0 = log(upper/lower); cdf_inverse by the
+                                      reference's bisection.  Gaussian_from_Tc (src/distributions/
+                                      Gaussian_from_Tc.cpp) is tabled as the Gaussian(m, s) it wraps and
+                                      Jeffreys is an alias of LogUniform; Empirical has no table form.  */
+    KC_PRIOR_N_TYPES = 17
 };
 
 typedef struct kc_prior {

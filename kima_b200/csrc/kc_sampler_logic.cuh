@@ -136,6 +136,16 @@ KS_HD double expo_cdf(double s, double x) { return 1 - exp(-x / s); }
 KS_HD double expo_icdf(double s, double p) { return -s * log(1. - p); }
 KS_HD double clamp_lu(double x, double lo, double hi) { return fmax(fmin(x, hi), lo); }
 
+// mixGaussianLogUniform::cdf (src/distributions/mixGaussianLogUniform.cpp:19-22)
+KS_FN double mix_glu_cdf(const kc_prior& q, double x)
+{
+    const double a = q.p[0], b = q.p[1], c = q.p[2], d = q.p[3];
+    double lu = (log(x) - log(c)) / q.k[0];
+    if (x < c) lu = 0.0;
+    if (x > d) lu = 1.0;
+    return 0.5 * gauss_cdf(a, b, x) + 0.5 * lu;
+}
+
 KS_FN double prior_cdf(const kc_prior& q, double x)
 {
     const double a = q.p[0], b = q.p[1], c = q.p[2], d = q.p[3];
@@ -168,6 +178,7 @@ KS_FN double prior_cdf(const kc_prior& q, double x)
         if (x <= b) return pow(x - a, 2) / ((c - a) * (b - a));
         if (x < c) return 1. - pow(c - x, 2) / ((c - a) * (c - b));
         return 1.;
+    case KC_PRIOR_MIX_GAUSS_LOGUNIFORM: return mix_glu_cdf(q, x);
     case KC_PRIOR_PARETO:
         if (x <= a) return 0.0;
         return 1.0 - pow(x / a, b);
@@ -199,6 +210,19 @@ KS_FN double prior_cdf_inverse(const kc_prior& q, double x)
         return c - sqrt((1. - x) * (c - a) * (c - b));
     }
     case KC_PRIOR_PARETO: return a * pow(1.0 - x, 1.0 / b);
+    case KC_PRIOR_MIX_GAUSS_LOGUNIFORM: {
+        // the reference's bisection on [lower, upper], tolerance 2e-12 (mixGaussianLogUniform.cpp:25-46)
+        const double tol = 2e-12;
+        double lo = c, hi = q.p[3], mid = lo;
+        while ((hi - lo) >= tol) {
+            mid = (lo + hi) / 2;
+            const double fm = mix_glu_cdf(q, mid) - x;
+            if (fm == 0.0) break;
+            else if (fm * (mix_glu_cdf(q, lo) - x) < 0) hi = mid;
+            else lo = mid;
+        }
+        return mid;
+    }
     }
     return NAN;
 }
@@ -250,6 +274,12 @@ KS_FN double prior_log_pdf(const kc_prior& q, double x)
         if (x < a || x > c) return neg_inf();
         if (x > a && x <= b) return log(2.0 * (x - a)) - log((c - a) * (b - a));
         return log((c - a)) - log((c - a) * (c - b));  // the reference's third branch, as written
+    case KC_PRIOR_MIX_GAUSS_LOGUNIFORM: {
+        const double r = (x - a) / b;
+        const double lg = -0.5 * r * r - log(sqrt(2 * KS_PI));                              // Gaussian::log_pdf
+        const double ll = (x < c || x > d) ? neg_inf() : -log(x) - log(q.k[0]);             // LogUniform::log_pdf
+        return log(0.5 * exp(lg) + 0.5 * exp(ll));
+    }
     case KC_PRIOR_PARETO:
         if (x <= a) return -1E300;
         return log(b) + b * log(a) - (b + 1.0) * log(x);
@@ -768,7 +798,7 @@ KS_FN void step_accept(const SamplerParams& sp, int lane)
 // Rayleigh.cpp:49-52).
 inline int prior_make(int type, const double* p, int n_p, kc_prior* out)
 {
-    static const int nargs[KC_PRIOR_N_TYPES] = {1, 2, 2, 2, 2, 4, 2, 4, 1, 3, 2, 2, 1, 3, 3, 2};
+    static const int nargs[KC_PRIOR_N_TYPES] = {1, 2, 2, 2, 2, 4, 2, 4, 1, 3, 2, 2, 1, 3, 3, 2, 4};
     if (type < 0 || type >= KC_PRIOR_N_TYPES || !out || n_p != nargs[type]) return 1;
     kc_prior q{};
     q.type = type;
@@ -804,6 +834,10 @@ inline int prior_make(int type, const double* p, int n_p, kc_prior* out)
         break;
     case KC_PRIOR_TRIANGULAR: if (c < b || a > b || c <= a) return 1; break;
     case KC_PRIOR_PARETO: if (a <= 0.0 || b <= 0.0) return 1; break;
+    case KC_PRIOR_MIX_GAUSS_LOGUNIFORM:
+        if (b <= 0.0 || c <= 0.0 || d <= c) return 1;  // Gaussian / LogUniform constructors
+        q.k[0] = log(d / c);
+        break;
     default: break;
     }
     *out = q;

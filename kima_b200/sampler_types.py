@@ -8,7 +8,7 @@ PRIOR_TYPES = {
     "Fixed": 0, "Uniform": 1, "LogUniform": 2, "ModifiedLogUniform": 3, "Gaussian": 4,
     "TruncatedGaussian": 5, "Cauchy": 6, "TruncatedCauchy": 7, "Exponential": 8,
     "TruncatedExponential": 9, "Laplace": 10, "Kumaraswamy": 11, "Rayleigh": 12,
-    "TruncatedRayleigh": 13, "Triangular": 14, "Pareto": 15,
+    "TruncatedRayleigh": 13, "Triangular": 14, "Pareto": 15, "mixGaussianLogUniform": 16,
 }
 KC_PRIOR_NONE = -1
 

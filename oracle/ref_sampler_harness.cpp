@@ -19,6 +19,8 @@
 #define private public
 #define protected public
 #include "distributions/Fixed.h"
+#include "distributions/Gaussian_from_Tc.h"
+#include "distributions/mixGaussianLogUniform.h"
 #undef private
 #undef protected
 
@@ -61,6 +63,7 @@ std::shared_ptr<DNest4::ContinuousDistribution> make_dist(const kc_prior& q)
     case KC_PRIOR_TRUNC_RAYLEIGH: return std::make_shared<TruncatedRayleigh>(a, b, c);
     case KC_PRIOR_TRIANGULAR: return std::make_shared<Triangular>(a, b, c);
     case KC_PRIOR_PARETO: return std::make_shared<Pareto>(a, b);
+    case KC_PRIOR_MIX_GAUSS_LOGUNIFORM: return std::make_shared<mixGaussianLogUniform>(a, b, c, d);
     }
     return nullptr;
 }

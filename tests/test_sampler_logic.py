@@ -22,6 +22,7 @@ PRIOR_EXAMPLES = [
     ("TruncatedCauchy", (np.log(365.0), 1.0, np.log(365.0) - 21, np.log(365.0) + 21)), ("Exponential", (3.0,)),
     ("TruncatedExponential", (2.0, 0.5, 9.0)), ("Laplace", (5.9, 1.3)), ("Kumaraswamy", (0.867, 3.03)),
     ("Rayleigh", (0.2,)), ("TruncatedRayleigh", (0.2, 0.0, 1.0)), ("Triangular", (-1.0, 0.5, 3.0)), ("Pareto", (1.5, 2.0)),
+    ("mixGaussianLogUniform", (3.0, 0.7, 0.5, 40.0)),   # src/distributions/mixGaussianLogUniform.cpp
 ]
 
 
