@@ -599,7 +599,9 @@ def multi_gpu_sampler_leg(rank, world, local, threads, exch):
     # whole step on the GPUs (each rank keeps its lanes' particles in HBM) for both examples.
     # `scaling` = steps/s over run() at `world` ranks / (world x the same binary at the same lanes
     # per GPU in ONE process, which rank 0 runs first while the others wait).
-    legs = (("CoRoT7", 4096, 80, False), ("CoRoT7", 16384, 10, True), ("51Peg", 16384, 20, True))
+    # (51Peg: 200 barriers, so that run() lasts seconds and NCCL's lazy connection set-up inside the first
+    # barrier does not decide the figure)
+    legs = (("CoRoT7", 4096, 80, False), ("CoRoT7", 16384, 10, True), ("51Peg", 16384, 200, True))
     for i, (name, lpg, saves, dev) in enumerate(legs):
         env = {"KIMA_DEVICE_PROPOSALS": "1"} if dev else None
         one = None
