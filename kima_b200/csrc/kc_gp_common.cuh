@@ -6,6 +6,22 @@
 
 namespace kc {
 
+// Polynomial coefficients in the constant bank: an FP64 instruction takes a constant-bank operand
+// directly, whereas a 64-bit literal costs two uniform-register moves per use and a runtime choice
+// between two literals two selects more (ncu, r02: 25 UMOV + 28 FSEL of the ~200 instructions per
+// covariance entry).  The arithmetic is unchanged: same operations, same order, same roundings.
+static __constant__ double KC_SINCOS_POLY[2][6] = {
+    // [0]: sin on [-pi/4, pi/4], S6 .. S1;  [1]: cos, C6 .. C1 (fdlibm)
+    {1.58969099521155010221e-10, -2.50507602534068634195e-08, 2.75573137070700676789e-06,
+     -1.98412698298579493134e-04, 8.33333333332248946124e-03, -1.66666666666666324348e-01},
+    {-1.13596475577881948265e-11, 2.08757232129817482790e-09, -2.75573143513906633035e-07,
+     2.48015872894767294178e-05, -1.38888888888741095749e-03, 4.16666666666666019037e-02}};
+static __constant__ double KC_EXP_TAYLOR[12] = {
+    1.0 / 6227020800.0, 1.0 / 479001600.0, 1.0 / 39916800.0, 1.0 / 3628800.0, 1.0 / 362880.0, 1.0 / 40320.0,
+    1.0 / 5040.0, 1.0 / 720.0, 1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
+static __constant__ double KC_RED[6] = {TWO_OVER_PI, PIO2_HI, PIO2_MID, PIO2_LO, 1.44269504088896338700e+00 /* log2 e */,
+                                        6.93147180559890330187e-01 /* ln2 hi, 42 bits */};
+
 // sin(x) alone, |x| < ~1e5: one polynomial, chosen by quadrant.
 __device__ __forceinline__ double sin_core(double x);
 __device__ __forceinline__ double sin_fast(double x)
@@ -24,6 +40,22 @@ __device__ __forceinline__ double sin_core(double x)
                  C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
                  C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
     int k;
+#if defined(__CUDA_ARCH__)
+    double kd = rint_magic_i(x * KC_RED[0], k);
+    double r = kfma(-kd, KC_RED[1], x);
+    r = kfma(-kd, KC_RED[2], r);
+    r = kfma(-kd, KC_RED[3], r);
+    const bool odd = k & 1;
+    double z = r * r;
+    const double* cf = KC_SINCOS_POLY[k & 1];  // one indexed constant load per coefficient
+    double p = kfma(z, cf[0], cf[1]);
+    p = kfma(z, p, cf[2]);
+    p = kfma(z, p, cf[3]);
+    p = kfma(z, p, cf[4]);
+    p = kfma(z, p, cf[5]);
+    (void)S1; (void)S2; (void)S3; (void)S4; (void)S5; (void)S6;
+    (void)C1; (void)C2; (void)C3; (void)C4; (void)C5; (void)C6;
+#else
     double kd = rint_magic_i(x * TWO_OVER_PI, k);
     double r = kfma(-kd, PIO2_HI, x);
     r = kfma(-kd, PIO2_MID, r);
@@ -35,10 +67,38 @@ __device__ __forceinline__ double sin_core(double x)
     p = kfma(z, p, odd ? C3 : S3);
     p = kfma(z, p, odd ? C2 : S2);
     p = kfma(z, p, odd ? C1 : S1);
+#endif
     double base = odd ? kfma(-0.5, z, 1.0) : r;
-    double mult = odd ? z * z : r * z;
+    double mult = (odd ? z : r) * z;
     double v = kfma(mult, p, base);
+#if defined(__CUDA_ARCH__)
+    // quadrants 2, 3: flip the sign bit (the same value as -v, one integer instruction)
+    return __hiloint2double(__double2hiint(v) ^ ((k & 2) << 30), __double2loint(v));
+#else
     return (k & 2) ? -v : v;
+#endif
+}
+
+// exp_nonpos (kc_math.cuh) with its literals taken from the constant bank; bit-identical results.
+__device__ __forceinline__ double exp_nonpos_cb(double x)
+{
+    double xc = x < -746.0 ? -746.0 : x;  // NaN falls through
+    int k;
+    double kd = rint_magic_i(xc * KC_RED[4], k);
+    double rh = kfma(-kd, KC_RED[5], xc);          // exact
+    double rl = -kd * 5.49792301870837115524e-14;   // ln2 lo
+    double r = rh + rl;
+    double p = KC_EXP_TAYLOR[0];
+#pragma unroll
+    for (int i = 1; i < 12; i++) p = kfma(p, r, KC_EXP_TAYLOR[i]);
+    double r2 = r * r;
+    double t1 = kadd(1.0, rh);
+    double lo = kadd(kadd(rh, -kadd(t1, -1.0)), rl);
+    p = kadd(t1, kfma(p, r2, lo));
+    // 2^(k+64) as a high word: no 64-bit shift
+    double s1 = __hiloint2double((k + 64 + 1023) << 20, 0);
+    // exp(-746) = 9.9e-325 rounds to zero by itself: the clamp above already makes x < -746 return 0
+    return (p * s1) * 5.42101086242752217004e-20;  // 2^-64
 }
 
 struct GpConsts {
@@ -78,7 +138,7 @@ __device__ __forceinline__ double qp_kernel(const GpConsts& g, double tau)
     double s = sin_fast(div_by(kmul(PI, tau), g.eta3, g.r_eta3));
     double v = div_by(s, g.eta4, g.r_eta4);
     double a2 = 2.0 * kmul(v, v);
-    return kmul(g.eta1sq, exp_nonpos(kadd(a1, -a2)));
+    return kmul(g.eta1sq, exp_nonpos_cb(kadd(a1, -a2)));
 }
 
 // Two entries at once: two independent, branch-free dependency chains for the FP64 pipe
@@ -96,8 +156,8 @@ __device__ __forceinline__ void qp_kernel2(const GpConsts& g, double tau0, doubl
     double v0 = div_by(s0, g.eta4, g.r_eta4), v1 = div_by(s1, g.eta4, g.r_eta4);
     double e0 = kadd(-0.5 * kmul(u0, u0), -2.0 * kmul(v0, v0));
     double e1 = kadd(-0.5 * kmul(u1, u1), -2.0 * kmul(v1, v1));
-    c0 = kmul(g.eta1sq, exp_nonpos(e0));
-    c1 = kmul(g.eta1sq, exp_nonpos(e1));
+    c0 = kmul(g.eta1sq, exp_nonpos_cb(e0));
+    c1 = kmul(g.eta1sq, exp_nonpos_cb(e1));
 }
 
 __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
