@@ -19,10 +19,7 @@ __global__ void __launch_bounds__(CTA_THREADS) gp_cov_kernel(const KParams p, in
         if (threadIdx.x == 0) {
             sc.eta1 = ldp(p, L.row_eta, b); sc.eta2 = ldp(p, L.row_eta + 1, b);
             sc.eta3 = ldp(p, L.row_eta + 2, b); sc.eta4 = ldp(p, L.row_eta + 3, b);
-            g.eta1sq = kmul(sc.eta1, sc.eta1);
-            g.eta2 = sc.eta2; g.r_eta2 = kdiv(1.0, sc.eta2);
-            g.eta3 = sc.eta3; g.r_eta3 = kdiv(1.0, sc.eta3);
-            g.eta4 = sc.eta4; g.r_eta4 = kdiv(1.0, sc.eta4);
+            g = gp_consts(sc);
         }
         if (threadIdx.x < KC_MAX_INST) {
             double j2 = 0.0;
@@ -31,6 +28,8 @@ __global__ void __launch_bounds__(CTA_THREADS) gp_cov_kernel(const KParams p, in
         }
     }
     (void)dummy;
+    __shared__ double etab[64];
+    exp_tab_load(etab, threadIdx.x);
     __syncthreads();
     const int N = p.N;
     const bool multi = p.F.multi_instrument != 0;
@@ -43,7 +42,11 @@ __global__ void __launch_bounds__(CTA_THREADS) gp_cov_kernel(const KParams p, in
             int in = multi ? p.obsi[i] - 1 : 0;
             v = kadd(g.eta1sq, kadd(p.sig2[i], sc.jit2[in]));
         } else {
-            v = qp_kernel(g, kadd(p.t[lo], -p.t[hi]));  // the reference fills (i<j) and mirrors
+            // the reference fills (i<j) and mirrors; the generator is the product path's (qp_entry)
+            double si, ci, sj, cj;
+            gp_phase(g, p.t[lo], si, ci);
+            gp_phase(g, p.t[hi], sj, cj);
+            v = qp_entry(g, etab, kadd(p.t[lo], -p.t[hi]), si, ci, sj, cj);
         }
         C[e] = v;
     }

@@ -61,7 +61,9 @@ struct GpbStep {
 
 size_t gpb_ld(int N) { return ((size_t)N + 1 + 15) & ~(size_t)15; }
 // a whole number of columns per slot: the slot stride of the tensor maps is then a multiple of the column stride
-size_t gpb_slot_doubles(int N) { return gpb_ld(N) * ((size_t)N + (gpb::PAD_DOUBLES + gpb_ld(N) - 1) / gpb_ld(N)); }
+// columns 0 .. N-1: the factor (row N of each: the residual / z); columns N, N+1: sin and cos of the epochs' phases
+// (gp_phase), written by the prep kernel and read by every covariance generation of the lane
+size_t gpb_slot_doubles(int N) { return gpb_ld(N) * ((size_t)N + 2 + (gpb::PAD_DOUBLES + gpb_ld(N) - 1) / gpb_ld(N)); }
 
 // The two TMA descriptors over the factor storage of a context (see the plumbing comment below).
 cudaError_t gpb_make_tensor_maps(GpWorkspace& w, int N)
@@ -172,6 +174,15 @@ gpb_prep_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_double
         if (tid < KC_MAX_INST) lanes[slot].jit2[tid] = sc.jit2[tid];
     }
     __syncthreads();
+    {
+        const GpConsts g = gp_consts(sc);
+        for (int i = tid; i < N; i += CTA_THREADS) {
+            double s, c;
+            gp_phase(g, __ldg(p.t + i), s, c);
+            W[(size_t)N * ld + i] = s;
+            W[(size_t)(N + 1) * ld + i] = c;
+        }
+    }
     if (p.F.MA) {
         // residual with the MA(1) term (:378-386): recurrence in shared memory, then row N
         extern __shared__ __align__(16) double ma_buf[];
@@ -271,11 +282,20 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
     double* Ss = dsm + D_STAGES * D_STAGE_DOUBLES;     // [NB][S_LD], column-major
     double* T21 = pipe;                                // after the K loop: [32][H_LD], L21 row-major
     __shared__ double dinv_s[NB];
+    __shared__ double etab[64];        // 2^(j/64) for exp_tab
+    __shared__ double col_t[NB], col_s[NB], col_c[NB];  // epochs and phases of the block's columns
     __shared__ int fail_s;
     const int warp = tid >> 5, lane = tid & 31;
     const int N = p.N;
     const int nbc = min(NB, N - j0);
     __shared__ __align__(8) uint64_t dbars[2 * D_STAGES];
+    exp_tab_load(etab, tid);
+    if (tid >= 64) {
+        const int cc = tid - 64, col = min(j0 + cc, N - 1);
+        col_t[cc] = __ldg(p.t + col);
+        col_s[cc] = W[(size_t)N * ld + col];
+        col_c[cc] = W[(size_t)(N + 1) * ld + col];
+    }
     uint64_t* full = dbars;
     uint64_t* empty = dbars + D_STAGES;
     if (tid == 0) {
@@ -306,7 +326,7 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
         const bool multi = p.F.multi_instrument != 0;
         const int r = tid & (NB - 1);
         const int row = j0 + r;
-        const double trow = row < N ? __ldg(p.t + row) : 0.0;
+        const double trow = col_t[min(r, nbc - 1)], srow = col_s[min(r, nbc - 1)], crow = col_c[min(r, nbc - 1)];
         for (int cc = tid >> 6; cc < NB; cc += D_THREADS / NB) {
             double v;
             if (r >= nbc || cc >= nbc) {
@@ -319,7 +339,8 @@ __device__ __forceinline__ void diag_block(const KParams& p, double* __restrict_
                     // eta1^2 * exp(-0 - 0) + sig^2 + jit^2  (:193-206)
                     v = kadd(g.eta1sq, kadd(__ldg(p.sig2 + row), gl.jit2[in]));
                 } else {
-                    v = qp_kernel(g, kadd(__ldg(p.t + j0 + cc), -trow));
+                    // t[i]-t[j], i<j (:193): i is the column
+                    v = qp_entry(g, etab, kadd(col_t[cc], -trow), col_s[cc], col_c[cc], srow, crow);
                 }
                 v -= Ss[cc * S_LD + r];
             }
@@ -409,6 +430,8 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
     using namespace gpb;
     extern __shared__ __align__(128) double usm[];
     __shared__ __align__(8) uint64_t ubars[2 * STAGES + 1];
+    __shared__ double etab[64];                          // 2^(j/64) for exp_tab
+    __shared__ double col_t[NB], col_s[NB], col_c[NB];   // epochs and phases of block column J
     const int j0 = w.j0, first_row = w.first_row;
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
@@ -453,6 +476,13 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         }
         mbar_init(aux, 1);
         mbar_fence_init();
+    }
+    exp_tab_load(etab, tid);
+    if (tid >= 64 && tid < 64 + NB) {
+        const int cc = tid - 64, col = min(j0 + cc, N - 1);  // columns past a partial block: generated and dropped
+        col_t[cc] = __ldg(p.t + col);
+        col_s[cc] = W[(size_t)N * ld + col];
+        col_c[cc] = W[(size_t)(N + 1) * ld + col];
     }
     __syncthreads();
     if (tid == 0)
@@ -513,7 +543,9 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
         const int rl = tid & (R - 1);
         const int row = r0 + rl;
         const bool row_ok = row >= row_lo && row <= N;
-        const double trow = (row_ok && row < N) ? __ldg(p.t + row) : 0.0;
+        const bool gen = row_ok && row < N;
+        const double trow = gen ? __ldg(p.t + row) : 0.0;
+        const double srow = gen ? W[(size_t)N * ld + row] : 0.0, crow = gen ? W[(size_t)(N + 1) * ld + row] : 0.0;
         // four columns per pass (cl, cl + 2, cl + 4, cl + 6): four independent chains per thread
         constexpr int CS = CTA_THREADS / R;  // 2
         for (int cl = tid >> 7; cl < NB; cl += 4 * CS) {
@@ -524,12 +556,12 @@ gpb_update_kernel(const KParams p, double* __restrict__ ws_all, size_t slot_doub
                     for (int q = 0; q < 4; q++)
                         if (cl + q * CS < nbc) v[q] = W[(size_t)(j0 + cl + q * CS) * ld + N];
                 } else {
-                    // t[i]-t[j], i<j (:193); columns past a partial block are generated and dropped
-                    double tc[4];
+                    // t[i]-t[j], i<j (:193): i is the column
 #pragma unroll
-                    for (int q = 0; q < 4; q++) tc[q] = __ldg(p.t + min(j0 + cl + q * CS, N - 1));
-                    qp_kernel2(g, kadd(tc[0], -trow), kadd(tc[1], -trow), v[0], v[1]);
-                    qp_kernel2(g, kadd(tc[2], -trow), kadd(tc[3], -trow), v[2], v[3]);
+                    for (int q = 0; q < 4; q++) {
+                        const int cc = cl + q * CS;
+                        v[q] = qp_entry(g, etab, kadd(col_t[cc], -trow), col_s[cc], col_c[cc], srow, crow);
+                    }
                 }
 #pragma unroll
                 for (int q = 0; q < 4; q++) v[q] = cl + q * CS < nbc ? v[q] - SsT[(cl + q * CS) * A_LD + rl] : 0.0;

@@ -106,7 +106,92 @@ struct GpConsts {
     double eta2, r_eta2;      // eta and its correctly rounded reciprocal
     double eta3, r_eta3;
     double eta4, r_eta4;
+    double g1, g2;            // -0.5 / eta2^2 and -2 / eta4^2: the two coefficients of the exponent (qp_entry)
 };
+
+// ---- the covariance generator of the product path ---------------------------------------------
+// C(i,j) = eta1^2 exp(-tau^2 / (2 eta2^2) - 2 sin^2(pi tau / eta3) / eta4^2), tau = t_i - t_j (:193-194).
+// Evaluated as written that is ~75 FP64 operations per entry (three divisions, a sine with its range
+// reduction, a 12-term exponential), and the N^2/2 entries are the second largest consumer of the FP64
+// pipe after the factorisation itself.  The product path uses two facts instead:
+//   * sin(pi (t_i - t_j) / eta3) = s_i c_j - c_i s_j with s_i = sin(pi t_i / eta3), c_i = cos(pi t_i / eta3):
+//     2N sines per particle instead of N^2/2.  The phases are formed from a double-double quotient
+//     t_i / eta3 (gp_phase), so s_i, c_i carry <= 2 ulp whatever the magnitude of t_i (JD 2.45e6 included)
+//     and the difference formula is as accurate as the direct one for every pair, near or far;
+//   * exp(x), x <= 0, from a 64-entry table of 2^(j/64) and a degree-5 polynomial on |r| <= ln2/128.
+// 19 FP64 operations per entry.  The entries agree with the reference's to a few 1e-16 eta1^2 -- the
+// same distance the reference's own entries have from an 80-bit evaluation of the kernel
+// (variants/fastgen/proto.py; tests/test_gpu_parity.py pins the bound through kc_gp_cov).
+static __device__ const double KC_EXP2_TAB[64] = {
+    1.00000000000000000e+00, 1.01088928605170048e+00, 1.02189714865411663e+00, 1.03302487902122841e+00,
+    1.04427378242741375e+00, 1.05564517836055716e+00, 1.06714040067682370e+00, 1.07876079775711986e+00,
+    1.09050773266525769e+00, 1.10238258330784089e+00, 1.11438674259589243e+00, 1.12652161860824185e+00,
+    1.13878863475669156e+00, 1.15118922995298267e+00, 1.16372485877757748e+00, 1.17639699165028122e+00,
+    1.18920711500272103e+00, 1.20215673145270308e+00, 1.21524735998046896e+00, 1.22848053610687002e+00,
+    1.24185781207348400e+00, 1.25538075702469110e+00, 1.26905095719173322e+00, 1.28287001607877826e+00,
+    1.29683955465100964e+00, 1.31096121152476441e+00, 1.32523664315974132e+00, 1.33966752405330292e+00,
+    1.35425554693689265e+00, 1.36900242297459052e+00, 1.38390988196383202e+00, 1.39897967253831124e+00,
+    1.41421356237309515e+00, 1.42961333839197002e+00, 1.44518080697704665e+00, 1.46091779418064704e+00,
+    1.47682614593949935e+00, 1.49290772829126484e+00, 1.50916442759342284e+00, 1.52559815074453842e+00,
+    1.54221082540794074e+00, 1.55900440023783693e+00, 1.57598084510788650e+00, 1.59314215134226700e+00,
+    1.61049033194925428e+00, 1.62802742185734783e+00, 1.64575547815396495e+00, 1.66367658032673638e+00,
+    1.68179283050742900e+00, 1.70010635371852348e+00, 1.71861929812247793e+00, 1.73733383527370622e+00,
+    1.75625216037329945e+00, 1.77537649252652119e+00, 1.79470907500310717e+00, 1.81425217550039886e+00,
+    1.83400808640934243e+00, 1.85397912508338547e+00, 1.87416763411029996e+00, 1.89457598158696561e+00,
+    1.91520656139714740e+00, 1.93606179349229435e+00, 1.95714412417540018e+00, 1.97845602638795093e+00};
+// 64 / ln 2, ln 2 / 64 split (high part: 32 significant bits, so k * hi is exact for |k| < 2^20), 1/120 .. 1/2
+static __constant__ double KC_EXPT[7] = {9.23324826168936567683e+01, 1.08304246932675596327e-02, 2.98158582698529328128e-12,
+                                         1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
+
+// tab[64] in shared memory <- 2^(j/64); the caller synchronises before the first qp_entry
+__device__ __forceinline__ void exp_tab_load(double* tab, int tid)
+{
+    if (tid < 64) tab[tid] = KC_EXP2_TAB[tid];
+}
+
+// exp(x) for x <= 0 (NaN propagates; x < -708 returns exp(-708) = 3.3e-308, i.e. nothing), < 1 ulp + the
+// table's half ulp.  11 FP64 operations and one shared-memory load.
+__device__ __forceinline__ double exp_tab(double x, const double* __restrict__ tab)
+{
+    double xc = x < -708.0 ? -708.0 : x;
+    int k;
+    double kd = rint_magic_i(xc * KC_EXPT[0], k);
+    double r = kfma(-kd, KC_EXPT[1], xc);  // exact
+    r = kfma(-kd, KC_EXPT[2], r);
+    double q = kfma(r, KC_EXPT[3], KC_EXPT[4]);
+    q = kfma(q, r, KC_EXPT[5]);
+    q = kfma(q, r, KC_EXPT[6]);
+    double pl = kfma(q, r * r, r);         // e^r - 1
+    const double tj = tab[k & 63];
+    double v = kfma(tj, pl, tj);
+    // 2^(k >> 6), k >> 6 in [-1022, 0]: a normal number, built as a high word
+    return v * __hiloint2double(((k >> 6) + 1023) << 20, 0);
+}
+
+// s = sin(pi t / eta3), c = cos(pi t / eta3) to <= 2 ulp for any finite t: the quotient in double-double
+// (q correctly rounded, the remainder t - q eta3 is exact), its integer part dropped exactly.
+__device__ __forceinline__ void gp_phase(const GpConsts& g, double t, double& s, double& c)
+{
+    double q = div_by(t, g.eta3, g.r_eta3);
+    double ql = kfma(-q, g.eta3, t) * g.r_eta3;
+    double n = rint(q);
+    double w = (q - n) + ql;
+    sincospi(w, &s, &c);
+    // an odd integer part flips both (|q| >= 2^53 has no odd values; NaN stays NaN)
+    if (fabs(n) < 9.0e15 && (((long long)n) & 1)) {
+        s = -s;
+        c = -c;
+    }
+}
+
+// One off-diagonal entry from the phases of its two epochs.
+__device__ __forceinline__ double qp_entry(const GpConsts& g, const double* __restrict__ tab, double tau,
+                                           double si, double ci, double sj, double cj)
+{
+    double sd = kfma(-ci, sj, si * cj);           // sin(pi tau / eta3)
+    double e = kfma(sd * sd, g.g2, (tau * tau) * g.g1);
+    return g.eta1sq * exp_tab(e, tab);
+}
 
 // Per-lane state of the blocked path, living beside the factor storage in HBM.
 struct __align__(16) GpLane {
@@ -126,6 +211,8 @@ __device__ __forceinline__ GpConsts gp_consts(const ParticleScalars& sc)
     g.eta2 = sc.eta2; g.r_eta2 = kdiv(1.0, sc.eta2);
     g.eta3 = sc.eta3; g.r_eta3 = kdiv(1.0, sc.eta3);
     g.eta4 = sc.eta4; g.r_eta4 = kdiv(1.0, sc.eta4);
+    g.g1 = kdiv(-0.5, kmul(sc.eta2, sc.eta2));
+    g.g2 = kdiv(-2.0, kmul(sc.eta4, sc.eta4));
     return g;
 }
 

@@ -44,6 +44,7 @@ struct Hdr {
     ParticleScalars sc;
     GpConsts g;
     double dinv[T];
+    double etab[64];           // 2^(j/64) for exp_tab
     double quad;
     int base[MAXBLK];
     int ld[MAXBLK];
@@ -63,7 +64,7 @@ size_t gps_smem_bytes(int N)
     using namespace gps;
     const int nb = (N + T - 1) / T;
     if (nb > MAXBLK) return 0;
-    size_t d = 2 * (size_t)npad(N) + SLACK;
+    size_t d = 4 * (size_t)npad(N) + SLACK;  // epochs, noise variances, sin and cos of the phases
     for (int J = 0; J < nb; J++) d += (size_t)T * ld_for(N + 1 - T * J);
     size_t bytes = hdr_bytes() + d * sizeof(double);
     return bytes <= SMEM_LIMIT ? bytes : 0;
@@ -109,7 +110,10 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
     const int row = T * I + lane;
     const int c0 = j0 + GW * q;
     const bool row_ok = row < N;
-    const double trow = tS[row_ok ? row : N - 1];
+    const int NP = npad(N);
+    const double* sS = nS + NP;   // sin, cos of the phases (gp_phase), behind the noise variances
+    const double* cS = sS + NP;
+    const double trow = tS[row_ok ? row : N - 1], srow = sS[row_ok ? row : N - 1], crow = cS[row_ok ? row : N - 1];
     double* dst = M + H.base[J] + (size_t)(GW * q) * H.ld[J] + (row - j0);
     const int ldj = H.ld[J];
     const GpConsts g = H.g;
@@ -117,9 +121,9 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
     for (int cc = 0; cc < GW; cc += 2) {
         const int ca = c0 + cc, cb = ca + 1;
         // t[i]-t[j] with i<j (:193): i is the column (smaller index) of the lower triangle
-        const double ta = tS[ca < N ? ca : N - 1], tb = tS[cb < N ? cb : N - 1];
-        double va, vb;
-        qp_kernel2(g, kadd(ta, -trow), kadd(tb, -trow), va, vb);
+        const int ia = ca < N ? ca : N - 1, ib = cb < N ? cb : N - 1;
+        double va = qp_entry(g, H.etab, kadd(tS[ia], -trow), sS[ia], cS[ia], srow, crow);
+        double vb = qp_entry(g, H.etab, kadd(tS[ib], -trow), sS[ib], cS[ib], srow, crow);
         if (row_ok) {
             // eta1^2 * exp(-0 - 0) + sig^2 + jit^2 on the diagonal (:199-206)
             if (ca == row) va = kadd(g.eta1sq, nS[row]);
@@ -285,7 +289,9 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
     const int NP = npad(N);
     double* tS = reinterpret_cast<double*>(gps_smem + hdr_bytes());
     double* nS = tS + NP;
-    double* M = nS + NP;
+    double* sS = nS + NP;
+    double* cS = sS + NP;
+    double* M = cS + NP;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int b = blockIdx.x;
     const int nb = (N + T - 1) / T;
@@ -311,10 +317,13 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
     {
         const bool multi = p.F.multi_instrument != 0;
         for (int i = tid; i < N; i += THREADS) {
-            tS[i] = __ldg(p.t + i);
+            const double ti = __ldg(p.t + i);
+            tS[i] = ti;
             const int in = multi ? __ldg(p.obsi + i) - 1 : 0;
             nS[i] = kadd(__ldg(p.sig2 + i), H.sc.jit2[in]);
+            gp_phase(H.g, ti, sS[i], cS[i]);
         }
+        exp_tab_load(H.etab, tid);
         // residual = y - mu (:845-847) into row N of the block column that owns epoch i
         if (p.F.MA) {
             // with the MA(1) term (:378-386): recurrence in the (still unused) factor storage

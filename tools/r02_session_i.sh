@@ -1,12 +1,12 @@
 #!/bin/bash
 # r02 session i/l: parity gate (blocked path vs the C port), gps and blocked timings, GPU parity tests
-OUT=gpurun_out/r02l; mkdir -p $OUT
+OUT=gpurun_out/r02n; mkdir -p $OUT
 
 timeout 300 python tools/dev_gp.py parity > $OUT/dev_gp_parity.jsonl 2>&1; rc=$?; echo "parity rc=$rc" >> $OUT/dev_gp_parity.jsonl
 python - <<'PY'
 import json
 mx=0
-for l in open("gpurun_out/r02l/dev_gp_parity.jsonl"):
+for l in open("gpurun_out/r02n/dev_gp_parity.jsonl"):
     if l.startswith("{"):
         d=json.loads(l); mx=max(mx,d["max"])
         if d["max"]>1e-10 or not d["inf_match"]: print("BAD", d)
