@@ -121,7 +121,7 @@ struct GpConsts {
 //   * exp(x), x <= 0, from a 64-entry table of 2^(j/64) and a degree-5 polynomial on |r| <= ln2/128.
 // 19 FP64 operations per entry.  The entries agree with the reference's to a few 1e-16 eta1^2 -- the
 // same distance the reference's own entries have from an 80-bit evaluation of the kernel
-// (variants/fastgen/proto.py; tests/test_gpu_parity.py pins the bound through kc_gp_cov).
+// (tools/gp_generator_error_budget.py; tests/test_gpu_parity.py pins the bound through kc_gp_cov).
 static __device__ const double KC_EXP2_TAB[64] = {
     1.00000000000000000e+00, 1.01088928605170048e+00, 1.02189714865411663e+00, 1.03302487902122841e+00,
     1.04427378242741375e+00, 1.05564517836055716e+00, 1.06714040067682370e+00, 1.07876079775711986e+00,
@@ -204,16 +204,20 @@ struct __align__(16) GpLane {
 };
 static_assert(sizeof(GpLane) % 16 == 0, "lanes[] elements stay 16-byte aligned");
 
-__device__ __forceinline__ GpConsts gp_consts(const ParticleScalars& sc)
+__device__ __forceinline__ GpConsts gp_consts(double eta1, double eta2, double eta3, double eta4)
 {
     GpConsts g;
-    g.eta1sq = kmul(sc.eta1, sc.eta1);
-    g.eta2 = sc.eta2; g.r_eta2 = kdiv(1.0, sc.eta2);
-    g.eta3 = sc.eta3; g.r_eta3 = kdiv(1.0, sc.eta3);
-    g.eta4 = sc.eta4; g.r_eta4 = kdiv(1.0, sc.eta4);
-    g.g1 = kdiv(-0.5, kmul(sc.eta2, sc.eta2));
-    g.g2 = kdiv(-2.0, kmul(sc.eta4, sc.eta4));
+    g.eta1sq = kmul(eta1, eta1);
+    g.eta2 = eta2; g.r_eta2 = kdiv(1.0, eta2);
+    g.eta3 = eta3; g.r_eta3 = kdiv(1.0, eta3);
+    g.eta4 = eta4; g.r_eta4 = kdiv(1.0, eta4);
+    g.g1 = kdiv(-0.5, kmul(eta2, eta2));
+    g.g2 = kdiv(-2.0, kmul(eta4, eta4));
     return g;
+}
+__device__ __forceinline__ GpConsts gp_consts(const ParticleScalars& sc)
+{
+    return gp_consts(sc.eta1, sc.eta2, sc.eta3, sc.eta4);
 }
 
 // C(i,j) off the diagonal, with the reference's roundings (:193-194):
@@ -301,8 +305,10 @@ __device__ __forceinline__ int ld_acquire_cta(const int* p)
 
 constexpr int CHOL_PANEL = 8;
 
+// The same with the panel loop rolled (a quarter of the code; ~16 % slower alone: the trailing update's block
+// structure is then run-time control flow).
 template <bool MASK>
-__device__ __forceinline__ bool chol32_panels(double* S, int ldS, int lane, int nvalid, double& logdet,
+__device__ __forceinline__ bool chol32_panels_rolled(double* S, int ldS, int lane, int nvalid, double& logdet,
                                               double* dinv_out, double* __restrict__ Lout, size_t ld,
                                               int* progress = nullptr, int progress_base = 0)
 {
@@ -387,6 +393,106 @@ __device__ __forceinline__ bool chol32_panels(double* S, int ldS, int lane, int 
             __syncwarp();
         }
     }
+    double lg = lane < nvalid ? log(lmine) : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(FULL, lg, o);
+    logdet += lg;
+    return ok;
+}
+
+// One 8-column panel (P = 0 .. 3, compile time: the trailing update's block structure is then straight-line code).
+template <bool MASK, int P>
+__device__ __forceinline__ void chol32_panel(double* S, int ldS, int lane, int nvalid, bool& ok, double& lmine,
+                                             double* dinv_out, double* __restrict__ Lout, size_t ld, int* progress,
+                                             int progress_base)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int c0 = CHOL_PANEL * P;
+    const int fr = lane >> 2, fk = lane & 3;
+    // ---- the panel: 8 columns of row `lane` ----
+    double a[CHOL_PANEL];
+#pragma unroll
+    for (int k = 0; k < CHOL_PANEL; k++) {
+        const int c = c0 + k;
+        double v = (lane == c) ? 1.0 : 0.0;  // identity padding of a partial block; zeros above the diagonal
+        if (lane < nvalid && c <= lane) v = S[c * ldS + lane];
+        a[k] = v;
+    }
+    double d = __shfl_sync(FULL, a[0], c0), inv, l;
+    chol_pivot(d, inv, l);
+#pragma unroll
+    for (int k = 0; k < CHOL_PANEL; k++) {
+        const int c = c0 + k;
+        if (!(d > 0.0)) ok = false;  // NaN or non-positive pivot; the NaNs that follow are discarded
+        if (lane == c) lmine = l;
+        if (lane == k) dinv_out[c] = inv;
+        const double lrc = a[k] * inv;  // L(lane, c) below the diagonal
+        const double lcc = l;
+        if (k + 1 < CHOL_PANEL) {
+            // The next pivot is known to lane c+1 before the column is passed round:
+            // S(c+1,c+1) - L(c+1,c)^2, the same FMA the update below performs.  Its rsqrt
+            // chain (latency-bound) overlaps the shuffles + FMAs of the rest of the panel.
+            d = __shfl_sync(FULL, kfma(-lrc, lrc, a[k + 1]), c + 1);
+            chol_pivot(d, inv, l);
+#pragma unroll
+            for (int k2 = k + 1; k2 < CHOL_PANEL; k2++)
+                a[k2] = kfma(-lrc, __shfl_sync(FULL, lrc, c0 + k2), a[k2]);
+        }
+        a[k] = (lane == c) ? lcc : lrc;
+    }
+#pragma unroll
+    for (int k = 0; k < CHOL_PANEL; k++) {
+        const int c = c0 + k;
+        if (lane >= c && lane < nvalid) {
+            S[c * ldS + lane] = a[k];
+            if (Lout) Lout[(size_t)c * ld + lane] = a[k];
+        }
+    }
+    __syncwarp();
+    if (progress && lane == 0) st_release_cta(progress, progress_base + c0 + CHOL_PANEL);
+    // ---- trailing update of the block on the tensor cores: S(i,j) -= sum_k L(i,k) L(j,k) ----
+    if (P < 3) {
+        double af[4][2];  // fragments of L[8I .. 8I+7, panel]: A operand of row block I, B operand of column block I
+#pragma unroll
+        for (int I = P + 1; I < 4; I++) {
+            af[I][0] = af[I][1] = 0.0;
+            const int row = 8 * I + fr;
+            if (!MASK || row < nvalid) {
+                af[I][0] = S[(c0 + fk) * ldS + row];
+                af[I][1] = S[(c0 + 4 + fk) * ldS + row];
+            }
+        }
+#pragma unroll
+        for (int J = P + 1; J < 4; J++) {
+#pragma unroll
+            for (int I = J; I < 4; I++) {
+                double u0 = 0.0, u1 = 0.0;
+                dmma(u0, u1, af[I][0], af[J][0]);
+                dmma(u0, u1, af[I][1], af[J][1]);
+                const int row = 8 * I + fr;
+                double* q = S + (8 * J + 2 * fk) * ldS + row;
+                if (!MASK || row < nvalid) {
+                    q[0] -= u0;
+                    q[ldS] -= u1;
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+template <bool MASK>
+__device__ __forceinline__ bool chol32_panels(double* S, int ldS, int lane, int nvalid, double& logdet,
+                                              double* dinv_out, double* __restrict__ Lout, size_t ld,
+                                              int* progress = nullptr, int progress_base = 0)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    bool ok = true;
+    double lmine = 1.0;  // lane c keeps L(c,c) for the log-determinant
+    chol32_panel<MASK, 0>(S, ldS, lane, nvalid, ok, lmine, dinv_out, Lout, ld, progress, progress_base);
+    chol32_panel<MASK, 1>(S, ldS, lane, nvalid, ok, lmine, dinv_out, Lout, ld, progress, progress_base);
+    chol32_panel<MASK, 2>(S, ldS, lane, nvalid, ok, lmine, dinv_out, Lout, ld, progress, progress_base);
+    chol32_panel<MASK, 3>(S, ldS, lane, nvalid, ok, lmine, dinv_out, Lout, ld, progress, progress_base);
     double lg = lane < nvalid ? log(lmine) : 0.0;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(FULL, lg, o);

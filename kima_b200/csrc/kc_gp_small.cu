@@ -34,8 +34,11 @@ namespace gps {
 constexpr int T = 32;
 constexpr int WARPS_PER_SM = 16;      // 128 registers per thread: 1 x 16, 2 x 8, 3 x 5 or 4 x 4 warps fill the register file
 constexpr int MAXBLK = 8;
-constexpr int GW = 4;              // columns per generation item: two qp_kernel2 calls, four independent chains per lane
-constexpr int GQ = T / GW;         // generation items per 32x32 tile
+// Columns per generation item = independent qp_entry chains per lane: 8 where a particle has 7 or more
+// workers (3-7 % faster at N = 100 .. 208 than 4), 4 in the 4- and 5-warp CTAs of the smallest sizes, where an
+// 8-column item keeps one of three workers away from the factorisation for too long
+// (profiles/gps_variants_r02.txt).
+__host__ __device__ constexpr int gw_for(int nw) { return nw >= 8 ? 8 : 4; }
 constexpr int SLACK = 64;          // doubles past the last block column (strips read, never use, rows > N)
 constexpr size_t SMEM_LIMIT = 227 * 1024;
 
@@ -43,14 +46,20 @@ struct Hdr {
     PlanetInv inv[MAX_PLANETS];
     ParticleScalars sc;
     GpConsts g;
-    double dinv[T];
+    double dinv[2][T];         // 1 / diag(L_JJ), double-buffered by block parity (T_J may still read while block J+1 is factored)
     double etab[64];           // 2^(j/64) for exp_tab
     double quad;
     int base[MAXBLK];
     int ld[MAXBLK];
     int gen_end[MAXBLK];
     int gen_next, u_done, d_done, col_done;
+    int gen0;                  // generation items of block column 0; the residual items sit behind them in the queue
+    int setup_done, mean_cnt;  // planet invariants ready / finished residual items
+    int t0_done;               // J + 1 once T_J has finished the tile below the diagonal block (the rows of block J + 1)
+    int pre_cnt[MAXBLK];       // strips of the diagonal tile of block column J updated one block column behind
     int tile_cnt[MAXBLK + 1];  // block column 0: finished generation items per 32-row tile
+    int dcnt[MAXBLK];          // block column J > 0: finished generation items of its diagonal tile
+    int ccnt[MAXBLK];          // finished queue items of block column J (its covariance entries; for J = 0 the residuals too)
 };
 
 __host__ __device__ inline int ld_for(int rows) { return ((rows + 11) & ~15) + 4; }  // >= rows, = 4 mod 16
@@ -78,11 +87,29 @@ using namespace gps;
 #ifndef KC_GPS_ISOLATE
 #define KC_GPS_ISOLATE 0    // 16-warp CTAs: warps 4, 8, 12 (the diag warp's scheduler) stay idle
 #endif
-#ifndef KC_GPS_LOOKAHEAD
-#define KC_GPS_LOOKAHEAD 1  // U_J: the strips of the diagonal block first, then the diag warp starts
+#ifndef KC_GPS_ENDBAR
+#define KC_GPS_ENDBAR 0     // CTAs of fewer than 16 warps: all workers meet at the end of every step
 #endif
-#ifndef KC_GPS_TILEGEN
-#define KC_GPS_TILEGEN 0    // block column 0: factorisation / substitution start per generated tile
+#ifndef KC_GPS_ROLLED
+#define KC_GPS_ROLLED(nw) ((nw) == 8 || (nw) == 5)
+#endif
+#ifndef KC_GPS_GENONLY
+#define KC_GPS_GENONLY 0    // 16-warp CTAs: warps 4, 8, 12 only take queue items (covariance entries, residuals): no tensor-core work beside the diag warp
+#endif
+#ifndef KC_GPS_SETUP_BY_DIAG
+#define KC_GPS_SETUP_BY_DIAG 1  // the planet invariants by the diag warp (idle until the first tile exists), not by a worker
+#endif
+#ifndef KC_GPS_SLEEP_T
+#define KC_GPS_SLEEP_T 20
+#endif
+#ifndef KC_GPS_SLEEP_D
+#define KC_GPS_SLEEP_D 40
+#endif
+#ifndef KC_GPS_SLEEP_F
+#define KC_GPS_SLEEP_F 40
+#endif
+#ifdef KC_GPS_PROFILE
+__device__ long long g_prof_twait[1024], g_prof_tsub[1024], g_prof_tdmma[1024];   // per CTA (mod 1024): cycles warp 1 waited for col_done inside trsm_tile
 #endif
 template <int WORKERS>
 __device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"(WORKERS * 32) : "memory"); }
@@ -99,9 +126,11 @@ __device__ __forceinline__ int ld_uniform(const int* p, int lane)
 }
 
 // One generation item: rows 32I .. 32I+31 (a row per lane) x GW columns of block column J.
+template <int GW>
 __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS, double* M,
                                          int N, int item, int nb, int lane)
 {
+    constexpr int GQ = T / GW;  // generation items per 32x32 tile
     int J = 0;
     while (item >= H.gen_end[J]) J++;
     const int local = item - (J ? H.gen_end[J - 1] : 0);
@@ -117,6 +146,18 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
     double* dst = M + H.base[J] + (size_t)(GW * q) * H.ld[J] + (row - j0);
     const int ldj = H.ld[J];
     const GpConsts g = H.g;
+    if (I > J) {
+        // a tile below the diagonal: every column is an epoch before every row, nothing to select --
+        // GW independent chains per lane, one predicate on the stores (rows past N - 1: row N is the residual)
+        double v[GW];
+#pragma unroll
+        for (int k = 0; k < GW; k++)
+            v[k] = qp_entry(g, H.etab, kadd(tS[c0 + k], -trow), sS[c0 + k], cS[c0 + k], srow, crow);
+        if (row_ok) {
+#pragma unroll
+            for (int k = 0; k < GW; k++) dst[(size_t)k * ldj] = v[k];
+        }
+    } else
 #pragma unroll
     for (int cc = 0; cc < GW; cc += 2) {
         const int ca = c0 + cc, cb = ca + 1;
@@ -132,12 +173,46 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
             if (cb <= row && cb < N) dst[(size_t)(cc + 1) * ldj] = vb;
         }
     }
-#if KC_GPS_TILEGEN
-    if (J == 0) {
-        __syncwarp();
-        if (lane == 0) red_release_add(&H.tile_cnt[I], 1);
+    __syncwarp();
+    if (lane == 0) {
+        // block column 0 is consumed tile by tile (the diag warp and T_0 start as soon as their tile exists);
+        // U_J's look-ahead strips start as soon as the diagonal tile of block column J exists
+        if (J == 0) red_release_add(&H.tile_cnt[I], 1);
+        else if (I == J) red_release_add(&H.dcnt[J], 1);
+        red_release_add(&H.ccnt[J], 1);
     }
-#endif
+}
+
+// One residual item: y - mu (:845-847) at 32 epochs, an epoch per lane, into row N of the block columns
+// that own them.  Needs the planet invariants (setup_done); same summation order as model_mu2.
+template <int MODE>
+__device__ __noinline__ void mean_item(const KParams& p, Hdr& H, double* M, int N, int m, int lane)
+{
+    while (ld_uniform(&H.setup_done, lane) == 0) __nanosleep(KC_GPS_SLEEP_F);
+    const int i = T * m + lane;
+    if (i < N) {
+        const double ti = __ldg(p.t + i);
+        const int in = p.F.multi_instrument ? __ldg(p.obsi + i) - 1 : 0;
+        double mu = model_background(p, &H.sc, i, ti, in);
+        const int npl = H.sc.npl;
+        for (int j = 0; j < npl; j++) mu += kepler_term<MODE>(H.inv[j], ti);
+        const int J = i / T;
+        M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = __ldg(p.y + i) - mu;
+    }
+    __syncwarp();
+    if (lane == 0) {
+        red_release_add(&H.mean_cnt, 1);
+        red_release_add(&H.ccnt[0], 1);
+    }
+}
+
+// Whatever the queue holds at position `it`: covariance entries, or (behind block column 0) residuals.
+template <int MODE, int GW>
+__device__ __forceinline__ void work_item(const KParams& p, Hdr& H, const double* tS, const double* nS, double* M,
+                                          int N, int it, int nb, int lane)
+{
+    if (it >= H.gen0 && it < H.gen_end[0]) mean_item<MODE>(p, H, M, N, it - H.gen0, lane);
+    else gen_item<GW>(H, tS, nS, M, N, it, nb, lane);
 }
 
 __device__ __forceinline__ int claim(Hdr& H, int lane)
@@ -151,14 +226,15 @@ __device__ __forceinline__ int claim(Hdr& H, int lane)
 // all earlier block columns, one read-modify-write of the strip at the end.  8 rows (one
 // fragment row) per item: at these sizes the number of items per step, not the operand
 // reuse, decides how many of the four tensor pipes are busy.
-__device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int J, int strip, int lane)
+__device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int J, int strip, int lane, int k_begin,
+                                             int k_end)
 {
     const int j0 = T * J;
     const int r0 = j0 + 8 * strip;
     double acc[4][2];
 #pragma unroll
     for (int n = 0; n < 4; n++) acc[n][0] = acc[n][1] = 0.0;
-    for (int Jk = 0; Jk < J; Jk++) {
+    for (int Jk = k_begin; Jk < k_end; Jk++) {
         const int ldk = H.ld[Jk];
         const double* Acol = M + H.base[Jk] + (r0 - T * Jk) + (lane >> 2) + (size_t)(lane & 3) * ldk;
         const double* Bcol = M + H.base[Jk] + (j0 - T * Jk) + (lane >> 2) + (size_t)(lane & 3) * ldk;
@@ -186,21 +262,98 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
     }
 }
 
+// The same for a full block (32 columns, every block but a partial last one): no column bounds, so the
+// panel is straight-line code -- 1/diag, the lane's 8 entries and the 28 entries of the panel's triangle are
+// all in flight before the substitution chain starts (8 x (multiply, fused multiply-add) = ~140 cycles, where
+// the bounds-checked version above spends ~1200 per panel waiting for its loads one column at a time), and the
+// trailing update's blocks are unrolled.  ROLLED keeps the panel loop rolled (a quarter of the code).
+template <bool ROLLED>
+__device__ __forceinline__ void trsm_tile_full(Hdr& H, double* M, int N, int J, int tile, int lane)
+{
+    const int j0 = T * J;
+    const int row0 = T + T * tile;  // first row of the tile, relative to j0
+    const int row = j0 + row0 + lane;
+    const bool ok = row <= N;
+    const int ldj = H.ld[J];
+    double* S = M + H.base[J];
+    double* mine = S + (ok ? row0 + lane : T);
+    double* tileS = S + row0;
+    const int fr = lane >> 2, fk = lane & 3;
+    const double* dinv = H.dinv[J & 1];
+    // rows past N of the last tile: computed on a clamped address, never stored
+    bool rok[4];
+#pragma unroll
+    for (int Ir = 0; Ir < 4; Ir++) rok[Ir] = j0 + row0 + 8 * Ir + fr <= N;
+    double q = 0.0;
+    auto panel = [&](const int p) {
+        const int c0 = CHOL_PANEL * p;
+        while (ld_uniform(&H.col_done, lane) < j0 + c0 + CHOL_PANEL) __nanosleep(KC_GPS_SLEEP_T);
+        double x[CHOL_PANEL], dv[CHOL_PANEL], l[CHOL_PANEL][CHOL_PANEL];
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++) {
+            x[k] = mine[(size_t)(c0 + k) * ldj];
+            dv[k] = dinv[c0 + k];
+        }
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++)
+#pragma unroll
+            for (int k2 = k + 1; k2 < CHOL_PANEL; k2++) l[k][k2] = S[(size_t)(c0 + k) * ldj + c0 + k2];  // L_JJ(c0 + k2, c0 + k)
+#pragma unroll
+        for (int k = 0; k < CHOL_PANEL; k++) {
+            const double x0 = x[k] * dv[k];
+            x[k] = x0;
+            q = kfma(x0, x0, q);
+#pragma unroll
+            for (int k2 = k + 1; k2 < CHOL_PANEL; k2++) x[k2] = kfma(-x0, l[k][k2], x[k2]);
+        }
+        if (ok) {
+#pragma unroll
+            for (int k = 0; k < CHOL_PANEL; k++) mine[(size_t)(c0 + k) * ldj] = x[k];
+        }
+        __syncwarp();
+        if (p < T / CHOL_PANEL - 1) {
+            // A fragments: X(tile row 8 Ir + fr, panel column 4 h + fk)
+            double af[4][2];
+#pragma unroll
+            for (int Ir = 0; Ir < 4; Ir++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) af[Ir][h] = tileS[(size_t)(c0 + 4 * h + fk) * ldj + 8 * Ir + fr];
+#pragma unroll
+            for (int cbi = p + 1; cbi < T / 8; cbi++) {
+                const int cb = 8 * cbi;
+                // B fragment: L_JJ(cb + fr, panel column 4 h + fk)
+                const double b0 = S[(size_t)(c0 + fk) * ldj + cb + fr], b1 = S[(size_t)(c0 + 4 + fk) * ldj + cb + fr];
+#pragma unroll
+                for (int Ir = 0; Ir < 4; Ir++) {
+                    double u0 = 0.0, u1 = 0.0;
+                    dmma(u0, u1, af[Ir][0], b0);
+                    dmma(u0, u1, af[Ir][1], b1);
+                    double* qd = tileS + (size_t)(cb + 2 * fk) * ldj + 8 * Ir + fr;
+                    if (rok[Ir]) {
+                        qd[0] -= u0;
+                        qd[ldj] -= u1;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    };
+    if constexpr (ROLLED) {
+#pragma unroll 1
+        for (int p = 0; p < T / CHOL_PANEL; p++) panel(p);
+    } else {
+#pragma unroll
+        for (int p = 0; p < T / CHOL_PANEL; p++) panel(p);
+    }
+    if (ok && row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
+}
+
 // T_J for 32 rows below the diagonal block: X L_JJ^T = S in place, a row per lane, following the
 // diag warp panel by panel (8 columns).  Within a panel: plain substitution on the 8 columns of
 // the lane's row in registers (L_JJ read as shared-memory broadcasts); the columns to the right
 // of the panel are then updated on the tensor cores, X[:, rest] -= X[:, panel] L_JJ[rest, panel]^T,
 // fragments read-modify-written in shared memory: 4x fewer issue slots than a 31-wide register
 // window per column.
-#ifndef KC_GPS_SLEEP_T
-#define KC_GPS_SLEEP_T 20
-#endif
-#ifndef KC_GPS_SLEEP_D
-#define KC_GPS_SLEEP_D 40
-#endif
-#ifndef KC_GPS_SLEEP_F
-#define KC_GPS_SLEEP_F 40
-#endif
 __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int nbc, int tile, int lane)
 {
     const int j0 = T * J;
@@ -216,7 +369,14 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
 #pragma unroll 1
     for (int c0 = 0; c0 < nbc; c0 += CHOL_PANEL) {
         const int want = j0 + min(c0 + CHOL_PANEL, nbc);
+#ifdef KC_GPS_PROFILE
+        long long tw0 = clock64();
+#endif
         while (ld_uniform(&H.col_done, lane) < want) __nanosleep(KC_GPS_SLEEP_T);
+#ifdef KC_GPS_PROFILE
+        long long tw1 = clock64();
+        if (threadIdx.x == 32) g_prof_twait[blockIdx.x & 1023] += tw1 - tw0;
+#endif
         double x[CHOL_PANEL];
 #pragma unroll
         for (int k = 0; k < CHOL_PANEL; k++) x[k] = mine[(size_t)min(c0 + k, nbc - 1) * ldj];
@@ -224,7 +384,7 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
         for (int k = 0; k < CHOL_PANEL; k++) {
             const int c = c0 + k;
             if (c < nbc) {  // warp-uniform
-                const double x0 = x[k] * H.dinv[c];
+                const double x0 = x[k] * H.dinv[J & 1][c];
                 x[k] = x0;
                 q = kfma(x0, x0, q);
                 const double* lc = S + (size_t)c * ldj + c0;  // lc[k2] = L_JJ(c0 + k2, c)
@@ -236,6 +396,10 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
         for (int k = 0; k < CHOL_PANEL; k++)
             if (ok && c0 + k < nbc) mine[(size_t)(c0 + k) * ldj] = x[k];
         __syncwarp();
+#ifdef KC_GPS_PROFILE
+        long long tw2 = clock64();
+        if (threadIdx.x == 32) g_prof_tsub[blockIdx.x & 1023] += tw2 - tw1;
+#endif
         if (c0 + CHOL_PANEL < nbc) {
             // A fragments: X(tile row 8 Ir + fr, panel column 4 h + fk); columns past a partial block are zero
             double af[4][2];
@@ -271,6 +435,9 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
             }
             __syncwarp();
         }
+#ifdef KC_GPS_PROFILE
+        if (threadIdx.x == 32) g_prof_tdmma[blockIdx.x & 1023] += clock64() - tw2;
+#endif
     }
     if (ok && row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
 }
@@ -281,8 +448,19 @@ template <int MODE, int NW>
 __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const KParams p)
 {
     constexpr int THREADS = NW * 32;
+    constexpr int GW = gw_for(NW), GQ = T / GW;
+    // 16-warp CTAs (one particle per SM, N > 128): the next diagonal tile is updated one block column behind,
+    // off the critical path (+3-4 % at N = 177, 208; with 7 or fewer workers it costs more than it saves)
+    constexpr bool PRE = NW >= 16;
+    // Two 8-warp or three 5-warp CTAs per SM run measurably faster with the panel loops of the factorisation
+    // and of the substitution rolled (N = 100: 1.19 -> 1.10 ms per 8192 lanes, N = 128: 1.37 -> 1.20, N = 96:
+    // 0.768 -> 0.731; the unrolled code of several particles in different phases does not fit the instruction
+    // cache), one 16-warp or four 4-warp CTAs with them unrolled (N = 177: 2.71 -> 2.62 ms, N = 64: 0.421 ->
+    // 0.399; profiles/gps_variants_r02.txt)
+    constexpr bool ROLLED = KC_GPS_ROLLED(NW);
     constexpr bool ISO = KC_GPS_ISOLATE && NW == 16;
-    constexpr int WORKERS = ISO ? NW - 4 : NW - 1;
+    constexpr bool GENONLY = KC_GPS_GENONLY && NW == 16 && !ISO;
+    constexpr int WORKERS = (ISO || GENONLY) ? NW - 4 : NW - 1;
     extern __shared__ __align__(16) unsigned char gps_smem[];
     Hdr& H = *reinterpret_cast<Hdr*>(gps_smem);
     const int N = p.N;
@@ -295,168 +473,261 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int b = blockIdx.x;
     const int nb = (N + T - 1) / T;
+#ifdef KC_GPS_PROFILE
+    __shared__ long long prof_c[4];
+    if (tid == 0) prof_c[0] = clock64();
+#endif
 
-    if (warp == 0) {
-        particle_setup(p, b, H.inv, &H.sc, lane);
-        if (lane == 0) {
-            H.g = gp_consts(H.sc);
+    // ---- start-up.  Nothing the factorisation's first steps need waits for the planets: every thread reads
+    // the four GP hyperparameters and its epochs' jitter itself (covariance entries need nothing else), the
+    // planet invariants are prepared by the last worker warp while the others already generate block column 0,
+    // and the residuals y - mu are queue items behind that block column (first needed by the last tile of T_0).
+    {
+        const kc_layout& L = p.L;
+        const GpConsts g = gp_consts(ldp(p, L.row_eta, b), ldp(p, L.row_eta + 1, b), ldp(p, L.row_eta + 2, b),
+                                     ldp(p, L.row_eta + 3, b));
+        const bool multi = p.F.multi_instrument != 0;
+        for (int i = tid; i < N; i += THREADS) {
+            const double ti = __ldg(p.t + i);
+            tS[i] = ti;
+            const int in = multi ? __ldg(p.obsi + i) - 1 : 0;
+            double j2 = 0.0;
+            if (in < L.n_jit) {
+                const double jt = ldp(p, L.row_jit + in, b);
+                j2 = kmul(jt, jt);
+            }
+            nS[i] = kadd(__ldg(p.sig2 + i), j2);
+            gp_phase(g, ti, sS[i], cS[i]);
+        }
+        exp_tab_load(H.etab, tid);
+        if (tid == THREADS - 1) {
+            H.g = g;
+            // residual items: none with the MA(1) term (its recurrence runs before the factorisation, below)
+            const int nm = p.F.MA ? 0 : (N + T - 1) / T;
             int off = 0, ge = 0;
             for (int J = 0; J < nb; J++) {
                 H.base[J] = off;
                 H.ld[J] = ld_for(N + 1 - T * J);
                 off += T * H.ld[J];
                 ge += (nb - J) * GQ;
-                H.gen_end[J] = ge;
+                if (J == 0) H.gen0 = ge;
+                H.gen_end[J] = ge + nm;
             }
             H.gen_next = 0; H.u_done = 0; H.d_done = 0; H.col_done = 0;
+            H.setup_done = 0; H.mean_cnt = 0; H.t0_done = 0;
+            for (int I = 0; I < MAXBLK; I++) H.pre_cnt[I] = 0;
             H.quad = 0.0;
             for (int I = 0; I <= MAXBLK; I++) H.tile_cnt[I] = 0;
+            for (int I = 0; I < MAXBLK; I++) H.dcnt[I] = H.ccnt[I] = 0;
         }
     }
-    __syncthreads();
-    {
-        const bool multi = p.F.multi_instrument != 0;
+    if (p.F.MA) {
+        // residual with the MA(1) term (:378-386): planets first, then the recurrence in the (still unused)
+        // factor storage, all threads
+        if (warp == 0) particle_setup(p, b, H.inv, &H.sc, lane);
+        __syncthreads();
+        double* rbuf = M;
+        ma_residuals<MODE>(p, &H.sc, H.inv, rbuf, rbuf + NP, tid, THREADS);
+        double rv[(MAXBLK * T + THREADS - 1) / THREADS];
+        int k = 0;
+        for (int i = tid; i < N; i += THREADS) rv[k++] = rbuf[i];
+        __syncthreads();
+        k = 0;
         for (int i = tid; i < N; i += THREADS) {
-            const double ti = __ldg(p.t + i);
-            tS[i] = ti;
-            const int in = multi ? __ldg(p.obsi + i) - 1 : 0;
-            nS[i] = kadd(__ldg(p.sig2 + i), H.sc.jit2[in]);
-            gp_phase(H.g, ti, sS[i], cS[i]);
+            const int J = i / T;
+            M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = rv[k++];
         }
-        exp_tab_load(H.etab, tid);
-        // residual = y - mu (:845-847) into row N of the block column that owns epoch i
-        if (p.F.MA) {
-            // with the MA(1) term (:378-386): recurrence in the (still unused) factor storage
-            __syncthreads();
-            double* rbuf = M;  // nothing of the factor storage is live yet
-            ma_residuals<MODE>(p, &H.sc, H.inv, rbuf, rbuf + NP, tid, THREADS);
-            double rv[(MAXBLK * T + THREADS - 1) / THREADS];
-            int k = 0;
-            for (int i = tid; i < N; i += THREADS) rv[k++] = rbuf[i];
-            __syncthreads();
-            k = 0;
-            for (int i = tid; i < N; i += THREADS) {
-                const int J = i / T;
-                M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = rv[k++];
-            }
-        } else
-        for (int i0 = tid; i0 < N; i0 += 2 * THREADS) {
-            int i1 = i0 + THREADS;
-            const bool has1 = i1 < N;
-            if (!has1) i1 = i0;
-            const double t0 = __ldg(p.t + i0), t1 = __ldg(p.t + i1);
-            const int in0 = multi ? __ldg(p.obsi + i0) - 1 : 0;
-            const int in1 = multi ? __ldg(p.obsi + i1) - 1 : 0;
-            double mu0, mu1;
-            model_mu2<MODE>(p, &H.sc, H.inv, i0, i1, t0, t1, in0, in1, mu0, mu1);
-            {
-                const int J = i0 / T;
-                M[H.base[J] + (size_t)(i0 % T) * H.ld[J] + (N - T * J)] = __ldg(p.y + i0) - mu0;
-            }
-            if (has1) {
-                const int J = i1 / T;
-                M[H.base[J] + (size_t)(i1 % T) * H.ld[J] + (N - T * J)] = __ldg(p.y + i1) - mu1;
-            }
-        }
+        if (tid == 0) H.setup_done = 1;
     }
     __syncthreads();
+#ifdef KC_GPS_PROFILE
+    if (tid == 0) prof_c[1] = clock64();
+#endif
 
     const int total_items = H.gen_end[nb - 1];
 #ifdef KC_GPS_PROFILE
     __shared__ long long prof_t[2][MAXBLK][4];
-    const bool prof = (b == 0) && lane == 0 && warp < 2;
+    const bool prof = (b == gridDim.x / 2) && lane == 0 && warp < 2;
     long long tp = clock64();
+    if (tid == 0) prof_c[2] = tp;
 #define PROF(tag)                                                                          \
     if (prof) { long long tn = clock64(); prof_t[warp][J][tag] = tn - tp; tp = tn; }
+    __shared__ long long prof_abs[MAXBLK][6];
+#define PABS(k) if (prof) prof_abs[J][k] = clock64() - prof_c[2];
 #else
 #define PROF(tag)
+#define PABS(k)
 #endif
     double logdet = 0.0;
     bool ok = true;
 
     if (warp == 0) {
         // ---- diag role ----
+#if KC_GPS_SETUP_BY_DIAG
+        if (!p.F.MA) {
+            // the planets (needed by the residual items only), while the workers generate the first tile
+            particle_setup(p, b, H.inv, &H.sc, lane);
+            if (lane == 0) st_release_cta(&H.setup_done, 1);
+        }
+#endif
         for (int J = 0; J < nb; J++) {
             const int j0 = T * J;
-#if KC_GPS_TILEGEN
+            // the first block as soon as its tile is generated, the others once U_J has updated them
             if (J == 0) while (ld_uniform(&H.tile_cnt[0], lane) < GQ) __nanosleep(KC_GPS_SLEEP_D);
-            else
-#endif
-            while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(KC_GPS_SLEEP_D);
+            else while (ld_uniform(&H.u_done, lane) < J + 1) __nanosleep(KC_GPS_SLEEP_D);
             PROF(0);
+            PABS(0);
             const int nv = min(T, N - j0);
-            if (!chol32_panels<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv, nullptr, 0,
-                                     &H.col_done, T * J))
-                ok = false;
+            bool fine;
+            if constexpr (ROLLED)
+                fine = chol32_panels_rolled<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv[J & 1], nullptr, 0,
+                                                  &H.col_done, T * J);
+            else
+                fine = chol32_panels<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv[J & 1], nullptr, 0,
+                                           &H.col_done, T * J);
+            if (!fine) ok = false;
             __syncwarp();
             if (lane == 0) st_release_cta(&H.d_done, J + 1);
             PROF(1);
+            PABS(1);
+        }
+    } else if (GENONLY && (warp & 3) == 0) {
+        // ---- the diag warp's scheduler mates: queue items only ----
+        while (ld_uniform(&H.gen_next, lane) < total_items) {
+            const int it = claim(H, lane);
+            if (it < total_items) work_item<MODE, GW>(p, H, tS, nS, M, N, it, nb, lane);
         }
     } else if (!(ISO && (warp & 3) == 0)) {
         // ---- worker role ----
-        const int wid = ISO ? warp - 1 - (warp >> 2) : warp - 1;
+        const int wid = (ISO || GENONLY) ? warp - 1 - (warp >> 2) : warp - 1;
+        if (!KC_GPS_SETUP_BY_DIAG && warp == NW - 1 && !p.F.MA) {
+            // the planets: needed by the residual items only, which sit behind block column 0 in the queue
+            particle_setup(p, b, H.inv, &H.sc, lane);
+            if (lane == 0) st_release_cta(&H.setup_done, 1);
+        }
         for (int J = 0; J < nb; J++) {
             const int j0 = T * J;
             const int nbc = min(T, N - j0);
-            // every entry of block column J exists before it is updated
-            while (ld_uniform(&H.gen_next, lane) < H.gen_end[J]) {
-                const int it = claim(H, lane);
-                if (it < total_items) gen_item(H, tS, nS, M, N, it, nb, lane);
-            }
-#if KC_GPS_TILEGEN
-            if (J > 0)   // block column 0 is followed tile by tile (tile_cnt), not as a whole
-#endif
-            worker_bar<WORKERS>();
-            PROF(0);
-            if (J > 0) {
+            if (J == 0) {
+                // block column 0 is followed tile by tile (tile_cnt), not as a whole; the residual items are
+                // claimed here too
+                while (ld_uniform(&H.gen_next, lane) < H.gen_end[0]) {
+                    const int it = claim(H, lane);
+                    if (it < total_items) work_item<MODE, GW>(p, H, tS, nS, M, N, it, nb, lane);
+                }
+                PROF(0);
+            } else {
+                // Only the diagonal tile of block column J stands between T_{J-1} and the next factorisation
+                // step: its (up to four) 8-row strips are updated as soon as it is generated, the diag warp
+                // starts, and the rest of the block column is generated and updated behind it.
                 const int nstrips = (N + 1 - j0 + 7) / 8;
-#if KC_GPS_LOOKAHEAD
-                // the four strips of the diagonal block first: the diag warp starts while the
-                // rows below are still being updated
                 const int ndiag = min(4, nstrips);
-                for (int s = wid; s < ndiag; s += WORKERS) update_strip(H, M, N, J, s, lane);
+                while (ld_uniform(&H.gen_next, lane) < H.gen_end[J - 1] + GQ) {
+                    const int it = claim(H, lane);
+                    if (it < total_items) work_item<MODE, GW>(p, H, tS, nS, M, N, it, nb, lane);
+                }
+                if (wid < ndiag) {
+                    // what the strips need: the tile generated, the rows of block J of T_{J-1} (its first tile),
+                    // and, one block column behind, the contributions of block columns 0 .. J-2 (below).  The
+                    // other tiles of T_{J-1} may still be running: nothing here touches them.
+                    while (ld_uniform(&H.dcnt[J], lane) < GQ) __nanosleep(KC_GPS_SLEEP_T);
+                    while (ld_uniform(&H.t0_done, lane) < J) __nanosleep(KC_GPS_SLEEP_T);
+                    if (PRE && J >= 2)
+                        while (ld_uniform(&H.pre_cnt[J], lane) < ndiag) __nanosleep(KC_GPS_SLEEP_T);
+                    for (int s = wid; s < ndiag; s += WORKERS) update_strip(H, M, N, J, s, lane, PRE ? J - 1 : 0, J);
+                    // the strip warps among themselves (barrier 2), then the diag warp may go
+                    asm volatile("bar.sync 2, %0;" ::"r"(min(ndiag, WORKERS) * 32) : "memory");
+                    if (wid == 0 && lane == 0) st_release_cta(&H.u_done, J + 1);
+                }
+                PROF(0);
+                PABS(2);
+                // before the rest of block column J is updated: every entry of it exists (the other workers
+                // have been generating since they left T_{J-1}) and T_{J-1} is complete -- one barrier for both
+                while (ld_uniform(&H.gen_next, lane) < H.gen_end[J]) {
+                    const int it = claim(H, lane);
+                    if (it < total_items) work_item<MODE, GW>(p, H, tS, nS, M, N, it, nb, lane);
+                }
+                if (GENONLY)  // items still in the hands of warps that are not part of the barrier
+                    while (ld_uniform(&H.ccnt[J], lane) < H.gen_end[J] - H.gen_end[J - 1]) __nanosleep(KC_GPS_SLEEP_T);
                 worker_bar<WORKERS>();
-                if (wid == 0 && lane == 0) st_release_cta(&H.u_done, J + 1);
-                for (int s = ndiag + wid; s < nstrips; s += WORKERS) update_strip(H, M, N, J, s, lane);
+                for (int s = ndiag + wid; s < nstrips; s += WORKERS) update_strip(H, M, N, J, s, lane, 0, J);
                 worker_bar<WORKERS>();
-#else
-                for (int s = wid; s < nstrips; s += WORKERS) update_strip(H, M, N, J, s, lane);
-                worker_bar<WORKERS>();
-#endif
             }
             PROF(1);
-            if (wid == 0 && lane == 0) st_release_cta(&H.u_done, J + 1);
+            if (PRE && J >= 1 && J + 1 < nb) {
+                // Off the critical path, while the diag warp factors block J: the diagonal tile of block column
+                // J+1 takes the contributions of block columns 0 .. J-1 now (all final), so that only block
+                // column J's is left between T_J and the next factorisation step.  The last workers do it
+                // (they have no T tile at the sizes with 7 or more workers).
+                const int nd1 = min(4, (N + 1 - (j0 + T) + 7) / 8);
+                const int rev = WORKERS - 1 - wid;
+                if (rev < nd1) {
+                    while (ld_uniform(&H.dcnt[J + 1], lane) < GQ) {
+                        // its generation items come first in the queue of block column J+1: help if unclaimed
+                        if (ld_uniform(&H.gen_next, lane) < H.gen_end[J] + GQ) {
+                            const int it = claim(H, lane);
+                            if (it < total_items) work_item<MODE, GW>(p, H, tS, nS, M, N, it, nb, lane);
+                        } else {
+                            __nanosleep(KC_GPS_SLEEP_T);
+                        }
+                    }
+                    int done = 0;
+                    for (int s = rev; s < nd1; s += WORKERS, done++) update_strip(H, M, N, J + 1, s, lane, 0, J);
+                    __syncwarp();
+                    if (lane == 0) red_release_add(&H.pre_cnt[J + 1], done);
+                }
+            }
             // T_J follows the diag warp column by column (one 32-row tile per warp); the
             // other workers generate ahead until the block is factored
+            PABS(3);
             const int first = j0 + nbc;
             const int ntiles = (N + 1 - first + T - 1) / T;
             if (wid < ntiles) {
                 for (int tl = wid; tl < ntiles; tl += WORKERS) {
-#if KC_GPS_TILEGEN
-                    // every item of block column 0 has been claimed by now: the tile completes without us
-                    if (J == 0 && tl + 1 < nb)
-                        while (ld_uniform(&H.tile_cnt[tl + 1], lane) < GQ) __nanosleep(KC_GPS_SLEEP_T);
-#endif
-                    trsm_tile(H, M, N, J, nbc, tl, lane);
+                    if (J == 0) {
+                        // every item of block column 0 has been claimed by now: the tile completes without us
+                        if (tl + 1 < nb)
+                            while (ld_uniform(&H.tile_cnt[tl + 1], lane) < GQ) __nanosleep(KC_GPS_SLEEP_T);
+                        // the last tile holds row N, the residuals
+                        if (tl == ntiles - 1)
+                            while (ld_uniform(&H.mean_cnt, lane) < H.gen_end[0] - H.gen0) __nanosleep(KC_GPS_SLEEP_T);
+                    }
+                    if (nbc == T) trsm_tile_full<ROLLED>(H, M, N, J, tl, lane);
+                    else trsm_tile(H, M, N, J, nbc, tl, lane);
+                    if (tl == 0) {
+                        __syncwarp();
+                        if (lane == 0) st_release_cta(&H.t0_done, J + 1);
+                    }
                 }
             } else {
                 while (ld_uniform(&H.d_done, lane) < J + 1) {
                     if (ld_uniform(&H.gen_next, lane) < total_items) {
                         const int it = claim(H, lane);
-                        if (it < total_items) gen_item(H, tS, nS, M, N, it, nb, lane);
+                        if (it < total_items) work_item<MODE, GW>(p, H, tS, nS, M, N, it, nb, lane);
                     } else {
                         __nanosleep(KC_GPS_SLEEP_F);
                     }
                 }
             }
             PROF(2);
-            worker_bar<WORKERS>();
-            PROF(3);
+            PABS(4);
+#if KC_GPS_ENDBAR
+            if (NW < 16) worker_bar<WORKERS>();
+#endif
         }
     }
     __syncthreads();
 #ifdef KC_GPS_PROFILE
-    if (b == 0 && tid == 0)
+    if (b == gridDim.x / 2 && tid == 0) {
+        printf("N %d warps %d: setup %lld mean+phases %lld factor %lld; warp 1 waited for col_done in T, all J: %lld\n", N, NW,
+               prof_c[1] - prof_c[0], prof_c[2] - prof_c[1], clock64() - prof_c[2], g_prof_twait[blockIdx.x & 1023]);
+        printf("warp 1 in T, all J: substitution %lld trailing %lld\n", g_prof_tsub[blockIdx.x & 1023], g_prof_tdmma[blockIdx.x & 1023]);
+    }
+    if (b == gridDim.x / 2 && tid == 0)
+        for (int J = 0; J < nb; J++)
+            printf("J%d abs: chol %lld .. %lld | warp 1: strips done %lld, T %lld .. %lld\n", J, prof_abs[J][0], prof_abs[J][1],
+                   prof_abs[J][2], prof_abs[J][3], prof_abs[J][4]);
+    if (b == gridDim.x / 2 && tid == 0)
         for (int J = 0; J < nb; J++)
             printf("J%d diag: wait_u %lld chol %lld | worker: gen_pre %lld U %lld fill %lld T %lld\n", J,
                    prof_t[0][J][0], prof_t[0][J][1], prof_t[1][J][0], prof_t[1][J][1], prof_t[1][J][2], prof_t[1][J][3]);

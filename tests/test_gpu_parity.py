@@ -48,7 +48,7 @@ def test_golden_logL_mu(gpu, name, mode):
         if g["C0"] is not None:
             # kc_gp_cov runs the product path's generator (phase table + table-driven exp, kc_gp_common.cuh):
             # the diagonal is the reference's bit for bit; off it, within 4e-15 eta1^2 of the reference's
-            # entries (whose own distance from an 80-bit evaluation is ~1e-15 eta1^2, variants/fastgen/proto.py)
+            # entries (whose own distance from an 80-bit evaluation is ~1e-15 eta1^2, tools/gp_generator_error_budget.py)
             # and within |x| ulp(x) of the exponent, relatively, far down the exponential tail
             C = eng.calculate_C(0)
             C0 = g["C0"]

@@ -6,7 +6,7 @@ from kima_b200 import LikelihoodEngine, ModelFlags
 from kima_b200.synthetic import make_data, make_params
 
 tag = os.path.basename(os.environ.get("KIMA_CUDA_LIB", "product"))
-for N, B in ((177, 8192), (100, 8192), (208, 4096), (64, 8192)):
+for N, B in ((177, 8192), (100, 8192), (208, 4096), (64, 8192), (96, 8192), (128, 8192), (150, 8192)):
     flags = ModelFlags(GP=True, npmax=5)
     d = make_data(N)
     P, nps = make_params(flags, d, B, "max")
