@@ -190,6 +190,23 @@ int kc_stream(kc_ctx* ctx, void** stream);
  *              1 = the reference's operation chain (acos + cos(f+w)). */
 int kc_set_option(kc_ctx* ctx, const char* key, int value);
 
+/* Factor cache of the shared-memory-resident GP path (GP=true, standard kernel, N small enough for it, no
+ * MA term).  The covariance matrix of RVmodel::calculate_C (src/RVmodel.cpp:170-216) depends on eta1..eta4
+ * and the jitters only, and most of RVmodel::perturb's proposals (src/RVmodel.cpp:448-544) leave them alone;
+ * the reference factors C anyway on every log_likelihood() call (src/RVmodel.cpp:841-873).  With a cache of
+ * n_slots slots, a lane that names a slot (kc_set_slots; the device-side sampler names the particle it moves)
+ * finds the factor of its covariance matrix in one of the slot's two entries whenever that matrix was one of
+ * the last two factored there -- the particle's state or its latest proposal -- and then only recomputes the
+ * residuals and the solve.  Results do not depend on the cache: a hit returns the bits a miss would.
+ * n_slots = 0 frees the cache.  Costs 2 x n_slots x ~N^2/2 doubles of device memory (KC_ERR_ARG when that
+ * does not fit); succeeds and stays inactive on contexts the cache does not apply to (kc_gp_cache_slots
+ * then reports 0).  kc_upload_data / kc_configure drop the cache.  No counterpart in the reference. */
+int kc_gp_cache_enable(kc_ctx* ctx, int n_slots);
+int kc_gp_cache_slots(kc_ctx* ctx, int* n_slots);
+/* The slots of lanes 0 .. B-1 of the NEXT kc_eval / kc_eval_async / kc_eval_device call of exactly B lanes
+ * (consumed by it): slots[i] < 0 = lane i is evaluated without the cache; no slot twice in one batch. */
+int kc_set_slots(kc_ctx* ctx, int B, const int32_t* slots);
+
 /* ---- instrumentation ---------------------------------------------------- */
 /* Device time (CUDA events on the context stream) of the kernels of the last
  * evaluation call, and the number of kernel launches since kc_create. */

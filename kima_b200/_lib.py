@@ -49,6 +49,9 @@ SIGNATURES = {
     "kc_sync": (ctypes.c_int, [_vp]),
     "kc_stream": (ctypes.c_int, [_vp, ctypes.POINTER(_vp)]),
     "kc_set_option": (ctypes.c_int, [_vp, ctypes.c_char_p, ctypes.c_int]),
+    "kc_gp_cache_enable": (ctypes.c_int, [_vp, ctypes.c_int]),
+    "kc_gp_cache_slots": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_int)]),
+    "kc_set_slots": (ctypes.c_int, [_vp, ctypes.c_int, _ip]),
     "kc_last_kernel_ms": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_float),
                                          ctypes.POINTER(ctypes.c_float)]),
     "kc_flush_l2": (ctypes.c_int, [_vp]),

@@ -41,6 +41,7 @@ namespace {
 void free_model(kc_ctx* c)
 {
     kc::sampler_free(c);
+    kc::gp_cache_free(c);
     if (c->h_params) cudaFreeHost(c->h_params);
     if (c->h_np) cudaFreeHost(c->h_np);
     if (c->h_logL) cudaFreeHost(c->h_logL);
@@ -59,6 +60,7 @@ void free_model(kc_ctx* c)
 }
 void free_data(kc_ctx* c)
 {
+    kc::gp_cache_free(c);  // the cached factors are those of the old epochs
     cudaFree(c->d_t); cudaFree(c->d_y); cudaFree(c->d_sig2); cudaFree(c->d_actind);
     cudaFree(c->d_obsi);
     c->d_t = c->d_y = c->d_sig2 = c->d_actind = nullptr;
@@ -82,7 +84,22 @@ kc::KParams make_params(kc_ctx* c, int B, double* d_logL, const double* d_params
 }  // namespace
 
 namespace kc {
-int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np, bool timed)
+void gp_cache_free(kc_ctx* c)
+{
+    cudaFree(c->gpc.img);
+    cudaFree(c->gpc.meta);
+    cudaFree(c->d_slots);
+    if (c->h_slots) cudaFreeHost(c->h_slots);
+    if (c->slots_ev) cudaEventDestroy(c->slots_ev);
+    c->slots_ev = nullptr;
+    c->gpc = GpsCache{};
+    c->gpc_nslots = 0;
+    c->d_slots = c->h_slots = nullptr;
+    c->slots_B = 0;
+}
+
+int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np, bool timed,
+                const int32_t* d_slots)
 {
     kc::KParams p = make_params(c, B, d_logL, d_params, d_np);
     int n = 0;
@@ -91,7 +108,12 @@ int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const 
     if (c->F.GP && c->F.kernel == 1)
         e = kc::launch_gp_celerite(p, c->d_resid, c->ld, c->kepler_mode, c->stream, &n);
     else if (c->F.GP && c->gp_small_opt && kc::gps_smem_bytes(c->N))
-        e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n);
+    {
+        kc::GpsCache gc = c->gpc;
+        gc.slots = d_slots;
+        gc.stamp = ++c->gpc.stamp;
+        e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n, gc.img && d_slots ? &gc : nullptr);
+    }
     else if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
     if (e != cudaSuccess) return fail_cuda(e, "kernel launch");
@@ -322,6 +344,14 @@ int kc_eval_async(kc_ctx* c, int B, double* logL_host)
     if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is already in flight");
     CU(cudaSetDevice(c->device));
     if (B == 0) return KC_OK;
+    // slots named by kc_set_slots for exactly this batch: consumed here
+    const int32_t* slots = nullptr;
+    if (c->slots_B == B && c->gpc.img) {
+        CU(cudaMemcpyAsync(c->d_slots, c->h_slots, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaEventRecord(c->slots_ev, c->stream));
+        slots = c->d_slots;
+    }
+    c->slots_B = 0;
     const int chunk = c->eval_chunk_opt;
     if (chunk > 0 && B >= 2 * chunk) {
         // large batches: the columns travel in chunks on a copy stream while the kernels of the
@@ -343,7 +373,7 @@ int kc_eval_async(kc_ctx* c, int B, double* logL_host)
                                c->copy_stream));
             CU(cudaEventRecord(c->copy_ev, c->copy_stream));
             CU(cudaStreamWaitEvent(c->stream, c->copy_ev, 0));
-            rc = kc::run_kernels(c, nb, c->d_logL + c0, c->d_params + c0, c->d_np + c0, false);
+            rc = kc::run_kernels(c, nb, c->d_logL + c0, c->d_params + c0, c->d_np + c0, false, slots ? slots + c0 : nullptr);
             if (rc) return rc;
         }
         CU(cudaEventRecord(c->ev1, c->stream));
@@ -353,7 +383,7 @@ int kc_eval_async(kc_ctx* c, int B, double* logL_host)
         CU(cudaMemcpy2DAsync(c->d_params, sizeof(double) * c->ld, c->h_params, sizeof(double) * c->ld,
                              sizeof(double) * B, c->L.n_rows, cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(c->d_np, c->h_np, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
-        rc = run_kernels(c, B, c->d_logL);
+        rc = kc::run_kernels(c, B, c->d_logL, nullptr, nullptr, true, slots);
         if (rc) return rc;
     }
     CU(cudaMemcpyAsync(c->h_logL, c->d_logL, sizeof(double) * B, cudaMemcpyDeviceToHost, c->stream));
@@ -388,7 +418,65 @@ int kc_eval_device(kc_ctx* c, int B, double* d_logL)
     if (rc) return rc;
     CU(cudaSetDevice(c->device));
     if (B == 0) return KC_OK;
-    return run_kernels(c, B, d_logL ? d_logL : c->d_logL);
+    const int32_t* slots = nullptr;
+    if (c->slots_B == B && c->gpc.img) {
+        CU(cudaMemcpyAsync(c->d_slots, c->h_slots, sizeof(int32_t) * B, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaEventRecord(c->slots_ev, c->stream));
+        slots = c->d_slots;
+    }
+    c->slots_B = 0;
+    return kc::run_kernels(c, B, d_logL ? d_logL : c->d_logL, nullptr, nullptr, true, slots);
+}
+
+int kc_gp_cache_enable(kc_ctx* c, int n_slots)
+{
+    if (!c || !c->configured) return fail(KC_ERR_ARG, "context not configured");
+    if (n_slots < 0) return fail(KC_ERR_ARG, "n_slots is negative");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    kc::gp_cache_free(c);
+    // only the shared-memory-resident dense path keeps factors (and not with the MA(1) term, whose residual
+    // recurrence borrows the factor storage): elsewhere the call succeeds and the cache stays inactive
+    if (n_slots == 0 || !c->F.GP || c->F.kernel != 0 || c->F.MA || !c->gp_small_opt || !kc::gps_smem_bytes(c->N))
+        return KC_OK;
+    const size_t img = kc::gps_cache_img_doubles(c->N);
+    const size_t bytes = (size_t)n_slots * 2 * img * sizeof(double);
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    if (bytes > free_b / 10 * 9) return fail(KC_ERR_ARG, "factor cache: n_slots x 2 factors do not fit the free device memory");
+    cudaError_t e = cudaMalloc(&c->gpc.img, bytes);
+    if (e != cudaSuccess) { kc::gp_cache_free(c); return fail_cuda(e, "cudaMalloc (factor cache)"); }
+    e = cudaMalloc(&c->gpc.meta, sizeof(kc::GpsCacheMeta) * 2 * (size_t)n_slots);
+    if (e == cudaSuccess) e = cudaMemsetAsync(c->gpc.meta, 0, sizeof(kc::GpsCacheMeta) * 2 * (size_t)n_slots, c->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_slots, sizeof(int32_t) * (size_t)c->max_batch);
+    if (e == cudaSuccess) e = cudaMallocHost(&c->h_slots, sizeof(int32_t) * (size_t)c->max_batch);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->slots_ev, cudaEventDisableTiming);
+    if (e != cudaSuccess) { kc::gp_cache_free(c); return fail_cuda(e, "factor cache allocation"); }
+    c->gpc.img_doubles = img;
+    c->gpc_nslots = n_slots;
+    return KC_OK;
+}
+
+int kc_gp_cache_slots(kc_ctx* c, int* n_slots)
+{
+    if (!c || !n_slots) return fail(KC_ERR_ARG, "null argument");
+    *n_slots = c->gpc_nslots;
+    return KC_OK;
+}
+
+int kc_set_slots(kc_ctx* c, int B, const int32_t* slots)
+{
+    int rc = check_ready(c, B);
+    if (rc) return rc;
+    if (!slots) return fail(KC_ERR_ARG, "slots is null");
+    if (!c->gpc.img) return KC_OK;  // inactive cache: nothing to name
+    if (c->pending_out) return fail(KC_ERR_ARG, "an asynchronous evaluation is in flight");
+    for (int i = 0; i < B; i++)
+        if (slots[i] >= c->gpc_nslots) return fail(KC_ERR_ARG, "slot index outside the cache");
+    CU(cudaEventSynchronize(c->slots_ev));  // the previous upload has left the staging buffer
+    std::memcpy(c->h_slots, slots, sizeof(int32_t) * (size_t)B);
+    c->slots_B = B;
+    return KC_OK;
 }
 
 int kc_sync(kc_ctx* c)

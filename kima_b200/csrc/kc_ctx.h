@@ -28,6 +28,12 @@ struct kc_ctx {
     kc::GpWorkspace gp{};
     int gp_streams_opt = 2;
     double* d_resid = nullptr;   // kernel = celerite: residuals, [N][ld]
+    // factor cache of the shared-memory-resident GP path (kc_gp_cache_enable)
+    kc::GpsCache gpc{};
+    int gpc_nslots = 0;
+    int32_t *d_slots = nullptr, *h_slots = nullptr;  // slots of the lanes of the next evaluation
+    int slots_B = 0;                                  // lanes kc_set_slots named (0: none pending)
+    cudaEvent_t slots_ev = nullptr;                   // the last upload of h_slots
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
@@ -62,7 +68,8 @@ namespace kc {
 int fail(int code, const std::string& msg);
 int fail_cuda(cudaError_t e, const char* what);
 int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const int32_t* d_np,
-                bool timed = true);
+                bool timed = true, const int32_t* d_slots = nullptr);
+void gp_cache_free(kc_ctx* c);
 int check_ready(kc_ctx* c, int B);
 void sampler_free(kc_ctx* c);  // kc_sampler_api.cu
 }  // namespace kc

@@ -46,7 +46,7 @@ struct Hdr {
     PlanetInv inv[MAX_PLANETS];
     ParticleScalars sc;
     GpConsts g;
-    double dinv[2][T];         // 1 / diag(L_JJ), double-buffered by block parity (T_J may still read while block J+1 is factored)
+    alignas(16) double dinv[MAXBLK][T];    // 1 / diag(L_JJ) of every block (T_J may still read while block J+1 is factored; the factor cache keeps them)
     double etab[64];           // 2^(j/64) for exp_tab
     double quad;
     int base[MAXBLK];
@@ -55,6 +55,10 @@ struct Hdr {
     int gen_next, u_done, d_done, col_done;
     int gen0;                  // generation items of block column 0; the residual items sit behind them in the queue
     int setup_done, mean_cnt;  // planet invariants ready / finished residual items
+    int hit, victim, slot;     // factor cache: entry that holds this particle's factor (-1: none), entry to fill, slot
+    double key[4 + KC_MAX_INST];
+    double logdet;
+    unsigned long long cache_bar;  // mbarrier of the factor image's bulk copies
     int t0_done;               // J + 1 once T_J has finished the tile below the diagonal block (the rows of block J + 1)
     int pre_cnt[MAXBLK];       // strips of the diagonal tile of block column J updated one block column behind
     int tile_cnt[MAXBLK + 1];  // block column 0: finished generation items per 32-row tile
@@ -77,6 +81,16 @@ size_t gps_smem_bytes(int N)
     for (int J = 0; J < nb; J++) d += (size_t)T * ld_for(N + 1 - T * J);
     size_t bytes = hdr_bytes() + d * sizeof(double);
     return bytes <= SMEM_LIMIT ? bytes : 0;
+}
+
+// Doubles of one factor-cache entry: the block columns as they sit in shared memory, then 1/diag of every block.
+size_t gps_cache_img_doubles(int N)
+{
+    using namespace gps;
+    const int nb = (N + T - 1) / T;
+    size_t d = (size_t)nb * T;
+    for (int J = 0; J < nb; J++) d += (size_t)T * ld_for(N + 1 - T * J);
+    return d;
 }
 
 namespace {
@@ -186,7 +200,7 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
 // One residual item: y - mu (:845-847) at 32 epochs, an epoch per lane, into row N of the block columns
 // that own them.  Needs the planet invariants (setup_done); same summation order as model_mu2.
 template <int MODE>
-__device__ __noinline__ void mean_item(const KParams& p, Hdr& H, double* M, int N, int m, int lane)
+__device__ __noinline__ void mean_item(const KParams& p, Hdr& H, double* M, int N, int m, int lane, double* stage = nullptr)
 {
     while (ld_uniform(&H.setup_done, lane) == 0) __nanosleep(KC_GPS_SLEEP_F);
     const int i = T * m + lane;
@@ -197,7 +211,10 @@ __device__ __noinline__ void mean_item(const KParams& p, Hdr& H, double* M, int 
         const int npl = H.sc.npl;
         for (int j = 0; j < npl; j++) mu += kepler_term<MODE>(H.inv[j], ti);
         const int J = i / T;
-        M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = __ldg(p.y + i) - mu;
+        const double r = __ldg(p.y + i) - mu;
+        // factor-cache hits stage the residuals: row N belongs to the factor image still on its way in
+        if (stage) stage[i] = r;
+        else M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = r;
     }
     __syncwarp();
     if (lane == 0) {
@@ -226,6 +243,9 @@ __device__ __forceinline__ int claim(Hdr& H, int lane)
 // all earlier block columns, one read-modify-write of the strip at the end.  8 rows (one
 // fragment row) per item: at these sizes the number of items per step, not the operand
 // reuse, decides how many of the four tensor pipes are busy.
+// ZONLY (factor-cache hits, gps_solve_cached): the same instructions, but only row N -- the residual row -- is
+// written back; the other rows of the strip hold finished entries of L.
+template <bool ZONLY = false>
 __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int J, int strip, int lane, int k_begin,
                                              int k_end)
 {
@@ -251,7 +271,7 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
     double* S = M + H.base[J];
     const int ldj = H.ld[J];
     const int row = r0 + (lane >> 2);
-    if (row <= N) {
+    if (ZONLY ? row == N : row <= N) {
 #pragma unroll
         for (int n = 0; n < 4; n++)
 #pragma unroll
@@ -267,23 +287,26 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
 // all in flight before the substitution chain starts (8 x (multiply, fused multiply-add) = ~140 cycles, where
 // the bounds-checked version above spends ~1200 per panel waiting for its loads one column at a time), and the
 // trailing update's blocks are unrolled.  ROLLED keeps the panel loop rolled (a quarter of the code).
-template <bool ROLLED>
+template <bool ROLLED, bool ZONLY = false>
 __device__ __forceinline__ void trsm_tile_full(Hdr& H, double* M, int N, int J, int tile, int lane)
 {
     const int j0 = T * J;
     const int row0 = T + T * tile;  // first row of the tile, relative to j0
     const int row = j0 + row0 + lane;
-    const bool ok = row <= N;
+    const bool ok = ZONLY ? row == N : row <= N;  // rows that are written back (all of them are computed)
     const int ldj = H.ld[J];
     double* S = M + H.base[J];
-    double* mine = S + (ok ? row0 + lane : T);
+    double* mine = S + (row <= N ? row0 + lane : T);
     double* tileS = S + row0;
     const int fr = lane >> 2, fk = lane & 3;
-    const double* dinv = H.dinv[J & 1];
+    const double* dinv = H.dinv[J];
     // rows past N of the last tile: computed on a clamped address, never stored
     bool rok[4];
 #pragma unroll
-    for (int Ir = 0; Ir < 4; Ir++) rok[Ir] = j0 + row0 + 8 * Ir + fr <= N;
+    for (int Ir = 0; Ir < 4; Ir++) {
+        const int r = j0 + row0 + 8 * Ir + fr;
+        rok[Ir] = ZONLY ? r == N : r <= N;
+    }
     double q = 0.0;
     auto panel = [&](const int p) {
         const int c0 = CHOL_PANEL * p;
@@ -345,7 +368,7 @@ __device__ __forceinline__ void trsm_tile_full(Hdr& H, double* M, int N, int J, 
 #pragma unroll
         for (int p = 0; p < T / CHOL_PANEL; p++) panel(p);
     }
-    if (ok && row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
+    if (row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
 }
 
 // T_J for 32 rows below the diagonal block: X L_JJ^T = S in place, a row per lane, following the
@@ -354,15 +377,16 @@ __device__ __forceinline__ void trsm_tile_full(Hdr& H, double* M, int N, int J, 
 // of the panel are then updated on the tensor cores, X[:, rest] -= X[:, panel] L_JJ[rest, panel]^T,
 // fragments read-modify-written in shared memory: 4x fewer issue slots than a 31-wide register
 // window per column.
+template <bool ZONLY = false>
 __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int nbc, int tile, int lane)
 {
     const int j0 = T * J;
     const int row0 = nbc + T * tile;  // first row of the tile, relative to j0
     const int row = j0 + row0 + lane;
-    const bool ok = row <= N;
+    const bool ok = ZONLY ? row == N : row <= N;  // rows that are written back
     const int ldj = H.ld[J];
     double* S = M + H.base[J];
-    double* mine = S + (ok ? row0 + lane : nbc);
+    double* mine = S + (row <= N ? row0 + lane : nbc);
     double* tileS = S + row0;
     const int fr = lane >> 2, fk = lane & 3;
     double q = 0.0;
@@ -384,7 +408,7 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
         for (int k = 0; k < CHOL_PANEL; k++) {
             const int c = c0 + k;
             if (c < nbc) {  // warp-uniform
-                const double x0 = x[k] * H.dinv[J & 1][c];
+                const double x0 = x[k] * H.dinv[J][c];
                 x[k] = x0;
                 q = kfma(x0, x0, q);
                 const double* lc = S + (size_t)c * ldj + c0;  // lc[k2] = L_JJ(c0 + k2, c)
@@ -427,7 +451,7 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
                     const int col = cb + 2 * fk;
                     const int r = j0 + row0 + 8 * Ir + fr;
                     double* qd = tileS + (size_t)col * ldj + 8 * Ir + fr;
-                    if (r <= N) {
+                    if (ZONLY ? r == N : r <= N) {
                         if (col < nbc) qd[0] -= u0;
                         if (col + 1 < nbc) qd[ldj] -= u1;
                     }
@@ -439,13 +463,98 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
         if (threadIdx.x == 32) g_prof_tdmma[blockIdx.x & 1023] += clock64() - tw2;
 #endif
     }
-    if (ok && row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
+    if (row == N) H.quad += q;  // |z|^2 of this block column; one writer per step
+}
+
+// ---- factor cache ---------------------------------------------------------------------------------
+// Most proposals of a nested-sampling run leave the covariance matrix alone (they move planets, offsets,
+// the trend: 62 % of RVmodel::perturb's draws in GP mode, src/RVmodel.cpp:448-544), and C -- hence L --
+// depends on eta1..eta4 and the jitters only.  With a cache attached (kc_gp_cache_enable) every lane names a
+// slot, the particle it carries; the slot keeps the factors of the last two covariance matrices seen there
+// (the particle's state and its last rejected or not-yet-superseded proposal), keyed by those parameters.
+// A hit skips the generation and the factorisation: the factor image comes back from HBM (161 KB at N = 177),
+// the residuals are recomputed and one warp takes the residual row through exactly the instructions the
+// full path runs on it (update_strip / trsm_tile with ZONLY: all rows computed, only row N written), so the
+// log-likelihood of a hit is the log-likelihood of a miss, bit for bit -- chains do not depend on the cache.
+template <int MODE, int NW>
+__device__ __noinline__ void gps_solve_cached(const KParams& p, const GpsCache& gc, Hdr& H, double* M, int N, int b)
+{
+    constexpr int THREADS = NW * 32;
+    constexpr bool PRE = NW >= 16;
+    constexpr bool ROLLED = KC_GPS_ROLLED(NW);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nb = (N + T - 1) / T;
+    GpsCacheMeta& me = gc.meta[(size_t)H.slot * 2 + H.hit];
+    const double* src = gc.img + ((size_t)H.slot * 2 + H.hit) * gc.img_doubles;
+    const size_t d_tiles = gc.img_doubles - (size_t)nb * T;
+    // the image (block columns + 1/diag, contiguous) by bulk copies, 32 KB at a time, behind one mbarrier;
+    // the planets and the residuals meanwhile (staged in the noise-variance array, which a hit does not use)
+    double* stage = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(&H) + hdr_bytes()) + npad(N);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(&H.cache_bar);
+    if (tid == THREADS - 1) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+        const size_t bytes = d_tiles * sizeof(double);
+        mbar_expect_tx(bar, (uint32_t)(bytes + (size_t)nb * T * sizeof(double)));
+        for (size_t o = 0; o < bytes; o += 32768)
+            bulk_load(reinterpret_cast<unsigned char*>(M) + o, reinterpret_cast<const unsigned char*>(src) + o,
+                      (uint32_t)(bytes - o < 32768 ? bytes - o : 32768), bar);
+        bulk_load(&H.dinv[0][0], src + d_tiles, (uint32_t)((size_t)nb * T * sizeof(double)), bar);
+    }
+    if (warp == 0) {
+        particle_setup(p, b, H.inv, &H.sc, lane);
+        if (lane == 0) H.setup_done = 1;
+    }
+    __syncthreads();
+    // residual = y - mu (:845-847): the very routine the full path queues (same code, same bits)
+    {
+        for (int m = warp; m < (N + T - 1) / T; m += NW) mean_item<MODE>(p, H, M, N, m, lane, stage);
+        __syncthreads();
+        mbar_wait(bar, 0);
+        for (int i = tid; i < N; i += THREADS) {
+            const int J = i / T;
+            M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = stage[i];
+        }
+        if (tid == 0) H.col_done = 0x7fffffff;  // every panel of every block is there
+    }
+    __syncthreads();
+    if (warp == 0) {
+        for (int J = 0; J < nb; J++) {
+            const int j0 = T * J;
+            const int nbc = min(T, N - j0);
+            if (J >= 1) {
+                const int nstrips = (N + 1 - j0 + 7) / 8;
+                const int ndiag = min(4, nstrips);
+                const int sN = (N - j0) / 8;  // the strip that holds row N
+                if (sN < ndiag) {
+                    // a short last block: the residual row rides with the look-ahead strips of the full path
+                    if (PRE && J >= 2) update_strip<true>(H, M, N, J, sN, lane, 0, J - 1);
+                    update_strip<true>(H, M, N, J, sN, lane, PRE ? J - 1 : 0, J);
+                } else {
+                    update_strip<true>(H, M, N, J, sN, lane, 0, J);
+                }
+                __syncwarp();
+            }
+            const int first = j0 + nbc;
+            const int ntiles = (N + 1 - first + T - 1) / T;
+            if (nbc == T) trsm_tile_full<ROLLED, true>(H, M, N, J, ntiles - 1, lane);
+            else trsm_tile<true>(H, M, N, J, nbc, ntiles - 1, lane);
+            __syncwarp();
+        }
+        if (lane == 0) {
+            const double pinf = __longlong_as_double(0x7ff0000000000000ll);
+            double logL = -0.5 * N * 1.8378770664093453 - me.logdet - 0.5 * H.quad;
+            if (isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
+            p.logL[b] = logL;
+            me.stamp = gc.stamp;
+        }
+    }
 }
 
 // NW warps per CTA (1 diag + NW-1 workers); 16 / NW CTAs share an SM when the factor is small
 // enough, so that the serial chains of several particles overlap.
 template <int MODE, int NW>
-__global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const KParams p)
+__global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const KParams p, const GpsCache gc)
 {
     constexpr int THREADS = NW * 32;
     constexpr int GW = gw_for(NW), GQ = T / GW;
@@ -519,6 +628,40 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             H.quad = 0.0;
             for (int I = 0; I <= MAXBLK; I++) H.tile_cnt[I] = 0;
             for (int I = 0; I < MAXBLK; I++) H.dcnt[I] = H.ccnt[I] = 0;
+            H.hit = H.victim = H.slot = -1;
+        }
+        if (gc.img && warp == NW - 1) {
+            // factor cache: is the factor of this covariance matrix in one of the slot's two entries?
+            constexpr int KEYLEN = 4 + KC_MAX_INST;
+            __syncwarp();
+            const int slot = gc.slots ? gc.slots[b] : -1;
+            if (slot >= 0) {
+                double mine = 0.0;
+                if (lane < 4) mine = ldp(p, L.row_eta + lane, b);
+                else if (lane < 4 + L.n_jit && lane < KEYLEN) mine = ldp(p, L.row_jit + lane - 4, b);
+                const GpsCacheMeta* m = gc.meta + (size_t)slot * 2;
+                bool eq0 = true, eq1 = true;
+                if (lane < KEYLEN) {
+                    H.key[lane] = mine;
+                    eq0 = __double_as_longlong(m[0].key[lane]) == __double_as_longlong(mine);
+                    eq1 = __double_as_longlong(m[1].key[lane]) == __double_as_longlong(mine);
+                }
+                const bool hit0 = __all_sync(0xffffffffu, eq0) && m[0].valid;
+                const bool hit1 = __all_sync(0xffffffffu, eq1) && m[1].valid;
+                if (lane == 0) {
+                    H.slot = slot;
+                    H.hit = hit0 ? 0 : hit1 ? 1 : -1;
+                    // the entry to fill on a miss: an empty one, else the one used longer ago
+                    H.victim = !m[0].valid ? 0 : !m[1].valid ? 1 : (m[0].stamp - m[1].stamp <= 0 ? 0 : 1);
+                }
+            }
+        }
+    }
+    if (gc.img) {
+        __syncthreads();
+        if (H.hit >= 0) {
+            gps_solve_cached<MODE, NW>(p, gc, H, M, N, b);
+            return;
         }
     }
     if (p.F.MA) {
@@ -580,10 +723,10 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             const int nv = min(T, N - j0);
             bool fine;
             if constexpr (ROLLED)
-                fine = chol32_panels_rolled<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv[J & 1], nullptr, 0,
+                fine = chol32_panels_rolled<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv[J], nullptr, 0,
                                                   &H.col_done, T * J);
             else
-                fine = chol32_panels<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv[J & 1], nullptr, 0,
+                fine = chol32_panels<true>(M + H.base[J], H.ld[J], lane, nv, logdet, H.dinv[J], nullptr, 0,
                                            &H.col_done, T * J);
             if (!fine) ok = false;
             __syncwarp();
@@ -739,32 +882,58 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
         if (!ok || isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
         p.logL[b] = logL;
     }
+    if (gc.img && H.slot >= 0) {
+        // factor cache, a miss: the factor goes to the slot's older entry (not a failed factorisation)
+        GpsCacheMeta& me = gc.meta[(size_t)H.slot * 2 + H.victim];
+        double* dst = gc.img + ((size_t)H.slot * 2 + H.victim) * gc.img_doubles;
+        const size_t d_tiles = gc.img_doubles - (size_t)nb * T;
+        fence_proxy_async();  // the factor was written with ordinary stores: every writer fences, then the barrier
+        __syncthreads();
+        if (tid == 0) {
+            const size_t bytes = d_tiles * sizeof(double);
+            for (size_t o = 0; o < bytes; o += 32768)
+                bulk_store(reinterpret_cast<unsigned char*>(dst) + o, reinterpret_cast<const unsigned char*>(M) + o,
+                           (uint32_t)(bytes - o < 32768 ? bytes - o : 32768));
+            bulk_store(dst + d_tiles, &H.dinv[0][0], (uint32_t)((size_t)nb * T * sizeof(double)));
+            bulk_store_commit_wait();
+        }
+        if (tid < 4 + KC_MAX_INST) me.key[tid] = H.key[tid];
+        if (tid == 0) {
+            me.logdet = logdet;
+            me.valid = ok ? 1 : 0;
+            me.stamp = gc.stamp;
+        }
+    }
 }
 
 }  // namespace
 
 template <int MODE, int NW>
-static cudaError_t launch_one(const KParams& p, size_t smem, cudaStream_t stream)
+static cudaError_t launch_one(const KParams& p, size_t smem, cudaStream_t stream, const GpsCache& gc)
 {
     cudaError_t e = cudaFuncSetAttribute(gps_kernel<MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    gps_kernel<MODE, NW><<<p.B, NW * 32, smem, stream>>>(p);
+    gps_kernel<MODE, NW><<<p.B, NW * 32, smem, stream>>>(p, gc);
     return cudaGetLastError();
 }
 
-cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches)
+cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches,
+                            const GpsCache* cache)
 {
     if (p.B <= 0) return cudaSuccess;
+    GpsCache gc{};
+    // with the MA(1) term the residual recurrence uses the factor storage as scratch: no cache then
+    if (cache && cache->img && cache->slots && !p.F.MA) gc = *cache;
     const size_t smem = gps_smem_bytes(p.N);
     if (!smem) return cudaErrorInvalidValue;
     // CTAs per SM by shared-memory footprint (228 KB per SM, 1 KB reserved per CTA)
     const size_t per_sm = 228 * 1024;
     const int fit = (int)(per_sm / (smem + 1024));
     cudaError_t e;
-    if (fit >= 4) e = kepler_mode == 0 ? launch_one<0, 4>(p, smem, stream) : launch_one<1, 4>(p, smem, stream);
-    else if (fit == 3) e = kepler_mode == 0 ? launch_one<0, 5>(p, smem, stream) : launch_one<1, 5>(p, smem, stream);
-    else if (fit == 2) e = kepler_mode == 0 ? launch_one<0, 8>(p, smem, stream) : launch_one<1, 8>(p, smem, stream);
-    else e = kepler_mode == 0 ? launch_one<0, 16>(p, smem, stream) : launch_one<1, 16>(p, smem, stream);
+    if (fit >= 4) e = kepler_mode == 0 ? launch_one<0, 4>(p, smem, stream, gc) : launch_one<1, 4>(p, smem, stream, gc);
+    else if (fit == 3) e = kepler_mode == 0 ? launch_one<0, 5>(p, smem, stream, gc) : launch_one<1, 5>(p, smem, stream, gc);
+    else if (fit == 2) e = kepler_mode == 0 ? launch_one<0, 8>(p, smem, stream, gc) : launch_one<1, 8>(p, smem, stream, gc);
+    else e = kepler_mode == 0 ? launch_one<0, 16>(p, smem, stream, gc) : launch_one<1, 16>(p, smem, stream, gc);
     *n_launches += 1;
     return e;
 }

@@ -80,7 +80,24 @@ cudaError_t launch_predict_model(const KParams& p, int kepler_mode, const double
                                  double* d_out, cudaStream_t s, int* n_launches);
 // small-N path (kc_gp_small.cu): shared-memory-resident, one CTA per particle
 size_t gps_smem_bytes(int N);  // 0 = N does not fit
-cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches);
+// Factor cache of the small path (kc_gp_small.cu, "factor cache"): two entries per slot -- a slot is whatever
+// the caller says carries one particle from evaluation to evaluation (the samplers: the particle index) -- each
+// the factor of the last covariance matrices seen in that slot, keyed by the parameters C depends on.
+struct GpsCacheMeta {
+    double key[4 + KC_MAX_INST];  // eta1..eta4 and the jitters, as given
+    double logdet;
+    int valid, stamp;             // stamp: launch counter of the last use (the older entry is replaced)
+};
+struct GpsCache {
+    double* img;                  // [n_slots][2][img_doubles]: the factor as it sits in shared memory + 1/diag; null = no cache
+    GpsCacheMeta* meta;           // [n_slots][2]
+    const int32_t* slots;         // [B]: slot of every lane of this launch (< 0: not cached)
+    size_t img_doubles;
+    int stamp;
+};
+size_t gps_cache_img_doubles(int N);
+cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches,
+                            const GpsCache* cache = nullptr);
 // kernel = celerite (kc_celerite.cu): resid is [N][ldr] doubles of scratch
 cudaError_t launch_gp_celerite(const KParams& p, double* resid, int ldr, int kepler_mode,
                                cudaStream_t stream, int* n_launches);

@@ -690,7 +690,9 @@ int kc_sampler_run(kc_ctx* c, int steps)
     kc::launch_propose(sp, B, false, grid, c->stream);
     c->launches += 1;
     for (int i = 0; i < steps; i++) {
-        rc = kc::run_kernels(c, sp.lanes, const_cast<double*>(sp.logl_q), sp.Q, sp.npq);
+        // factor cache (kc_gp_cache_enable with >= n_particles slots): the slot of a lane is the particle it moves
+        rc = kc::run_kernels(c, sp.lanes, const_cast<double*>(sp.logl_q), sp.Q, sp.npq, true,
+                             c->gpc_nslots >= sp.SL.n_particles ? sp.which : nullptr);
         if (rc) return rc;
         if (i + 1 < steps) kc::launch_propose(sp, B, true, grid, c->stream);
         else kc::smp_accept_kernel<<<grid, kc::LANE_THREADS, 0, c->stream>>>(sp);

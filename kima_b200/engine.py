@@ -119,6 +119,20 @@ class LikelihoodEngine:
     def set_option(self, key: str, value: int) -> None:
         _lib.check(self.lib.kc_set_option(self._ctx, key.encode(), int(value)))
 
+    # ---- factor cache of the shared-memory-resident GP path (kima_cuda.h: kc_gp_cache_enable) ----
+    def enable_gp_cache(self, n_slots: int) -> int:
+        """Keep the last two factors of every slot; returns the active slot count (0: the cache does not
+        apply to this context).  No counterpart in the reference, which factors C on every call."""
+        _lib.check(self.lib.kc_gp_cache_enable(self._ctx, int(n_slots)))
+        n = ctypes.c_int(0)
+        _lib.check(self.lib.kc_gp_cache_slots(self._ctx, ctypes.byref(n)))
+        return n.value
+
+    def set_slots(self, slots) -> None:
+        """Slots of the lanes of the next evaluation (consumed by it; < 0 = uncached lane)."""
+        slots = np.ascontiguousarray(slots, np.int32)
+        _lib.check(self.lib.kc_set_slots(self._ctx, slots.size, slots.ctypes.data_as(_ip)))
+
     def log_likelihood_async(self, B: int, out: np.ndarray) -> None:
         _lib.check(self.lib.kc_eval_async(self._ctx, B, _d(out)))
 
