@@ -65,6 +65,7 @@ class BatchedSampler : public Sampler<ModelType> {
     std::shared_ptr<kima_b200::LanePool> pool;
     std::vector<char> xbuf_send, xbuf_recv;  // exchange() buffers, kept between rounds
     // wall-clock split of run(), printed at the end when KIMA_PROFILE is set
+    bool cache_tried = false;  // the evaluator's factor cache is asked for once, at the first step
     double prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // perturb, stage, submit, wait, phase B, bookkeeping, exchange, level copies
     static double now()
     {
@@ -160,7 +161,11 @@ class BatchedSampler : public Sampler<ModelType> {
         for (unsigned int k = k0; k < k1; ++k) lane_steps[k].slot = lane_steps[k].scored ? nb++ : -1;
         pool->run((int)k0, (int)k1, [&](int a, int b) {
             for (int k = a; k < b; ++k)
-                if (lane_steps[k].scored) evaluator->stage(g, lane_steps[k].slot, lane_steps[k].proposal);
+                if (lane_steps[k].scored) {
+                    evaluator->stage(g, lane_steps[k].slot, lane_steps[k].proposal);
+                    // the particle behind the lane, numbered within the group (factor cache)
+                    evaluator->stage_slot(g, lane_steps[k].slot, (int)(lane_steps[k].which - k0 * P));
+                }
         });
         prof[1] += now() - t1;
         return nb;
@@ -329,6 +334,12 @@ class BatchedSampler : public Sampler<ModelType> {
         const unsigned int k0 = lane_lo(), k1 = lane_hi(), n = k1 - k0;
         const unsigned int split[3] = {k0, n < 2 ? k1 : k0 + (n + 1) / 2, k1};
         const int ngroups = n < 2 ? 1 : 2;
+        if (!cache_tried) {
+            // one factor-cache slot per particle of each group (inactive where it does not apply)
+            cache_tried = true;
+            for (int g = 0; g < ngroups; ++g)
+                evaluator->enable_factor_cache(g, (int)((split[g + 1] - split[g]) * this->options.num_particles));
+        }
         int nb[2] = {0, 0};
         for (unsigned int i = 0; i < this->options.thread_steps; ++i) {
             for (int g = 0; g < ngroups; ++g) {

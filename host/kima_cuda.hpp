@@ -67,6 +67,16 @@ public:
     void eval_async(int B, double* logL) { check(kc_eval_async(ctx_, B, logL)); }
     void wait() { check(kc_wait(ctx_)); }
     void set_option(const char* key, int value) { check(kc_set_option(ctx_, key, value)); }
+    // factor cache of the shared-memory-resident GP path (kima_cuda.h: kc_gp_cache_enable): returns the
+    // active slot count, 0 where the cache does not apply or does not fit
+    int gp_cache_enable(int n_slots)
+    {
+        if (kc_gp_cache_enable(ctx_, n_slots) != KC_OK) return 0;  // does not fit: evaluate without it
+        int n = 0;
+        check(kc_gp_cache_slots(ctx_, &n));
+        return n;
+    }
+    void set_slots(int B, const int32_t* slots) { check(kc_set_slots(ctx_, B, slots)); }
     long long launch_count() const { return (long long)kc_launch_count(ctx_); }
 
     // posterior-predictive curves of the first B staged parameter vectors

@@ -187,7 +187,12 @@ int kc_stream(kc_ctx* ctx, void** stream);
 
 /* ---- tuning (all have safe defaults) -------------------------------------
  * kepler_mode: 0 = algebraic true-anomaly form (default, no acos),
- *              1 = the reference's operation chain (acos + cos(f+w)). */
+ *              1 = the reference's operation chain (acos + cos(f+w)).
+ * gp_small:    1 = shared-memory-resident GP kernel whenever N fits (default), 0 = always the blocked path.
+ * gp_streams:  lane groups of the blocked GP path, 1..4 (default 2); gp_slots: lanes in flight (0 = by memory);
+ *              both take effect at the next kc_configure.
+ * eval_chunk:  kc_eval batches of >= 2 chunks overlap H2D with the kernels (default 32768 lanes, 0 = off).
+ * gp_cache:    1 = kc_sampler_create attaches a factor cache, one slot per particle (default), 0 = it does not. */
 int kc_set_option(kc_ctx* ctx, const char* key, int value);
 
 /* Factor cache of the shared-memory-resident GP path (GP=true, standard kernel, N small enough for it, no

@@ -120,7 +120,10 @@ typedef struct kc_sampler_layout {
     int32_t n_particles; /* lanes * num_particles = columns */
 } kc_sampler_layout;
 
-/* Needs kc_upload_data + kc_configure(max_batch >= lanes).  One sampler per context. */
+/* Needs kc_upload_data + kc_configure(max_batch >= lanes).  One sampler per context.
+ * Unless kc_set_option(ctx, "gp_cache", 0) was called before, the sampler attaches a factor cache with one
+ * slot per particle (kima_cuda.h: kc_gp_cache_enable) where that applies and fits the device memory; a lane's
+ * slot is the particle it moves.  Chains are the same bits with and without it. */
 int kc_sampler_create(kc_ctx* ctx, const kc_prior_table* priors, const kc_sampler_config* cfg);
 int kc_sampler_destroy(kc_ctx* ctx);
 int kc_sampler_get_layout(kc_ctx* ctx, kc_sampler_layout* out);

@@ -88,6 +88,9 @@ void gp_cache_free(kc_ctx* c)
 {
     cudaFree(c->gpc.img);
     cudaFree(c->gpc.meta);
+    cudaFree(c->gpc.cls);  // one allocation: cls, hit_list, miss_list, cnt
+    cudaFree(c->d_chk);
+    c->d_chk = nullptr;
     cudaFree(c->d_slots);
     if (c->h_slots) cudaFreeHost(c->h_slots);
     if (c->slots_ev) cudaEventDestroy(c->slots_ev);
@@ -113,6 +116,15 @@ int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const 
         gc.slots = d_slots;
         gc.stamp = ++c->gpc.stamp;
         e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n, gc.img && d_slots ? &gc : nullptr);
+        if (e == cudaSuccess && gc.img && d_slots && gc.debug >= 2) {
+            // developer check (KIMA_CUDA_GP_CACHE_DEBUG=2): the same lanes through the uncached kernel, compared on the device
+            if (!c->d_chk) cudaMalloc(&c->d_chk, sizeof(double) * c->max_batch);
+            double* d_chk = c->d_chk;
+            kc::KParams q = p;
+            q.logL = d_chk;
+            e = kc::launch_gp_small(q, c->kepler_mode, c->stream, &n, nullptr);
+            if (e == cudaSuccess) kc::launch_gp_cache_compare(p, d_chk, gc, c->stream);
+        }
     }
     else if (c->F.GP) e = kc::launch_gp_blocked(p, c->gp, c->kepler_mode, c->sm_count, c->stream, &n);
     else e = kc::launch_keplerian(p, c->kepler_mode, c->sm_count, c->stream, &n);
@@ -449,11 +461,18 @@ int kc_gp_cache_enable(kc_ctx* c, int n_slots)
     e = cudaMalloc(&c->gpc.meta, sizeof(kc::GpsCacheMeta) * 2 * (size_t)n_slots);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->gpc.meta, 0, sizeof(kc::GpsCacheMeta) * 2 * (size_t)n_slots, c->stream);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_slots, sizeof(int32_t) * (size_t)c->max_batch);
+    if (e == cudaSuccess) e = cudaMalloc(&c->gpc.cls, sizeof(int) * (3 * (size_t)c->max_batch + 2));
+    if (e == cudaSuccess) {
+        c->gpc.hit_list = c->gpc.cls + c->max_batch;
+        c->gpc.miss_list = c->gpc.hit_list + c->max_batch;
+        c->gpc.cnt = c->gpc.miss_list + c->max_batch;
+    }
     if (e == cudaSuccess) e = cudaMallocHost(&c->h_slots, sizeof(int32_t) * (size_t)c->max_batch);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->slots_ev, cudaEventDisableTiming);
     if (e != cudaSuccess) { kc::gp_cache_free(c); return fail_cuda(e, "factor cache allocation"); }
     c->gpc.img_doubles = img;
     c->gpc_nslots = n_slots;
+    if (const char* dbg = std::getenv("KIMA_CUDA_GP_CACHE_DEBUG")) c->gpc.debug = std::atoi(dbg);
     return KC_OK;
 }
 
@@ -510,6 +529,8 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
     } else if (k == "eval_chunk") {
         if (value < 0) return fail(KC_ERR_ARG, "eval_chunk must be >= 0 (0 = one copy, no overlap)");
         c->eval_chunk_opt = value;
+    } else if (k == "gp_cache") {
+        c->gp_cache_opt = value ? 1 : 0;  // kc_sampler_create attaches a factor cache (takes effect at the next call)
     } else if (k == "gp_slots") {
         if (value < 0) return fail(KC_ERR_ARG, "gp_slots must be >= 0");
         c->gp_slots_opt = value;  // takes effect at the next kc_configure

@@ -34,12 +34,14 @@ struct kc_ctx {
     int32_t *d_slots = nullptr, *h_slots = nullptr;  // slots of the lanes of the next evaluation
     int slots_B = 0;                                  // lanes kc_set_slots named (0: none pending)
     cudaEvent_t slots_ev = nullptr;                   // the last upload of h_slots
+    double* d_chk = nullptr;                          // developer check (KIMA_CUDA_GP_CACHE_DEBUG=2): uncached results
     // options / instrumentation
     int kepler_mode = 0;
     int gp_slots_opt = 0;
     int eval_chunk_opt = 32768;  // kc_eval: batches of >= 2 chunks overlap H2D with the kernels (0 = off)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t copy_ev = nullptr;
+    int gp_cache_opt = 1;   // kc_sampler_create: one factor-cache slot per particle where the cache applies
     int gp_small_opt = 1;   // 1 = shared-memory-resident kernel whenever N fits, 0 = always blocked
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;

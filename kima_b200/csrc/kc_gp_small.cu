@@ -24,6 +24,7 @@
 //     issue slots at this size) hides under the factorisation chain.
 #include "kc_model.cuh"
 #include "kc_gp_common.cuh"
+#include <cstdio>
 #ifdef KC_GPS_PROFILE
 #include <cstdio>
 #endif
@@ -55,10 +56,7 @@ struct Hdr {
     int gen_next, u_done, d_done, col_done;
     int gen0;                  // generation items of block column 0; the residual items sit behind them in the queue
     int setup_done, mean_cnt;  // planet invariants ready / finished residual items
-    int hit, victim, slot;     // factor cache: entry that holds this particle's factor (-1: none), entry to fill, slot
-    double key[4 + KC_MAX_INST];
-    double logdet;
-    unsigned long long cache_bar;  // mbarrier of the factor image's bulk copies
+    int victim, slot;          // factor cache: entry of the slot this particle's factor goes to (-1: not kept)
     int t0_done;               // J + 1 once T_J has finished the tile below the diagonal block (the rows of block J + 1)
     int pre_cnt[MAXBLK];       // strips of the diagonal tile of block column J updated one block column behind
     int tile_cnt[MAXBLK + 1];  // block column 0: finished generation items per 32-row tile
@@ -197,24 +195,33 @@ __device__ __noinline__ void gen_item(Hdr& H, const double* tS, const double* nS
     }
 }
 
+// y - mu at epoch i (:845-847): ONE compiled body for the full path's queue items and for the hit kernel
+// (inlined copies may contract mu += K * (...) differently, and a hit has to return the bits of a miss)
+template <int MODE>
+__device__ __noinline__ double residual_at(const KParams& p, const ParticleScalars* sc, const PlanetInv* inv, int i)
+{
+    const double ti = __ldg(p.t + i);
+    const int in = p.F.multi_instrument ? __ldg(p.obsi + i) - 1 : 0;
+    double mu = model_background(p, sc, i, ti, in);
+    const int npl = sc->npl;
+    for (int j = 0; j < npl; j++) mu += kepler_term<MODE>(inv[j], ti);
+    return __ldg(p.y + i) - mu;
+}
+__device__ __noinline__ void particle_setup_shared(const KParams& p, int b, PlanetInv* inv, ParticleScalars* sc, int lane)
+{
+    particle_setup(p, b, inv, sc, lane);
+}
+
 // One residual item: y - mu (:845-847) at 32 epochs, an epoch per lane, into row N of the block columns
 // that own them.  Needs the planet invariants (setup_done); same summation order as model_mu2.
 template <int MODE>
-__device__ __noinline__ void mean_item(const KParams& p, Hdr& H, double* M, int N, int m, int lane, double* stage = nullptr)
+__device__ __noinline__ void mean_item(const KParams& p, Hdr& H, double* M, int N, int m, int lane)
 {
     while (ld_uniform(&H.setup_done, lane) == 0) __nanosleep(KC_GPS_SLEEP_F);
     const int i = T * m + lane;
     if (i < N) {
-        const double ti = __ldg(p.t + i);
-        const int in = p.F.multi_instrument ? __ldg(p.obsi + i) - 1 : 0;
-        double mu = model_background(p, &H.sc, i, ti, in);
-        const int npl = H.sc.npl;
-        for (int j = 0; j < npl; j++) mu += kepler_term<MODE>(H.inv[j], ti);
         const int J = i / T;
-        const double r = __ldg(p.y + i) - mu;
-        // factor-cache hits stage the residuals: row N belongs to the factor image still on its way in
-        if (stage) stage[i] = r;
-        else M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = r;
+        M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = residual_at<MODE>(p, &H.sc, H.inv, i);
     }
     __syncwarp();
     if (lane == 0) {
@@ -243,9 +250,6 @@ __device__ __forceinline__ int claim(Hdr& H, int lane)
 // all earlier block columns, one read-modify-write of the strip at the end.  8 rows (one
 // fragment row) per item: at these sizes the number of items per step, not the operand
 // reuse, decides how many of the four tensor pipes are busy.
-// ZONLY (factor-cache hits, gps_solve_cached): the same instructions, but only row N -- the residual row -- is
-// written back; the other rows of the strip hold finished entries of L.
-template <bool ZONLY = false>
 __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int J, int strip, int lane, int k_begin,
                                              int k_end)
 {
@@ -271,7 +275,7 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
     double* S = M + H.base[J];
     const int ldj = H.ld[J];
     const int row = r0 + (lane >> 2);
-    if (ZONLY ? row == N : row <= N) {
+    if (row <= N) {
 #pragma unroll
         for (int n = 0; n < 4; n++)
 #pragma unroll
@@ -287,26 +291,23 @@ __device__ __forceinline__ void update_strip(const Hdr& H, double* M, int N, int
 // all in flight before the substitution chain starts (8 x (multiply, fused multiply-add) = ~140 cycles, where
 // the bounds-checked version above spends ~1200 per panel waiting for its loads one column at a time), and the
 // trailing update's blocks are unrolled.  ROLLED keeps the panel loop rolled (a quarter of the code).
-template <bool ROLLED, bool ZONLY = false>
+template <bool ROLLED>
 __device__ __forceinline__ void trsm_tile_full(Hdr& H, double* M, int N, int J, int tile, int lane)
 {
     const int j0 = T * J;
     const int row0 = T + T * tile;  // first row of the tile, relative to j0
     const int row = j0 + row0 + lane;
-    const bool ok = ZONLY ? row == N : row <= N;  // rows that are written back (all of them are computed)
+    const bool ok = row <= N;
     const int ldj = H.ld[J];
     double* S = M + H.base[J];
-    double* mine = S + (row <= N ? row0 + lane : T);
+    double* mine = S + (ok ? row0 + lane : T);
     double* tileS = S + row0;
     const int fr = lane >> 2, fk = lane & 3;
     const double* dinv = H.dinv[J];
     // rows past N of the last tile: computed on a clamped address, never stored
     bool rok[4];
 #pragma unroll
-    for (int Ir = 0; Ir < 4; Ir++) {
-        const int r = j0 + row0 + 8 * Ir + fr;
-        rok[Ir] = ZONLY ? r == N : r <= N;
-    }
+    for (int Ir = 0; Ir < 4; Ir++) rok[Ir] = j0 + row0 + 8 * Ir + fr <= N;
     double q = 0.0;
     auto panel = [&](const int p) {
         const int c0 = CHOL_PANEL * p;
@@ -377,16 +378,15 @@ __device__ __forceinline__ void trsm_tile_full(Hdr& H, double* M, int N, int J, 
 // of the panel are then updated on the tensor cores, X[:, rest] -= X[:, panel] L_JJ[rest, panel]^T,
 // fragments read-modify-written in shared memory: 4x fewer issue slots than a 31-wide register
 // window per column.
-template <bool ZONLY = false>
 __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int nbc, int tile, int lane)
 {
     const int j0 = T * J;
     const int row0 = nbc + T * tile;  // first row of the tile, relative to j0
     const int row = j0 + row0 + lane;
-    const bool ok = ZONLY ? row == N : row <= N;  // rows that are written back
+    const bool ok = row <= N;
     const int ldj = H.ld[J];
     double* S = M + H.base[J];
-    double* mine = S + (row <= N ? row0 + lane : nbc);
+    double* mine = S + (ok ? row0 + lane : nbc);
     double* tileS = S + row0;
     const int fr = lane >> 2, fk = lane & 3;
     double q = 0.0;
@@ -451,7 +451,7 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
                     const int col = cb + 2 * fk;
                     const int r = j0 + row0 + 8 * Ir + fr;
                     double* qd = tileS + (size_t)col * ldj + 8 * Ir + fr;
-                    if (ZONLY ? r == N : r <= N) {
+                    if (r <= N) {
                         if (col < nbc) qd[0] -= u0;
                         if (col + 1 < nbc) qd[ldj] -= u1;
                     }
@@ -472,88 +472,271 @@ __device__ __forceinline__ void trsm_tile(Hdr& H, double* M, int N, int J, int n
 // depends on eta1..eta4 and the jitters only.  With a cache attached (kc_gp_cache_enable) every lane names a
 // slot, the particle it carries; the slot keeps the factors of the last two covariance matrices seen there
 // (the particle's state and its last rejected or not-yet-superseded proposal), keyed by those parameters.
-// A hit skips the generation and the factorisation: the factor image comes back from HBM (161 KB at N = 177),
-// the residuals are recomputed and one warp takes the residual row through exactly the instructions the
-// full path runs on it (update_strip / trsm_tile with ZONLY: all rows computed, only row N written), so the
-// log-likelihood of a hit is the log-likelihood of a miss, bit for bit -- chains do not depend on the cache.
-template <int MODE, int NW>
-__device__ __noinline__ void gps_solve_cached(const KParams& p, const GpsCache& gc, Hdr& H, double* M, int N, int b)
+//   gps_classify_kernel  one thread per lane: key compare, hit and miss lists, the entry a miss will fill
+//   gps_hit_kernel       one WARP per hit: the factor stays in HBM / L2 (161 KB at N = 177, read once);
+//                        the warp recomputes the residuals and takes them through exactly the arithmetic
+//                        the full path applies to the residual row (same DMMA sequences with the same
+//                        operands, same FMA chains), so a hit returns the log-likelihood of a miss bit for
+//                        bit and chains do not depend on the cache.  32 hits in flight per SM.
+//   gps_kernel           the misses, as without a cache; the factor image then goes to the slot by bulk copy.
+__device__ __forceinline__ double cache_key(const KParams& p, int b, int i)
 {
-    constexpr int THREADS = NW * 32;
-    constexpr bool PRE = NW >= 16;
-    constexpr bool ROLLED = KC_GPS_ROLLED(NW);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nb = (N + T - 1) / T;
-    GpsCacheMeta& me = gc.meta[(size_t)H.slot * 2 + H.hit];
-    const double* src = gc.img + ((size_t)H.slot * 2 + H.hit) * gc.img_doubles;
-    const size_t d_tiles = gc.img_doubles - (size_t)nb * T;
-    // the image (block columns + 1/diag, contiguous) by bulk copies, 32 KB at a time, behind one mbarrier;
-    // the planets and the residuals meanwhile (staged in the noise-variance array, which a hit does not use)
-    double* stage = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(&H) + hdr_bytes()) + npad(N);
-    uint64_t* bar = reinterpret_cast<uint64_t*>(&H.cache_bar);
-    if (tid == THREADS - 1) {
-        mbar_init(bar, 1);
-        mbar_fence_init();
-        const size_t bytes = d_tiles * sizeof(double);
-        mbar_expect_tx(bar, (uint32_t)(bytes + (size_t)nb * T * sizeof(double)));
-        for (size_t o = 0; o < bytes; o += 32768)
-            bulk_load(reinterpret_cast<unsigned char*>(M) + o, reinterpret_cast<const unsigned char*>(src) + o,
-                      (uint32_t)(bytes - o < 32768 ? bytes - o : 32768), bar);
-        bulk_load(&H.dinv[0][0], src + d_tiles, (uint32_t)((size_t)nb * T * sizeof(double)), bar);
-    }
-    if (warp == 0) {
-        particle_setup(p, b, H.inv, &H.sc, lane);
-        if (lane == 0) H.setup_done = 1;
-    }
-    __syncthreads();
-    // residual = y - mu (:845-847): the very routine the full path queues (same code, same bits)
-    {
-        for (int m = warp; m < (N + T - 1) / T; m += NW) mean_item<MODE>(p, H, M, N, m, lane, stage);
-        __syncthreads();
-        mbar_wait(bar, 0);
-        for (int i = tid; i < N; i += THREADS) {
-            const int J = i / T;
-            M[H.base[J] + (size_t)(i % T) * H.ld[J] + (N - T * J)] = stage[i];
+    const kc_layout& L = p.L;
+    if (i < 4) return ldp(p, L.row_eta + i, b);
+    return i - 4 < L.n_jit ? ldp(p, L.row_jit + i - 4, b) : 0.0;
+}
+
+__global__ void gps_classify_kernel(const KParams p, const GpsCache gc)
+{
+    constexpr int KEYLEN = 4 + KC_MAX_INST;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.B) return;
+    const int slot = gc.slots[b];
+    int cl = -1;  // not cached
+    if (slot >= 0) {
+        GpsCacheMeta* m = gc.meta + (size_t)slot * 2;
+        bool eq0 = m[0].valid != 0, eq1 = m[1].valid != 0;
+        for (int i = 0; i < KEYLEN; i++) {
+            const long long k = __double_as_longlong(cache_key(p, b, i));
+            eq0 = eq0 && __double_as_longlong(m[0].key[i]) == k;
+            eq1 = eq1 && __double_as_longlong(m[1].key[i]) == k;
         }
-        if (tid == 0) H.col_done = 0x7fffffff;  // every panel of every block is there
+        if ((eq0 || eq1) && gc.debug != 1) {
+            cl = eq0 ? 0 : 1;
+            m[cl].stamp = gc.stamp;
+        } else {
+            // the entry to fill: an empty one, else the one used longer ago
+            int victim = !m[0].valid ? 0 : !m[1].valid ? 1 : (m[0].stamp - m[1].stamp <= 0 ? 0 : 1);
+            if (eq0 || eq1) victim = eq0 ? 0 : 1;  // (debug) refill the entry that matched
+            cl = -2 - victim;
+        }
+    }
+    gc.cls[b] = cl;
+    if (cl >= 0) gc.hit_list[atomicAdd(gc.cnt + 0, 1)] = b;
+    else gc.miss_list[atomicAdd(gc.cnt + 1, 1)] = b;
+}
+
+namespace hit {
+constexpr int WARPS = 8;
+struct WarpState {
+    PlanetInv inv[MAX_PLANETS];
+    ParticleScalars sc;
+    double z[MAXBLK * T];   // the residual row: z[32 J + c] = entry (N, 32 J + c)
+};
+}  // namespace hit
+
+template <int MODE>
+__global__ void __launch_bounds__(hit::WARPS * 32, 4) gps_hit_kernel(const KParams p, const GpsCache gc, const int pre)
+{
+    extern __shared__ __align__(16) unsigned char hit_smem[];
+    __shared__ int base[MAXBLK], ld[MAXBLK];
+    const int N = p.N;
+    const int nb = (N + T - 1) / T;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int fr = lane >> 2, fk = lane & 3;
+    if (tid == 0) {
+        int off = 0;
+        for (int J = 0; J < nb; J++) {
+            base[J] = off;
+            ld[J] = ld_for(N + 1 - T * J);
+            off += T * ld[J];
+        }
     }
     __syncthreads();
-    if (warp == 0) {
-        for (int J = 0; J < nb; J++) {
-            const int j0 = T * J;
-            const int nbc = min(T, N - j0);
-            if (J >= 1) {
-                const int nstrips = (N + 1 - j0 + 7) / 8;
-                const int ndiag = min(4, nstrips);
-                const int sN = (N - j0) / 8;  // the strip that holds row N
-                if (sN < ndiag) {
-                    // a short last block: the residual row rides with the look-ahead strips of the full path
-                    if (PRE && J >= 2) update_strip<true>(H, M, N, J, sN, lane, 0, J - 1);
-                    update_strip<true>(H, M, N, J, sN, lane, PRE ? J - 1 : 0, J);
-                } else {
-                    update_strip<true>(H, M, N, J, sN, lane, 0, J);
+    const int item = blockIdx.x * hit::WARPS + warp;
+    if (item >= gc.cnt[0]) return;
+    const int b = gc.hit_list[item];
+    const int slot = gc.slots[b], entry = gc.cls[b];
+    hit::WarpState& W = reinterpret_cast<hit::WarpState*>(hit_smem)[warp];
+    const double* __restrict__ img = gc.img + ((size_t)slot * 2 + entry) * gc.img_doubles;
+    const size_t d_tiles = gc.img_doubles - (size_t)nb * T;
+    const double* __restrict__ dinv = img + d_tiles;
+    // The image is read once, in a known order, 32x32 blocks at a time.  Thousands of warps are in flight on
+    // the chip (L2 holds ~26 KB for each), so a warp asks L2 for one block ahead of its use, no more: lane c
+    // the 256 bytes of column c.
+    auto prefetch_block = [&](const double* blk, const int ldk) {
+        const double* q = blk + (size_t)lane * ldk;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(q + 16));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(q + 31));
+    };
+    prefetch_block(img + base[0], ld[0]);  // the first diagonal block, behind the residuals
+
+    particle_setup_shared(p, b, W.inv, &W.sc, lane);
+    __syncwarp();
+    for (int m = 0; m < nb; m++) {
+        const int i = T * m + lane;
+        W.z[i] = i < N ? residual_at<MODE>(p, &W.sc, W.inv, i) : 0.0;
+    }
+    __syncwarp();
+
+    // U_J on the residual row: z_J -= sum_k z_k L(J,k)^T over block columns [kb, ke), the DMMA sequence of
+    // update_strip (the A operand carries the row in all eight fragment rows: every row of the output is it)
+    auto U = [&](const int J, const int kb, const int ke) {
+        const int j0 = T * J;
+        double acc[4][2];
+#pragma unroll
+        for (int n = 0; n < 4; n++) acc[n][0] = acc[n][1] = 0.0;
+        for (int Jk = kb; Jk < ke; Jk++) {
+            const int ldk = ld[Jk];
+            const double* Bp = img + base[Jk] + (j0 - T * Jk) + fr + (size_t)fk * ldk;
+            const double* zk = W.z + T * Jk;
+            if (Jk + 1 < ke) prefetch_block(img + base[Jk + 1] + (j0 - T * (Jk + 1)), ld[Jk + 1]);
+#pragma unroll
+            for (int k4 = 0; k4 < T; k4 += 4) {
+                double bf[4];
+                const double af = zk[k4 + fk];
+#pragma unroll
+                for (int n = 0; n < 4; n++) bf[n] = __ldcg(Bp + (size_t)k4 * ldk + 8 * n);
+#pragma unroll
+                for (int n = 0; n < 4; n++) dmma(acc[n][0], acc[n][1], af, bf[n]);
+            }
+        }
+        if (fr == 0) {
+#pragma unroll
+            for (int n = 0; n < 4; n++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) W.z[T * J + 8 * n + 2 * fk + h] -= acc[n][h];
+        }
+        __syncwarp();
+    };
+
+    double quad = 0.0;
+    for (int J = 0; J < nb; J++) {
+        const int j0 = T * J;
+        const int nbc = min(T, N - j0);
+        if (J >= 1) {
+            const int nstrips = (N + 1 - j0 + 7) / 8;
+            const int ndiag = min(4, nstrips);
+            const int sN = (N - j0) / 8;  // the strip that holds row N
+            if (sN < ndiag) {
+                // a short last block: the residual row rides with the look-ahead strips of the full path,
+                // which 16-warp CTAs update one block column behind
+                if (pre && J >= 2) U(J, 0, J - 1);
+                U(J, pre ? J - 1 : 0, J);
+            } else {
+                U(J, 0, J);
+            }
+        }
+        // T_J on the residual row: the arithmetic of trsm_tile_full (full blocks) / trsm_tile (a partial last one)
+        const int ldj = ld[J];
+        const double* S = img + base[J];
+        double* zj = W.z + T * J;
+        double q = 0.0;
+        // the next step opens with block (J+1, 0) and closes with diagonal block J+1
+        if (J + 1 < nb) {
+            prefetch_block(img + base[0] + T * (J + 1), ld[0]);
+            prefetch_block(img + base[J + 1], ld[J + 1]);
+        }
+        if (nbc == T) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < T; c0 += CHOL_PANEL) {
+                double x[CHOL_PANEL], dv[CHOL_PANEL], l[CHOL_PANEL][CHOL_PANEL];
+#pragma unroll
+                for (int k = 0; k < CHOL_PANEL; k++) {
+                    x[k] = zj[c0 + k];
+                    dv[k] = __ldcg(dinv + T * J + c0 + k);
+                }
+#pragma unroll
+                for (int k = 0; k < CHOL_PANEL; k++)
+#pragma unroll
+                    for (int k2 = k + 1; k2 < CHOL_PANEL; k2++) l[k][k2] = __ldcg(S + (size_t)(c0 + k) * ldj + c0 + k2);
+#pragma unroll
+                for (int k = 0; k < CHOL_PANEL; k++) {
+                    const double x0 = x[k] * dv[k];
+                    x[k] = x0;
+                    q = kfma(x0, x0, q);
+#pragma unroll
+                    for (int k2 = k + 1; k2 < CHOL_PANEL; k2++) x[k2] = kfma(-x0, l[k][k2], x[k2]);
                 }
                 __syncwarp();
+                if (lane == 0) {
+#pragma unroll
+                    for (int k = 0; k < CHOL_PANEL; k++) zj[c0 + k] = x[k];
+                }
+                __syncwarp();
+                if (c0 + CHOL_PANEL < T) {
+                    const double af0 = zj[c0 + fk], af1 = zj[c0 + 4 + fk];
+                    for (int cb = c0 + CHOL_PANEL; cb < T; cb += 8) {
+                        const double b0 = __ldcg(S + (size_t)(c0 + fk) * ldj + cb + fr);
+                        const double b1 = __ldcg(S + (size_t)(c0 + 4 + fk) * ldj + cb + fr);
+                        double u0 = 0.0, u1 = 0.0;
+                        dmma(u0, u1, af0, b0);
+                        dmma(u0, u1, af1, b1);
+                        if (fr == 0) {
+                            zj[cb + 2 * fk] -= u0;
+                            zj[cb + 2 * fk + 1] -= u1;
+                        }
+                    }
+                    __syncwarp();
+                }
             }
-            const int first = j0 + nbc;
-            const int ntiles = (N + 1 - first + T - 1) / T;
-            if (nbc == T) trsm_tile_full<ROLLED, true>(H, M, N, J, ntiles - 1, lane);
-            else trsm_tile<true>(H, M, N, J, nbc, ntiles - 1, lane);
-            __syncwarp();
+        } else {
+#pragma unroll 1
+            for (int c0 = 0; c0 < nbc; c0 += CHOL_PANEL) {
+                double x[CHOL_PANEL];
+#pragma unroll
+                for (int k = 0; k < CHOL_PANEL; k++) x[k] = zj[min(c0 + k, nbc - 1)];
+#pragma unroll
+                for (int k = 0; k < CHOL_PANEL; k++) {
+                    const int c = c0 + k;
+                    if (c < nbc) {
+                        const double x0 = x[k] * __ldcg(dinv + T * J + c);
+                        x[k] = x0;
+                        q = kfma(x0, x0, q);
+                        const double* lc = S + (size_t)c * ldj + c0;
+#pragma unroll
+                        for (int k2 = k + 1; k2 < CHOL_PANEL; k2++) x[k2] = kfma(-x0, __ldcg(lc + k2), x[k2]);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) {
+#pragma unroll
+                    for (int k = 0; k < CHOL_PANEL; k++)
+                        if (c0 + k < nbc) zj[c0 + k] = x[k];
+                }
+                __syncwarp();
+                if (c0 + CHOL_PANEL < nbc) {
+                    double af[2];
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const int c = c0 + 4 * h + fk;
+                        af[h] = c < nbc ? zj[c] : 0.0;
+                    }
+                    for (int cb = c0 + CHOL_PANEL; cb < nbc; cb += 8) {
+                        double bf[2];
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            const int c = c0 + 4 * h + fk;
+                            bf[h] = (c < nbc && cb + fr < nbc) ? __ldcg(S + (size_t)c * ldj + cb + fr) : 0.0;
+                        }
+                        double u0 = 0.0, u1 = 0.0;
+                        dmma(u0, u1, af[0], bf[0]);
+                        dmma(u0, u1, af[1], bf[1]);
+                        const int col = cb + 2 * fk;
+                        if (fr == 0) {
+                            if (col < nbc) zj[col] -= u0;
+                            if (col + 1 < nbc) zj[col + 1] -= u1;
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
         }
-        if (lane == 0) {
-            const double pinf = __longlong_as_double(0x7ff0000000000000ll);
-            double logL = -0.5 * N * 1.8378770664093453 - me.logdet - 0.5 * H.quad;
-            if (isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
-            p.logL[b] = logL;
-            me.stamp = gc.stamp;
-        }
+        quad += q;  // |z|^2 block column by block column, the order of the full path
+    }
+    if (lane == 0) {
+        const double pinf = __longlong_as_double(0x7ff0000000000000ll);
+        // -0.5 N log(2 pi) - 0.5 * (2 sum log L_ii) - 0.5 r^T C^-1 r   (:858-870)
+        double logL = -0.5 * N * 1.8378770664093453 - gc.meta[(size_t)slot * 2 + entry].logdet - 0.5 * quad;
+        if (isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
+        p.logL[b] = logL;
     }
 }
 
 // NW warps per CTA (1 diag + NW-1 workers); 16 / NW CTAs share an SM when the factor is small
 // enough, so that the serial chains of several particles overlap.
-template <int MODE, int NW>
+template <int MODE, int NW, bool CACHE>
 __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const KParams p, const GpsCache gc)
 {
     constexpr int THREADS = NW * 32;
@@ -580,7 +763,13 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
     double* cS = sS + NP;
     double* M = cS + NP;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int b = blockIdx.x;
+    // One particle per CTA, a CTA per lane of the batch -- or, with a factor cache attached, a grid that fills
+    // the SMs once and walks the list of lanes gps_classify_kernel found no factor for (their number is only
+    // known on the device).
+    int item = blockIdx.x;
+    if (CACHE && item >= gc.cnt[1]) return;
+    do {  // without a cache: this CTA's lane, once (no back edge)
+    const int b = CACHE ? gc.miss_list[item] : item;
     const int nb = (N + T - 1) / T;
 #ifdef KC_GPS_PROFILE
     __shared__ long long prof_c[4];
@@ -628,46 +817,20 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             H.quad = 0.0;
             for (int I = 0; I <= MAXBLK; I++) H.tile_cnt[I] = 0;
             for (int I = 0; I < MAXBLK; I++) H.dcnt[I] = H.ccnt[I] = 0;
-            H.hit = H.victim = H.slot = -1;
-        }
-        if (gc.img && warp == NW - 1) {
-            // factor cache: is the factor of this covariance matrix in one of the slot's two entries?
-            constexpr int KEYLEN = 4 + KC_MAX_INST;
-            __syncwarp();
-            const int slot = gc.slots ? gc.slots[b] : -1;
-            if (slot >= 0) {
-                double mine = 0.0;
-                if (lane < 4) mine = ldp(p, L.row_eta + lane, b);
-                else if (lane < 4 + L.n_jit && lane < KEYLEN) mine = ldp(p, L.row_jit + lane - 4, b);
-                const GpsCacheMeta* m = gc.meta + (size_t)slot * 2;
-                bool eq0 = true, eq1 = true;
-                if (lane < KEYLEN) {
-                    H.key[lane] = mine;
-                    eq0 = __double_as_longlong(m[0].key[lane]) == __double_as_longlong(mine);
-                    eq1 = __double_as_longlong(m[1].key[lane]) == __double_as_longlong(mine);
-                }
-                const bool hit0 = __all_sync(0xffffffffu, eq0) && m[0].valid;
-                const bool hit1 = __all_sync(0xffffffffu, eq1) && m[1].valid;
-                if (lane == 0) {
-                    H.slot = slot;
-                    H.hit = hit0 ? 0 : hit1 ? 1 : -1;
-                    // the entry to fill on a miss: an empty one, else the one used longer ago
-                    H.victim = !m[0].valid ? 0 : !m[1].valid ? 1 : (m[0].stamp - m[1].stamp <= 0 ? 0 : 1);
+            H.victim = H.slot = -1;
+            if (CACHE) {
+                const int cl = gc.cls[b];   // -2 - victim: a cached lane whose factor is kept
+                if (cl <= -2) {
+                    H.victim = -2 - cl;
+                    H.slot = gc.slots[b];
                 }
             }
-        }
-    }
-    if (gc.img) {
-        __syncthreads();
-        if (H.hit >= 0) {
-            gps_solve_cached<MODE, NW>(p, gc, H, M, N, b);
-            return;
         }
     }
     if (p.F.MA) {
         // residual with the MA(1) term (:378-386): planets first, then the recurrence in the (still unused)
         // factor storage, all threads
-        if (warp == 0) particle_setup(p, b, H.inv, &H.sc, lane);
+        if (warp == 0) particle_setup_shared(p, b, H.inv, &H.sc, lane);
         __syncthreads();
         double* rbuf = M;
         ma_residuals<MODE>(p, &H.sc, H.inv, rbuf, rbuf + NP, tid, THREADS);
@@ -709,7 +872,7 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
 #if KC_GPS_SETUP_BY_DIAG
         if (!p.F.MA) {
             // the planets (needed by the residual items only), while the workers generate the first tile
-            particle_setup(p, b, H.inv, &H.sc, lane);
+            particle_setup_shared(p, b, H.inv, &H.sc, lane);
             if (lane == 0) st_release_cta(&H.setup_done, 1);
         }
 #endif
@@ -745,7 +908,7 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
         const int wid = (ISO || GENONLY) ? warp - 1 - (warp >> 2) : warp - 1;
         if (!KC_GPS_SETUP_BY_DIAG && warp == NW - 1 && !p.F.MA) {
             // the planets: needed by the residual items only, which sit behind block column 0 in the queue
-            particle_setup(p, b, H.inv, &H.sc, lane);
+            particle_setup_shared(p, b, H.inv, &H.sc, lane);
             if (lane == 0) st_release_cta(&H.setup_done, 1);
         }
         for (int J = 0; J < nb; J++) {
@@ -882,7 +1045,7 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
         if (!ok || isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
         p.logL[b] = logL;
     }
-    if (gc.img && H.slot >= 0) {
+    if (CACHE && H.slot >= 0) {
         // factor cache, a miss: the factor goes to the slot's older entry (not a failed factorisation)
         GpsCacheMeta& me = gc.meta[(size_t)H.slot * 2 + H.victim];
         double* dst = gc.img + ((size_t)H.slot * 2 + H.victim) * gc.img_doubles;
@@ -897,13 +1060,17 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
             bulk_store(dst + d_tiles, &H.dinv[0][0], (uint32_t)((size_t)nb * T * sizeof(double)));
             bulk_store_commit_wait();
         }
-        if (tid < 4 + KC_MAX_INST) me.key[tid] = H.key[tid];
+        if (tid < 4 + KC_MAX_INST) me.key[tid] = cache_key(p, b, tid);
         if (tid == 0) {
             me.logdet = logdet;
             me.valid = ok ? 1 : 0;
             me.stamp = gc.stamp;
         }
     }
+    if (!CACHE) break;
+    __syncthreads();  // the next particle of this CTA reuses the shared memory
+    item += gridDim.x;
+    } while (item < gc.cnt[1]);
 }
 
 }  // namespace
@@ -911,10 +1078,41 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
 template <int MODE, int NW>
 static cudaError_t launch_one(const KParams& p, size_t smem, cudaStream_t stream, const GpsCache& gc)
 {
-    cudaError_t e = cudaFuncSetAttribute(gps_kernel<MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e;
+    if (gc.img) {
+        // the misses of a cached batch: a persistent grid, one wave of CTAs walking the miss list
+        e = cudaFuncSetAttribute(gps_kernel<MODE, NW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gps_kernel<MODE, NW, true>, NW * 32, smem);
+        if (e != cudaSuccess) return e;
+        int grid = sms * (per_sm > 0 ? per_sm : 1);
+        if (grid > p.B) grid = p.B;
+        gps_kernel<MODE, NW, true><<<grid, NW * 32, smem, stream>>>(p, gc);
+        return cudaGetLastError();
+    }
+    e = cudaFuncSetAttribute(gps_kernel<MODE, NW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    gps_kernel<MODE, NW><<<p.B, NW * 32, smem, stream>>>(p, gc);
+    gps_kernel<MODE, NW, false><<<p.B, NW * 32, smem, stream>>>(p, gc);
     return cudaGetLastError();
+}
+
+// developer check: cached against uncached results of one launch, mismatches reported from the device
+__global__ void gps_cache_compare_kernel(const KParams p, const double* plain, const GpsCache gc)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.B) return;
+    const double a = p.logL[b], r = plain[b];
+    if (__double_as_longlong(a) != __double_as_longlong(r))
+        printf("# factor cache MISMATCH lane %d slot %d class %d: cached %.17g uncached %.17g np %d eta %.17g %.17g %.17g %.17g jit %.17g\n", b,
+               gc.slots[b], gc.cls[b], a, r, p.np[b], ldp(p, p.L.row_eta, b), ldp(p, p.L.row_eta + 1, b), ldp(p, p.L.row_eta + 2, b),
+               ldp(p, p.L.row_eta + 3, b), ldp(p, p.L.row_jit, b));
+}
+void launch_gp_cache_compare(const KParams& p, const double* plain, const GpsCache& gc, cudaStream_t s)
+{
+    gps_cache_compare_kernel<<<(p.B + 127) / 128, 128, 0, s>>>(p, plain, gc);
 }
 
 cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches,
@@ -924,6 +1122,28 @@ cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stre
     GpsCache gc{};
     // with the MA(1) term the residual recurrence uses the factor storage as scratch: no cache then
     if (cache && cache->img && cache->slots && !p.F.MA) gc = *cache;
+    const size_t smem0 = gps_smem_bytes(p.N);
+    if (!smem0) return cudaErrorInvalidValue;
+    const int fit0 = (int)((size_t)(228 * 1024) / (smem0 + 1024));
+    if (gc.img) {
+        // hits first (a warp each, the factor read from HBM / L2), then the misses through the full kernel
+        cudaError_t e0 = cudaMemsetAsync(gc.cnt, 0, 2 * sizeof(int), stream);
+        if (e0 != cudaSuccess) return e0;
+        gps_classify_kernel<<<(p.B + 127) / 128, 128, 0, stream>>>(p, gc);
+        const size_t hsm = sizeof(hit::WarpState) * hit::WARPS;
+        const int pre = fit0 < 2 ? 1 : 0;  // 16-warp CTAs update the look-ahead strips one block column behind
+        const int hgrid = (p.B + hit::WARPS - 1) / hit::WARPS;
+        if (kepler_mode == 0) {
+            e0 = cudaFuncSetAttribute(gps_hit_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsm);
+            if (e0 != cudaSuccess) return e0;
+            gps_hit_kernel<0><<<hgrid, hit::WARPS * 32, hsm, stream>>>(p, gc, pre);
+        } else {
+            e0 = cudaFuncSetAttribute(gps_hit_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsm);
+            if (e0 != cudaSuccess) return e0;
+            gps_hit_kernel<1><<<hgrid, hit::WARPS * 32, hsm, stream>>>(p, gc, pre);
+        }
+        *n_launches += 2;
+    }
     const size_t smem = gps_smem_bytes(p.N);
     if (!smem) return cudaErrorInvalidValue;
     // CTAs per SM by shared-memory footprint (228 KB per SM, 1 KB reserved per CTA)

@@ -94,8 +94,15 @@ struct GpsCache {
     const int32_t* slots;         // [B]: slot of every lane of this launch (< 0: not cached)
     size_t img_doubles;
     int stamp;
+    // per-launch work lists (gps_classify_kernel), each [max_batch]
+    int* cls;                     // lane -> entry that holds its factor (0 / 1), -1: not cached, -2 - e: a miss that fills entry e
+    int* hit_list;
+    int* miss_list;
+    int* cnt;                     // [0]: hits, [1]: misses
+    int debug;                    // developer switch (KIMA_CUDA_GP_CACHE_DEBUG): 1 = every cached lane is treated as a miss
 };
 size_t gps_cache_img_doubles(int N);
+void launch_gp_cache_compare(const KParams& p, const double* plain, const GpsCache& gc, cudaStream_t s);  // developer check
 cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches,
                             const GpsCache* cache = nullptr);
 // kernel = celerite (kc_celerite.cu): resid is [N][ldr] doubles of scratch

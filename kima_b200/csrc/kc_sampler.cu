@@ -381,6 +381,11 @@ int kc_sampler_create(kc_ctx* c, const kc_prior_table* priors, const kc_sampler_
 {
     const int rc = sampler_create_impl(c, priors, cfg);
     if (rc != KC_OK && c) kc::sampler_free(c);  // no half-built sampler behind a failed call
+    if (rc == KC_OK && c->gp_cache_opt) {
+        // one factor-cache slot per particle (kima_cuda.h: kc_gp_cache_enable); a cache that does not fit the
+        // device memory, or a model it does not apply to, leaves the sampler as it is
+        (void)kc_gp_cache_enable(c, cfg->lanes * cfg->num_particles);
+    }
     return rc;
 }
 

@@ -169,3 +169,15 @@ def test_cache_is_inactive_where_it_does_not_apply(gpu):
         with pytest.raises(Exception):
             eng.set_slots(np.array([0, 1, 2, 3, 4, 5, 6, 8], np.int32))   # slot outside the cache
         assert eng.enable_gp_cache(0) == 0
+
+
+def test_device_proposal_chains_do_not_depend_on_the_cache(gpu, tmp_path):
+    """examples/CoRoT7 (GP, hyperpriors) with device-side proposals: kc_sampler_create attaches one slot per
+    particle; with and without it the run writes the same files, byte for byte.  (Host proposals: the cache
+    is opt-in there, host/RVmodelDevice.h::enable_factor_cache.)"""
+    from test_device_proposals import run
+    opts = "2\n500\n200\n50\n0\n10\n100\n400\n"   # 2 particles x 64 lanes, 50 thread steps, 400 saves
+    off = run("gpu", "CoRoT7", tmp_path, "off", 64, 43, True, opts, {"KIMA_CUDA_GP_CACHE": "0"})
+    on = run("gpu", "CoRoT7", tmp_path, "on", 64, 43, True, opts, {"KIMA_CUDA_GP_CACHE": "1"})
+    for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
+        assert (off / f).read_bytes() == (on / f).read_bytes(), f
