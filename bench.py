@@ -564,9 +564,13 @@ def main():
         # counters on the GPU as well (KIMA_DEVICE_PROPOSALS=1, include/kima_sampler.h): particles stay
         # in HBM, the host only does DNest4's bookkeeping between blocks of thread_steps steps
         dev_env = {"KIMA_DEVICE_PROPOSALS": "1"}
+        # CoRoT7 (GP): the sampler's factor cache (kima_cuda.h: kc_gp_cache_enable) is on by default with device
+        # proposals; the same run without it is reported beside it (the chains are the same bytes)
         out["sampler"]["device_proposals"] = [
             sampler_bench.run("gpu", "51Peg", 65536, 100, 20, env=dev_env),
-            sampler_bench.run("gpu", "CoRoT7", 16384, 100, 10, env=dev_env)]
+            dict(sampler_bench.run("gpu", "CoRoT7", 16384, 100, 10, env=dev_env) or {}, factor_cache=True),
+            dict(sampler_bench.run("gpu", "CoRoT7", 16384, 100, 10, env=dict(dev_env, KIMA_CUDA_GP_CACHE="0")) or {},
+                 factor_cache=False)]
         out["sampler"]["device_steps"] = sampler_device_leg(local)
     if rank == 0 and world == 1 and not a.skip_predictive and not a.skip_cpu_baseline:
         out["predictive"] = predictive_leg(make_data(1000), WORKLOADS["gp"]["flags"], local, threads)
