@@ -192,6 +192,8 @@ int kc_stream(kc_ctx* ctx, void** stream);
  * gp_streams:  lane groups of the blocked GP path, 1..4 (default 2); gp_slots: lanes in flight (0 = by memory);
  *              both take effect at the next kc_configure.
  * eval_chunk:  kc_eval batches of >= 2 chunks overlap H2D with the kernels (default 32768 lanes, 0 = off).
+ * gp_order:    1 = the shared-memory-resident GP kernel takes the lanes of a batch (>= 1024) in order of planet
+ *              count, which keeps the SMs in step (default; results do not depend on it), 0 = in lane order.
  * gp_cache:    1 = kc_sampler_create attaches a factor cache, one slot per particle (default), 0 = it does not. */
 int kc_set_option(kc_ctx* ctx, const char* key, int value);
 

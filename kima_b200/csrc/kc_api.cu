@@ -47,6 +47,8 @@ void free_model(kc_ctx* c)
     if (c->h_logL) cudaFreeHost(c->h_logL);
     cudaFree(c->d_params); cudaFree(c->d_np); cudaFree(c->d_logL);
     cudaFree(c->gp.ws); cudaFree(c->gp.lanes); cudaFree(c->d_resid);
+    cudaFree(c->d_order);
+    c->d_order = nullptr;
     c->d_resid = nullptr;
     for (int i = 0; i < 3; i++) {
         if (c->gp.aux[i]) cudaStreamDestroy(c->gp.aux[i]);
@@ -115,7 +117,9 @@ int run_kernels(kc_ctx* c, int B, double* d_logL, const double* d_params, const 
         kc::GpsCache gc = c->gpc;
         gc.slots = d_slots;
         gc.stamp = ++c->gpc.stamp;
-        e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n, gc.img && d_slots ? &gc : nullptr);
+        if (!c->d_order && c->gp_order_opt) CU(cudaMalloc(&c->d_order, sizeof(int) * (size_t)c->max_batch));
+        e = kc::launch_gp_small(p, c->kepler_mode, c->stream, &n, gc.img && d_slots ? &gc : nullptr,
+                                c->gp_order_opt && !c->np_uniform ? c->d_order : nullptr);
         if (e == cudaSuccess && gc.img && d_slots && gc.debug >= 2) {
             // developer check (KIMA_CUDA_GP_CACHE_DEBUG=2): the same lanes through the uncached kernel, compared on the device
             if (!c->d_chk) cudaMalloc(&c->d_chk, sizeof(double) * c->max_batch);
@@ -364,6 +368,10 @@ int kc_eval_async(kc_ctx* c, int B, double* logL_host)
         slots = c->d_slots;
     }
     c->slots_B = 0;
+    // the planet counts are at hand here: a batch in which they are all equal needs no ordering (gp_order)
+    c->np_uniform = true;
+    for (int i = 1; i < B && c->np_uniform; i++) c->np_uniform = c->h_np[i] == c->h_np[0];
+    struct Reset { bool& f; ~Reset() { f = false; } } reset_hint{c->np_uniform};
     const int chunk = c->eval_chunk_opt;
     if (chunk > 0 && B >= 2 * chunk) {
         // large batches: the columns travel in chunks on a copy stream while the kernels of the
@@ -529,6 +537,8 @@ int kc_set_option(kc_ctx* c, const char* key, int value)
     } else if (k == "eval_chunk") {
         if (value < 0) return fail(KC_ERR_ARG, "eval_chunk must be >= 0 (0 = one copy, no overlap)");
         c->eval_chunk_opt = value;
+    } else if (k == "gp_order") {
+        c->gp_order_opt = value ? 1 : 0;  // small GP path: lanes handed to the SMs in order of planet count
     } else if (k == "gp_cache") {
         c->gp_cache_opt = value ? 1 : 0;  // kc_sampler_create attaches a factor cache (takes effect at the next call)
     } else if (k == "gp_slots") {

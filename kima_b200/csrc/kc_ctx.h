@@ -41,6 +41,9 @@ struct kc_ctx {
     int eval_chunk_opt = 32768;  // kc_eval: batches of >= 2 chunks overlap H2D with the kernels (0 = off)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t copy_ev = nullptr;
+    int gp_order_opt = 1;   // small GP path: batches of >= 1024 lanes run in order of planet count (keeps the SMs in step)
+    int* d_order = nullptr;
+    bool np_uniform = false; // set by kc_eval_async around its launches: every lane of the batch has the same planet count
     int gp_cache_opt = 1;   // kc_sampler_create: one factor-cache slot per particle where the cache applies
     int gp_small_opt = 1;   // 1 = shared-memory-resident kernel whenever N fits, 0 = always blocked
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -121,7 +121,14 @@ using namespace gps;
 #define KC_GPS_SLEEP_F 40
 #endif
 #ifdef KC_GPS_PROFILE
-__device__ long long g_prof_twait[1024], g_prof_tsub[1024], g_prof_tdmma[1024];   // per CTA (mod 1024): cycles warp 1 waited for col_done inside trsm_tile
+__device__ long long g_prof_twait[1024], g_prof_tsub[1024], g_prof_tdmma[1024];
+__device__ unsigned long long g_prof_cta[3 * 32768];  // per lane: globaltimer at entry and exit (ns), SM id
+__device__ __forceinline__ unsigned long long prof_globaltimer()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}   // per CTA (mod 1024): cycles warp 1 waited for col_done inside trsm_tile
 #endif
 template <int WORKERS>
 __device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"(WORKERS * 32) : "memory"); }
@@ -769,11 +776,19 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
     int item = blockIdx.x;
     if (CACHE && item >= gc.cnt[1]) return;
     do {  // without a cache: this CTA's lane, once (no back edge)
-    const int b = CACHE ? gc.miss_list[item] : item;
+    const int b = CACHE ? gc.miss_list[item] : (p.order ? p.order[item] : item);
     const int nb = (N + T - 1) / T;
 #ifdef KC_GPS_PROFILE
     __shared__ long long prof_c[4];
-    if (tid == 0) prof_c[0] = clock64();
+    if (tid == 0) {
+        prof_c[0] = clock64();
+        if (b < 32768) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            g_prof_cta[3 * b] = prof_globaltimer();
+            g_prof_cta[3 * b + 2] = smid;
+        }
+    }
 #endif
 
     // ---- start-up.  Nothing the factorisation's first steps need waits for the planets: every thread reads
@@ -1044,6 +1059,9 @@ __global__ void __launch_bounds__(NW * 32, WARPS_PER_SM / NW) gps_kernel(const K
         double logL = -0.5 * N * 1.8378770664093453 - logdet - 0.5 * H.quad;
         if (!ok || isnan(logL) || isinf(logL)) logL = pinf;  // (:938-941)
         p.logL[b] = logL;
+#ifdef KC_GPS_PROFILE
+        if (b < 32768) g_prof_cta[3 * b + 1] = prof_globaltimer();
+#endif
     }
     if (CACHE && H.slot >= 0) {
         // factor cache, a miss: the factor goes to the slot's older entry (not a failed factorisation)
@@ -1115,10 +1133,73 @@ void launch_gp_cache_compare(const KParams& p, const double* plain, const GpsCac
     gps_cache_compare_kernel<<<(p.B + 127) / 128, 128, 0, s>>>(p, plain, gc);
 }
 
-cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches,
-                            const GpsCache* cache)
+// Lanes in order of planet count, most planets first (one CTA, a counting sort; the order within a count is
+// whatever the atomics make it: nothing depends on it).  Why: the kernel's hot code (~60-100 KB over its warp
+// roles) does not fit the SM's instruction cache, and SMs that run the same phase at the same time feed each
+// other through the shared levels.  A batch whose neighbouring CTAs differ in planet count -- any real one --
+// drifts out of step and EVERY particle gets slower, the planet-free ones included (N = 177, Np ~ U{0..5}:
+// 61.8 us per particle against 48.6 us for the same lanes sorted, 6.37 vs 5.27 ms per 16 384 lanes,
+// profiles/gps_timeline_r02.jsonl); CTAs are handed out in index order, so sorting keeps the SMs in step.
+// With `list` (the miss list of a cached batch, *n_list entries): the same over the lanes of that list.
+__global__ void __launch_bounds__(1024) gps_order_kernel(const int32_t* __restrict__ np, int B, int* __restrict__ order,
+                                                         const int* __restrict__ list, const int* __restrict__ n_list)
 {
-    if (p.B <= 0) return cudaSuccess;
+    constexpr int BUCKETS = 64;
+    __shared__ int cnt[BUCKETS], off[BUCKETS];
+    const int tid = threadIdx.x;
+    if (list) B = *n_list;
+    if (tid < BUCKETS) cnt[tid] = 0;
+    __syncthreads();
+    // warp-aggregated: lanes of a warp with the same count send one atomic (a batch of equal counts would
+    // otherwise serialise B atomics on one address)
+    const int nround = (B + blockDim.x - 1) / blockDim.x;
+    for (int r = 0; r < nround; r++) {
+        const int i = r * blockDim.x + tid;
+        const int b = i < B ? (list ? list[i] : i) : -1;
+        const int key = b >= 0 ? min(max(np[b], 0), BUCKETS - 1) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        if (key >= 0 && (tid & 31) == __ffs(peers) - 1) atomicAdd(&cnt[key], __popc(peers));
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int o = 0;
+        for (int k = BUCKETS - 1; k >= 0; k--) {
+            off[k] = o;
+            o += cnt[k];
+        }
+    }
+    __syncthreads();
+    for (int r = 0; r < nround; r++) {
+        const int i = r * blockDim.x + tid;
+        const int b = i < B ? (list ? list[i] : i) : -1;
+        const int key = b >= 0 ? min(max(np[b], 0), BUCKETS - 1) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs(peers) - 1, lane = tid & 31;
+        int base = 0;
+        if (key >= 0 && lane == leader) base = atomicAdd(&off[key], __popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (key >= 0) order[base + __popc(peers & ((1u << lane) - 1))] = b;
+    }
+}
+
+#ifdef KC_GPS_PROFILE
+extern "C" int kc_prof_fetch_cta(unsigned long long* out, int n)
+{
+    return (int)cudaMemcpyFromSymbol(out, g_prof_cta, sizeof(unsigned long long) * 3 * (size_t)n);
+}
+#endif
+
+cudaError_t launch_gp_small(const KParams& p0, int kepler_mode, cudaStream_t stream, int* n_launches,
+                            const GpsCache* cache, int* order_scratch)
+{
+    if (p0.B <= 0) return cudaSuccess;
+    KParams p = p0;
+    p.order = nullptr;
+    if (order_scratch && p.B >= 1024 && !(cache && cache->img && cache->slots)) {
+        gps_order_kernel<<<1, 1024, 0, stream>>>(p.np, p.B, order_scratch, nullptr, nullptr);
+        p.order = order_scratch;
+        *n_launches += 1;
+    }
     GpsCache gc{};
     // with the MA(1) term the residual recurrence uses the factor storage as scratch: no cache then
     if (cache && cache->img && cache->slots && !p.F.MA) gc = *cache;
@@ -1143,6 +1224,12 @@ cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stre
             gps_hit_kernel<1><<<hgrid, hit::WARPS * 32, hsm, stream>>>(p, gc, pre);
         }
         *n_launches += 2;
+        if (order_scratch && p.B >= 1024) {
+            // the misses in order of planet count too: the CTAs of the persistent grid walk the list in step
+            gps_order_kernel<<<1, 1024, 0, stream>>>(p.np, p.B, order_scratch, gc.miss_list, gc.cnt + 1);
+            gc.miss_list = order_scratch;
+            *n_launches += 1;
+        }
     }
     const size_t smem = gps_smem_bytes(p.N);
     if (!smem) return cudaErrorInvalidValue;

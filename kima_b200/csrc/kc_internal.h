@@ -31,6 +31,7 @@ struct KParams {
     int ld, B;
     double* logL;           // [B]
     int* counter;           // dynamic work counter (zeroed before launch)
+    const int* order;       // small GP path: lane run by CTA i (lanes in order of planet count), null = i
 };
 
 // Launchers (kc_keplerian.cu, kc_gp.cu).  All asynchronous on `stream`.
@@ -104,7 +105,7 @@ struct GpsCache {
 size_t gps_cache_img_doubles(int N);
 void launch_gp_cache_compare(const KParams& p, const double* plain, const GpsCache& gc, cudaStream_t s);  // developer check
 cudaError_t launch_gp_small(const KParams& p, int kepler_mode, cudaStream_t stream, int* n_launches,
-                            const GpsCache* cache = nullptr);
+                            const GpsCache* cache = nullptr, int* order_scratch = nullptr);
 // kernel = celerite (kc_celerite.cu): resid is [N][ldr] doubles of scratch
 cudaError_t launch_gp_celerite(const KParams& p, double* resid, int ldr, int kepler_mode,
                                cudaStream_t stream, int* n_launches);
