@@ -187,6 +187,35 @@ def test_gp_small_path_edges(gpu, port, N):
     assert relerr(got, blocked).max() <= LOGL_RTOL
 
 
+@pytest.mark.parametrize("N,mode", [(64, "mix"), (100, "mix"), (177, "mix"), (177, "max")])
+def test_gp_small_path_lane_order_does_not_matter(gpu, port, N, mode):
+    """Batches of >= 1024 lanes reach the SMs in order of planet count (gps_order_kernel, option gp_order:
+    it keeps the SMs in step).  The order is scheduling only: the same bits with it and without it, from
+    host buffers (kc_eval knows when all counts are equal and skips it) and from the device block, and
+    the oracle's values."""
+    flags = ModelFlags(GP=True, npmax=5, hyperpriors=True)
+    d = make_data(N, seed=8000 + N)
+    B = 3000
+    P, nps = make_params(flags, d, B, mode, seed=N)
+    port.set_rvdata(d)
+    port.set_flags(flags)
+    ref, _ = port.eval_batch(P[:, :256], nps[:256], nthreads=8)
+    with LikelihoodEngine(d, flags, B) as eng:
+        ordered = eng.evaluate(P, nps)
+        n0 = eng.launch_count()
+        eng.log_likelihood_device(B)
+        eng.sync()
+        assert eng.launch_count() - n0 == 2           # the ordering kernel + the likelihood kernel
+        eng.set_option("gp_order", 0)
+        plain = eng.evaluate(P, nps)
+        n0 = eng.launch_count()
+        eng.log_likelihood_device(B)
+        eng.sync()
+        assert eng.launch_count() - n0 == 1
+    assert np.array_equal(ordered, plain)
+    assert relerr(ordered[:256], ref).max() <= LOGL_RTOL
+
+
 def test_ragged_batches_and_reuse(gpu, port):
     """B = 1, odd sizes, reuse of one context for shrinking and growing batches."""
     flags = ModelFlags(npmax=3)
