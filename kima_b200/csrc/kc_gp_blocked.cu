@@ -12,12 +12,13 @@
 //   for J:    diag    S_JJ = C_JJ - L[J,0:j0] L[J,0:j0]^T, unblocked Cholesky in shared
 //                     memory, L_JJ and 1/diag to HBM, log det accumulated
 //             update  one CTA per (128-row tile, particle):
-//                     S = C[tile,J] - L[tile,0:j0] L[J,0:j0]^T   (DMMA, cp.async pipeline)
+//                     S = C[tile,J] - L[tile,0:j0] L[J,0:j0]^T   (DMMA, TMA + mbarrier pipeline)
 //                     X = S L_JJ^-T (forward substitution, a row per thread), X -> HBM
 //   finish    logL = -N/2 log 2pi - sum log L_ii - |z|^2/2, non-finite -> +inf
 //
-// C is never stored: every entry is generated from (t_i - t_j) inside the epilogue of
-// the tile that consumes it.  HBM traffic per particle is one write of L (4 N^2 B) and
+// C is never stored: every entry is generated inside the epilogue of the tile that consumes it, from
+// (t_i - t_j) and the epochs' phases (kc_gp_common.cuh: gp_phase / qp_entry; the prep kernel leaves
+// the 2N sines and cosines of a lane in two extra columns of its factor storage).  HBM traffic per particle is one write of L (4 N^2 B) and
 // N^3/(6 NB) * 8 B of panel re-reads; the FLOPs are the N^3/3 of the factorisation, all
 // of the O(N^3) part on the FP64 tensor cores (mma.sync m8n8k4, SASS DMMA).
 #include <cuda.h>  // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)

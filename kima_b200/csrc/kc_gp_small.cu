@@ -1,5 +1,5 @@
 // Kernel family 2, small-N path: the whole GP likelihood of one particle inside one CTA,
-// the factor resident in shared memory (N <= ~208: CoRoT7-sized data sets).
+// the factor resident in shared memory (N <= 211: CoRoT7-sized data sets).
 //
 // Replaces, per particle,  calculate_mu() -> calculate_C() -> log_likelihood()
 // (GP / standard-kernel branch) of the reference
@@ -13,21 +13,24 @@
 //
 // Warp roles (16 warps in one CTA per SM; 8, 5 or 4 warps in 2, 3 or 4 CTAs per SM when the factor
 // is small enough, so that the serial chains of several particles overlap):
-//   warp 0      "diag": the 32x32 Cholesky of each diagonal block (chol32_panels: 8-column panels
-//               with the rows in lanes, trailing update on the tensor cores) -- a serial chain of
-//               N column steps, the critical path
+//   warp 0      "diag": the planet invariants, then the 32x32 Cholesky of each diagonal block
+//               (chol32_panels: 8-column panels with the rows in lanes, trailing update on the
+//               tensor cores) -- a serial chain of N column steps, the critical path
 //   warps 1..   "workers", left-looking per block column J:
-//       U_J  S[:,J] = C[:,J] - L[:,0:j0] L[J,0:j0]^T   8x32 strips on the FP64 tensor cores
-//       T_J  X = S L_JJ^-T                              a row per lane, 8-column panels + DMMA
-//     and, whenever they would wait for the diag warp, they generate covariance entries of
-//     later block columns from a shared work queue: the generation (the largest consumer of
-//     issue slots at this size) hides under the factorisation chain.
+//       U_J  S[:,J] = C[:,J] - L[:,0:j0] L[J,0:j0]^T   8x32 strips on the FP64 tensor cores; the
+//            strips of the diagonal tile first, as soon as that tile exists and T_{J-1} has
+//            finished the rows of block J (flags, not barriers)
+//       T_J  X = S L_JJ^-T                              a row per lane, 8-column panels + DMMA,
+//            panel by panel behind the diag warp
+//     and, whenever they would wait, items of a work queue: covariance entries of later block
+//     columns (gen_item; the generator of kc_gp_common.cuh) and, behind block column 0, the
+//     residuals (mean_item).
+// Around it: gps_order_kernel hands the lanes of a batch to the SMs in order of planet count;
+// gps_classify_kernel / gps_hit_kernel / gps_kernel<.., CACHE = true> are the factor cache
+// (kima_cuda.h: kc_gp_cache_enable).  DESIGN.md sections 3.2.1 and 3.2.4 have the measurements.
 #include "kc_model.cuh"
 #include "kc_gp_common.cuh"
 #include <cstdio>
-#ifdef KC_GPS_PROFILE
-#include <cstdio>
-#endif
 
 namespace kc {
 
