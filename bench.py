@@ -560,6 +560,12 @@ def main():
         out["sampler"] = {"unit": "MCMC steps/s", "lanes": 4096, "cpu_threads": threads,
                           "runs": [sampler_bench.compare(n, 4096, threads, gpu_saves=80, cpu_saves=100)
                                    for n in ("CoRoT7", "51Peg")]}
+        # CoRoT7 (GP): one factor-cache slot per particle is the default on this path too
+        # (host/RVmodelDevice.h::enable_factor_cache); the same run without it beside it
+        out["sampler"]["runs"][0]["factor_cache"] = True
+        out["sampler"]["runs"].append(dict(example="CoRoT7", factor_cache=False,
+                                           gpu=sampler_bench.run("gpu", "CoRoT7", 4096, 100, 80,
+                                                                 env={"KIMA_CUDA_GP_CACHE": "0"})))
         # the same examples with proposals, prior test, accept logic and level
         # counters on the GPU as well (KIMA_DEVICE_PROPOSALS=1, include/kima_sampler.h): particles stay
         # in HBM, the host only does DNest4's bookkeeping between blocks of thread_steps steps

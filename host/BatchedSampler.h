@@ -150,6 +150,7 @@ class BatchedSampler : public Sampler<ModelType> {
                 st.particle_first = (rng.rand() <= 0.5);
                 if (!st.particle_first) this->update_level_assignment(k, st.which);
                 st.proposal = this->particles[st.which];
+                evaluator->own_lane_priors(st.proposal, (size_t)k);  // hyperpriors: no prior object shared between threads
                 double log_H = st.proposal.perturb(rng);
                 if (log_H > 0.0) log_H = 0.0;
                 st.scored = (rng.rand() <= exp(log_H));
@@ -168,6 +169,10 @@ class BatchedSampler : public Sampler<ModelType> {
                 }
         });
         prof[1] += now() - t1;
+        static const bool verify_stage = std::getenv("KIMA_VERIFY_STAGE") != nullptr;
+        if (verify_stage)  // developer check: the block the pool staged against a serial restaging
+            for (unsigned int k = k0; k < k1; ++k)
+                if (lane_steps[k].scored) evaluator->check_staged(g, lane_steps[k].slot, lane_steps[k].proposal, (int)k);
         return nb;
     }
 
@@ -329,6 +334,7 @@ class BatchedSampler : public Sampler<ModelType> {
         if (lane_steps.size() != T) {
             lane_steps.resize(T);
             for (auto& st : lane_steps) evaluator->strip(st.proposal);
+            evaluator->reserve_lane_priors(T);
         }
         // this rank's lanes [k0, k1), in two groups
         const unsigned int k0 = lane_lo(), k1 = lane_hi(), n = k1 - k0;

@@ -169,6 +169,34 @@ public:
         }
     }
 
+    // ---- hyperpriors: one pair of planet-prior objects per lane -------------------------------
+    // With hyperpriors the reference re-parameterises the period and amplitude priors before every use
+    // (Pprior->setpars(center, width); Kprior->setpars(muK): src/RVConditionalPrior.cpp:111-112, 135-136,
+    // 150-151) -- and those objects are shared: every copy of a particle (SamplerImpl.h:184, 208, and
+    // kill_lagging_particles' copies between threads, :487) aliases the shared_ptr of its source
+    // (RVConditionalPrior.h:30-32).  Two host threads that perturb descendants of one particle then race
+    // between one's setpars() and the other's cdf(): a period drawn with another particle's centre.  The
+    // reference's own -t threads have that race too; here it made one run in ten at 4096 lanes differ from
+    // the next.  Each lane therefore gets objects of its own (default-constructed as the reference's are,
+    // src/RVConditionalPrior.cpp:43-44; their state is overwritten by setpars before every read), and a
+    // proposal is pointed at its lane's pair before perturb() runs: the values are those of a serial run.
+    void reserve_lane_priors(size_t lanes)
+    {
+        if (!hyperpriors || lane_Pprior_.size() == lanes) return;
+        lane_Pprior_.resize(lanes);
+        lane_Kprior_.resize(lanes);
+        for (size_t k = 0; k < lanes; k++) {
+            lane_Pprior_[k] = std::make_shared<DNest4::Laplace>();
+            lane_Kprior_[k] = std::make_shared<DNest4::Exponential>();
+        }
+    }
+    void own_lane_priors(RVmodel& m, size_t lane) const
+    {
+        if (!hyperpriors || lane >= lane_Pprior_.size()) return;
+        m.planets.conditional_prior.Pprior = lane_Pprior_[lane];
+        m.planets.conditional_prior.Kprior = lane_Kprior_[lane];
+    }
+
     int max_batch() const { return ctx_[0]->max_batch(); }
     int max_batch(int g) const { return ctx_[g]->max_batch(); }
 
@@ -207,13 +235,39 @@ public:
     void stage(int g, int lane, const RVmodel& m)
     {
         kimacuda::Context* ctx_ = this->ctx_[g].get();
-        const kc_layout& L = ctx_->layout();
-        double* P = ctx_->params();
-        const size_t ld = (size_t)ctx_->ld();
+        stage_to(ctx_->layout(), ctx_->params(), (size_t)ctx_->ld(), ctx_->np(), lane, m);
+    }
+    // developer check (KIMA_VERIFY_STAGE=1, host/BatchedSampler.h): is column `lane` of the staging block what
+    // staging particle `m` now would write?  Rows staging leaves alone compare equal by construction.
+    bool check_staged(int g, int lane, const RVmodel& m, int tag)
+    {
+        kimacuda::Context* c = this->ctx_[g].get();
+        const kc_layout& L = c->layout();
+        const size_t ld = (size_t)c->ld();
+        std::vector<double> col((size_t)L.n_rows);
+        for (int r = 0; r < L.n_rows; r++) col[(size_t)r] = c->params()[(size_t)r * ld + lane];
+        int32_t npv = c->np()[lane];
+        const int32_t np_block = npv;
+        std::vector<double> want = col;
+        stage_to(L, want.data(), 1, &npv, 0, m);
+        bool ok = npv == np_block;
+        for (int r = 0; r < L.n_rows; r++)
+            if (std::memcmp(&want[(size_t)r], &col[(size_t)r], sizeof(double)) != 0) {
+                ok = false;
+                std::fprintf(stderr, "# STAGE MISMATCH group %d lane-tag %d column %d row %d: block %.17g, particle %.17g, block now %.17g\n",
+                             g, tag, lane, r, col[(size_t)r], want[(size_t)r], c->params()[(size_t)r * ld + lane]);
+            }
+        if (npv != np_block)
+            std::fprintf(stderr, "# STAGE MISMATCH group %d lane-tag %d column %d: np block %d particle %d now %d\n", g, tag, lane,
+                         (int)np_block, (int)npv, (int)c->np()[lane]);
+        return ok;
+    }
+    void stage_to(const kc_layout& L, double* P, const size_t ld, int32_t* npv, int lane, const RVmodel& m)
+    {
         auto put = [&](int row, double v) { P[(size_t)row * ld + lane] = v; };
         const auto& comps = m.planets.get_components();
         const int np = (int)comps.size();
-        ctx_->np()[lane] = np;
+        npv[lane] = np;
         for (int j = 0; j < np; j++) {
             put(L.row_P + j, comps[j][0]);   // P, or log P under hyperpriors (:357-360)
             put(L.row_K + j, comps[j][1]);
@@ -260,6 +314,7 @@ public:
     // the same, split: submit returns at once, wait blocks until logL[0..B) is there
     void submit(int g, int B, double* logL)
     {
+        if (trace_) trace_in_[g] = trace_hash_batch(g, B);
         if (cache_slots_[g] > 0) ctx_[g]->set_slots(B, slot_of_lane_[g].data());
         ctx_[g]->eval_async(B, logL);
         pending_B_[g] = B;
@@ -271,14 +326,9 @@ public:
     // perturb()'s proposals leave it alone (:448-544); results are the same bits with or without the cache.
     void enable_factor_cache(int g, int n_particles)
     {
-        // Opt-in on this path (KIMA_CUDA_GP_CACHE=1); the device-proposal path attaches its cache by default.
-        // With host proposals, two contexts and several host threads, runs with the cache reproduce the saved
-        // samples but now and then end with level counters a few counts off from run to run (one run in four
-        // at 4096 lanes x 6000 steps), although every cached batch checks out bit for bit against an uncached
-        // context (KIMA_CUDA_GP_CACHE_VERIFY=1) and one-host-thread runs are identical; not understood yet
-        // (DESIGN.md section 7).
+        // On unless KIMA_CUDA_GP_CACHE=0, as on the device-proposal path.
         const char* e = std::getenv("KIMA_CUDA_GP_CACHE");
-        cache_slots_[g] = (e && std::atoi(e) == 1) ? ctx_[g]->gp_cache_enable(n_particles) : 0;
+        cache_slots_[g] = (e && std::atoi(e) == 0) ? 0 : ctx_[g]->gp_cache_enable(n_particles);
         if (cache_slots_[g] > 0) slot_of_lane_[g].assign((size_t)ctx_[g]->max_batch(), -1);
     }
     void stage_slot(int g, int lane, int particle)
@@ -288,6 +338,13 @@ public:
     void wait(int g)
     {
         ctx_[g]->wait();
+        if (trace_ && pending_B_[g] > 0) {
+            // developer trace (KIMA_TRACE_HASH=file): one line per batch, hashes of what went in and what came back
+            uint64_t h = 1469598103934665603ull;
+            trace_mix(h, pending_out_[g], sizeof(double) * (size_t)pending_B_[g]);
+            std::fprintf(trace_, "%llu %d %d %016llx %016llx\n", (unsigned long long)trace_seq_++, g, pending_B_[g],
+                         (unsigned long long)trace_in_[g], (unsigned long long)h);
+        }
         if (verify_cache_ && cache_slots_[g] > 0 && pending_B_[g] > 0) {
             // KIMA_CUDA_GP_CACHE_VERIFY=1: the same staged batch once more without the cache, compared bit for bit
             // on a context of its own: nothing is added to the stream of the context under test
@@ -383,6 +440,7 @@ public:
 
 private:
     std::shared_ptr<kima_b200::LanePool> host_pool_;
+    std::vector<std::shared_ptr<DNest4::ContinuousDistribution>> lane_Pprior_, lane_Kprior_;
     void for_range(size_t n, const std::function<void(size_t, size_t)>& f)
     {
         if (host_pool_ && n >= 1024)
@@ -439,6 +497,29 @@ private:
     std::unique_ptr<kimacuda::Context> ctx_[GROUPS];
     int cache_slots_[GROUPS] = {0, 0};               // active factor-cache slots per group
     std::unique_ptr<kimacuda::Context> verify_ctx_;
+    // developer trace of every batch (KIMA_TRACE_HASH=file)
+    FILE* trace_ = std::getenv("KIMA_TRACE_HASH") ? std::fopen(std::getenv("KIMA_TRACE_HASH"), "w") : nullptr;
+    uint64_t trace_seq_ = 0, trace_in_[GROUPS] = {0, 0};
+    static void trace_mix(uint64_t& h, const void* p, size_t n)
+    {
+        const unsigned char* b = static_cast<const unsigned char*>(p);
+        size_t i = 0;
+        for (; i + 8 <= n; i += 8) {
+            uint64_t w;
+            std::memcpy(&w, b + i, 8);
+            h = (h ^ w) * 1099511628211ull;
+            h ^= h >> 29;
+        }
+        for (; i < n; i++) h = (h ^ b[i]) * 1099511628211ull;
+    }
+    uint64_t trace_hash_batch(int g, int B)
+    {
+        uint64_t h = 1469598103934665603ull;
+        const size_t n_rows = (size_t)ctx_[g]->layout().n_rows, ld = (size_t)ctx_[g]->ld();
+        for (size_t r = 0; r < n_rows; r++) trace_mix(h, ctx_[g]->params() + r * ld, sizeof(double) * (size_t)B);
+        trace_mix(h, ctx_[g]->np(), sizeof(int32_t) * (size_t)B);
+        return h;
+    }
     int pending_B_[GROUPS] = {0, 0};
     double* pending_out_[GROUPS] = {nullptr, nullptr};
     bool verify_cache_ = std::getenv("KIMA_CUDA_GP_CACHE_VERIFY") && std::atoi(std::getenv("KIMA_CUDA_GP_CACHE_VERIFY")) != 0;

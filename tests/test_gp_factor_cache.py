@@ -173,11 +173,28 @@ def test_cache_is_inactive_where_it_does_not_apply(gpu):
 
 def test_device_proposal_chains_do_not_depend_on_the_cache(gpu, tmp_path):
     """examples/CoRoT7 (GP, hyperpriors) with device-side proposals: kc_sampler_create attaches one slot per
-    particle; with and without it the run writes the same files, byte for byte.  (Host proposals: the cache
-    is opt-in there, host/RVmodelDevice.h::enable_factor_cache.)"""
+    particle; with and without it the run writes the same files, byte for byte."""
     from test_device_proposals import run
     opts = "2\n500\n200\n50\n0\n10\n100\n400\n"   # 2 particles x 64 lanes, 50 thread steps, 400 saves
     off = run("gpu", "CoRoT7", tmp_path, "off", 64, 43, True, opts, {"KIMA_CUDA_GP_CACHE": "0"})
     on = run("gpu", "CoRoT7", tmp_path, "on", 64, 43, True, opts, {"KIMA_CUDA_GP_CACHE": "1"})
     for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
         assert (off / f).read_bytes() == (on / f).read_bytes(), f
+
+
+def test_host_proposal_chains_do_not_depend_on_the_cache_or_on_the_host_threads(gpu, tmp_path):
+    """examples/CoRoT7 with host proposals (the lock-step sampler, two lane groups, one factor-cache slot per
+    particle of each group): the same files with and without the cache, and with 1 or 16 host threads.
+
+    The thread count mattered once: with hyperpriors the reference re-parameterises SHARED prior objects before
+    every use (src/RVConditionalPrior.cpp:111-112, 135-136, 150-151), which races between threads that perturb
+    descendants of one particle; host/RVmodelDevice.h::own_lane_priors gives every lane objects of its own.
+    512 lanes x 2 particles, enough steps for kill_lagging_particles to have spread copies over the lanes."""
+    opts = "2\n20000\n51200\n100\n0\n10\n100\n40\n"   # 2 particles per lane; a save (and a bookkeeping round) per 100 steps of every lane, 40 of them
+    base = run("gpu", "CoRoT7", tmp_path, "off", 512, 43, False, opts, {"KIMA_CUDA_GP_CACHE": "0", "KIMA_HOST_THREADS": "16"})
+    for tag, env in (("on", {"KIMA_CUDA_GP_CACHE": "1", "KIMA_HOST_THREADS": "16"}),
+                     ("on_again", {"KIMA_CUDA_GP_CACHE": "1", "KIMA_HOST_THREADS": "16"}),
+                     ("serial", {"KIMA_CUDA_GP_CACHE": "1", "KIMA_HOST_THREADS": "1"})):
+        d = run("gpu", "CoRoT7", tmp_path, tag, 512, 43, False, opts, env)
+        for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
+            assert (base / f).read_bytes() == (d / f).read_bytes(), (tag, f)

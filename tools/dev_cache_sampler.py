@@ -19,6 +19,9 @@ def one(name, threads, ts, saves, env):
     r = subprocess.run([exe, "-t", str(threads), "-s", "43"], cwd=d, capture_output=True, text=True, timeout=900, env=e)
     if r.returncode != 0:
         return d, {"error": r.stderr[-800:]}
+    for ln in r.stderr.split("\n"):
+        if "MISMATCH" in ln:
+            print(ln[:300], flush=True)
     steps = int(open(os.path.join(d, "sampler_state.txt")).read().split()[-1])
     run_s = sb._run_seconds(r.stderr)
     return d, {"steps": steps, "run_s": run_s, "steps_per_s_run": steps / run_s if run_s else None}

@@ -1,0 +1,3 @@
+#!/bin/bash
+OUT=gpurun_out/r02c26; mkdir -p $OUT
+echo "== verify stage"; KIMA_VERIFY_STAGE=1 KIMA_HOST_THREADS=16 timeout 1500 python tools/dev_host_repro.py CoRoT7 4096 60 26 0 2>&1 | cut -c1-400 | tee $OUT/trace.txt
