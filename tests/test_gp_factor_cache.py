@@ -190,6 +190,7 @@ def test_host_proposal_chains_do_not_depend_on_the_cache_or_on_the_host_threads(
     every use (src/RVConditionalPrior.cpp:111-112, 135-136, 150-151), which races between threads that perturb
     descendants of one particle; host/RVmodelDevice.h::own_lane_priors gives every lane objects of its own.
     512 lanes x 2 particles, enough steps for kill_lagging_particles to have spread copies over the lanes."""
+    from test_device_proposals import run
     opts = "2\n20000\n51200\n100\n0\n10\n100\n40\n"   # 2 particles per lane; a save (and a bookkeeping round) per 100 steps of every lane, 40 of them
     base = run("gpu", "CoRoT7", tmp_path, "off", 512, 43, False, opts, {"KIMA_CUDA_GP_CACHE": "0", "KIMA_HOST_THREADS": "16"})
     for tag, env in (("on", {"KIMA_CUDA_GP_CACHE": "1", "KIMA_HOST_THREADS": "16"}),
