@@ -199,3 +199,26 @@ def test_host_proposal_chains_do_not_depend_on_the_cache_or_on_the_host_threads(
         d = run("gpu", "CoRoT7", tmp_path, tag, 512, 43, False, opts, env)
         for f in ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt"):
             assert (base / f).read_bytes() == (d / f).read_bytes(), (tag, f)
+
+
+def test_cache_with_chunked_uploads(gpu):
+    """kc_eval uploads large batches in chunks that overlap the kernels (option eval_chunk): every chunk is a
+    launch sequence of its own over its part of the slots, sharing the classification scratch."""
+    N, B = 100, 200
+    flags = ModelFlags(GP=True, npmax=3)
+    data = make_data(N)
+    P, nps = make_params(flags, data, B, "mix", seed=9)
+    rng = np.random.default_rng(10)
+    with LikelihoodEngine(data, flags, B) as eng:
+        eng.set_option("eval_chunk", 64)                     # 200 lanes: chunks of 64, 64, 64, 8
+        L = eng.layout
+        assert eng.enable_gp_cache(B) == B
+        slots = rng.permutation(B).astype(np.int32)          # slots need not follow the lane order
+        ref = _no_cache(data, flags, P, nps)
+        for _ in range(2):                                   # misses, then hits
+            eng.set_slots(slots)
+            assert np.array_equal(eng.evaluate(P, nps), ref)
+        Q = _move_planets(P, L, rng)
+        Q[L["row_eta"] + 2, ::3] *= 1.02                     # a third of the lanes miss
+        eng.set_slots(slots)
+        assert np.array_equal(eng.evaluate(Q, nps), _no_cache(data, flags, Q, nps))
