@@ -414,6 +414,23 @@ class BatchedSampler : public Sampler<ModelType> {
         col.assign(mine.begin(), mine.begin() + S);
     }
 
+    // Engine outputs one rngs[0].rand() consumes (1 with mt19937_64, DNest4/code/RNG.h:17-20), found by trying:
+    // 0 = not a fixed number this code recognises, the caller keeps the serial loop.
+    int engine_outputs_per_rand()
+    {
+        static int k = -1;
+        if (k >= 0) return k;
+        DNest4::RNG probe = this->rngs[0];
+        auto stepped = probe.twister;
+        probe.rand();
+        k = 0;
+        for (int t = 1; t <= 2 && k == 0; ++t) {
+            stepped.discard(1);
+            if (stepped == probe.twister) k = t;
+        }
+        return k;
+    }
+
     // kill_lagging_particles (SamplerImpl.h:534-587) with the copies done in HBM: same draws from
     // rngs[0], same messages; a replacement taken from another rank's lane travels as one column
     void kill_lagging_device()
@@ -431,12 +448,66 @@ class BatchedSampler : public Sampler<ModelType> {
             push[j] = this->log_push((unsigned int)j);
             kill[j] = pow(1.0 - 1.0 / (1.0 + exp(-push[j] - 4.0)), 3);
         }
-        for (size_t i = 0; i < n; ++i) {
-            const unsigned int lv = this->level_assignments[i];
-            if (push[lv] > max_log_push) max_log_push = push[lv];
-            if (this->rngs[0].rand() <= kill[lv]) {
-                good[i] = false;
-                ++num_bad;
+        const int per_draw = world() > 1 ? engine_outputs_per_rand() : 0;
+        if (per_draw > 0) {
+            // Several ranks: the first loop is one draw per particle in particle order (:543-558), i.e. a fixed
+            // number of engine outputs per particle, so each rank draws for the particles it owns and steps the
+            // (replicated) engine over the others' -- mt19937_64::discard skips the tempering and the
+            // conversion, a tenth of a draw.  Same good[] and the same engine state afterwards as the serial
+            // loop; with millions of particles that loop was most of the replicated bookkeeping.
+            const size_t a = part_lo(), b = part_hi();
+            auto& tw = this->rngs[0].twister;
+            const auto check_engine = tw;  // KIMA_CHECK_SHARDED_KILL: the serial loop on a copy, below
+            tw.discard((unsigned long long)per_draw * a);
+            std::vector<uint32_t> bad;
+            double mx = max_log_push;
+            for (size_t i = a; i < b; ++i) {
+                const unsigned int lv = this->level_assignments[i];
+                if (push[lv] > mx) mx = push[lv];
+                if (this->rngs[0].rand() <= kill[lv]) bad.push_back((uint32_t)i);
+            }
+            tw.discard((unsigned long long)per_draw * (n - b));
+            struct Head { double mx; uint64_t cnt; } mine{mx, (uint64_t)bad.size()};
+            std::vector<Head> heads((size_t)world());
+            evaluator->allgather_bytes(&mine, sizeof(Head), heads.data());
+            size_t most = 0;
+            for (const Head& h : heads) {
+                if (h.mx > max_log_push) max_log_push = h.mx;
+                num_bad += (unsigned int)h.cnt;
+                most = std::max(most, (size_t)h.cnt);
+            }
+            if (most > 0) {
+                std::vector<uint32_t> send(most, 0u), recv(most * (size_t)world());
+                std::copy(bad.begin(), bad.end(), send.begin());
+                evaluator->allgather_bytes(send.data(), sizeof(uint32_t) * most, recv.data());
+                for (int r = 0; r < world(); ++r)
+                    for (uint64_t q = 0; q < heads[(size_t)r].cnt; ++q) good[recv[(size_t)r * most + q]] = false;
+            }
+            static const bool check = std::getenv("KIMA_CHECK_SHARDED_KILL") != nullptr;
+            if (check) {
+                // developer check: the reference's loop on a copy of the engine
+                DNest4::RNG serial = this->rngs[0];
+                serial.twister = check_engine;
+                std::vector<bool> good_serial(n, true);
+                double mx_serial = -std::numeric_limits<double>::max();
+                for (size_t i = 0; i < n; ++i) {
+                    const unsigned int lv = this->level_assignments[i];
+                    if (push[lv] > mx_serial) mx_serial = push[lv];
+                    if (serial.rand() <= kill[lv]) good_serial[i] = false;
+                }
+                if (good_serial != good || mx_serial != max_log_push || !(serial.twister == tw)) {
+                    std::cerr << "# SHARDED KILL MISMATCH on rank " << rank() << std::endl;
+                    std::abort();
+                }
+            }
+        } else {
+            for (size_t i = 0; i < n; ++i) {
+                const unsigned int lv = this->level_assignments[i];
+                if (push[lv] > max_log_push) max_log_push = push[lv];
+                if (this->rngs[0].rand() <= kill[lv]) {
+                    good[i] = false;
+                    ++num_bad;
+                }
             }
         }
         if (num_bad >= n) return;
@@ -581,8 +652,21 @@ class BatchedSampler : public Sampler<ModelType> {
         book_prof[2] += now() - tv;
         // record holder (:433-439)
         size_t best = 0;
-        for (size_t i = 1; i < this->log_likelihoods.size(); ++i)
-            if (this->log_likelihoods[best] < this->log_likelihoods[i]) best = i;
+        if (world() > 1) {
+            // each rank searches the particles it owns; the first maximum in particle order, as the serial loop
+            size_t mine = part_lo();
+            for (size_t i = part_lo() + 1; i < part_hi(); ++i)
+                if (this->log_likelihoods[mine] < this->log_likelihoods[i]) mine = i;
+            const uint64_t send = (uint64_t)mine;
+            std::vector<uint64_t> all((size_t)world());
+            evaluator->allgather_bytes(&send, sizeof(uint64_t), all.data());
+            best = (size_t)all[0];
+            for (int r = 1; r < world(); ++r)
+                if (this->log_likelihoods[best] < this->log_likelihoods[(size_t)all[(size_t)r]]) best = (size_t)all[(size_t)r];
+        } else {
+            for (size_t i = 1; i < this->log_likelihoods.size(); ++i)
+                if (this->log_likelihoods[best] < this->log_likelihoods[i]) best = i;
+        }
         if (this->best_ever_log_likelihood < this->log_likelihoods[best]) {
             std::vector<double> col;
             int32_t np = 0;
