@@ -437,6 +437,7 @@ class BatchedSampler : public Sampler<ModelType> {
     {
         const size_t n = this->particles.size();
         std::vector<bool> good(n, true);
+        std::vector<uint32_t> lagging;  // several ranks: the indices in particle order, so that nobody scans good[]
         double max_log_push = -std::numeric_limits<double>::max();
         unsigned int num_bad = 0;
         // log_push and the kill probability depend on the level alone: one evaluation per level instead of
@@ -480,8 +481,11 @@ class BatchedSampler : public Sampler<ModelType> {
                 std::vector<uint32_t> send(most, 0u), recv(most * (size_t)world());
                 std::copy(bad.begin(), bad.end(), send.begin());
                 evaluator->allgather_bytes(send.data(), sizeof(uint32_t) * most, recv.data());
-                for (int r = 0; r < world(); ++r)
-                    for (uint64_t q = 0; q < heads[(size_t)r].cnt; ++q) good[recv[(size_t)r * most + q]] = false;
+                for (int r = 0; r < world(); ++r)  // rank order is particle order
+                    for (uint64_t q = 0; q < heads[(size_t)r].cnt; ++q) {
+                        good[recv[(size_t)r * most + q]] = false;
+                        lagging.push_back(recv[(size_t)r * most + q]);
+                    }
             }
             static const bool check = std::getenv("KIMA_CHECK_SHARDED_KILL") != nullptr;
             if (check) {
@@ -515,8 +519,10 @@ class BatchedSampler : public Sampler<ModelType> {
         for (size_t j = 0; j < L; ++j) keep[j] = exp(push[j] - max_log_push);
         std::vector<size_t> dst, src;
         std::ostringstream msg;
-        for (size_t i = 0; i < n; ++i) {
-            if (good[i]) continue;
+        if (per_draw <= 0)
+            for (size_t i = 0; i < n; ++i)
+                if (!good[i]) lagging.push_back((uint32_t)i);
+        for (const uint32_t i : lagging) {
             int i_copy;
             do {
                 i_copy = this->rngs[0].rand_int((int)n);
@@ -765,11 +771,6 @@ class BatchedSampler : public Sampler<ModelType> {
                     xs[3 * i + 2] = (double)level[p0 + i];
                 }
                 evaluator->allgather_bytes(xs.data(), sizeof(double) * 3 * nl, xr.data());
-                for (size_t i = 0; i < n; ++i) {
-                    logl[i] = xr[3 * i];
-                    tb[i] = xr[3 * i + 1];
-                    level[i] = (int32_t)xr[3 * i + 2];
-                }
             }
             const double t1 = now();
             t_dev += tc - t0;
@@ -792,12 +793,20 @@ class BatchedSampler : public Sampler<ModelType> {
                     for (int i = a; i < b; ++i) dst[i] = LikelihoodType(above[2 * (size_t)i], above[2 * (size_t)i + 1]);
                 });
             }
-            pool->run(0, (int)n, [&](int a, int b) {
-                for (int i = a; i < b; ++i) {
-                    this->log_likelihoods[i] = LikelihoodType(logl[i], tb[i]);
-                    this->level_assignments[i] = (unsigned int)level[i];
-                }
-            });
+            if (W > 1)  // everybody's triples, straight from the exchange buffer
+                pool->run(0, (int)n, [&](int a, int b) {
+                    for (int i = a; i < b; ++i) {
+                        this->log_likelihoods[i] = LikelihoodType(xr[3 * (size_t)i], xr[3 * (size_t)i + 1]);
+                        this->level_assignments[i] = (unsigned int)xr[3 * (size_t)i + 2];
+                    }
+                });
+            else
+                pool->run(0, (int)n, [&](int a, int b) {
+                    for (int i = a; i < b; ++i) {
+                        this->log_likelihoods[i] = LikelihoodType(logl[i], tb[i]);
+                        this->level_assignments[i] = (unsigned int)level[i];
+                    }
+                });
             const double t2 = now();
             t_fold += t2 - t1;
             bookkeeping_device();
