@@ -24,6 +24,9 @@
 //     void strip(ModelType&);   (drop per-particle host state only the CPU likelihood needs)
 //     void slim_host_data();    (after initialise: drop host copies of the data the sampler no longer reads)
 //     void stage(int g, int slot, const ModelType&);  void submit(int g, int B, double* logL);  void wait(int g);
+//     typedef std::true_type / std::false_type has_device_sampler;   (the sampler_* members run_device() uses)
+// tests/cpp/RefEvaluator.h is a second instance: the reference's own log_likelihood() on the host cores, so
+// that the lock-step sampler itself is tested on a machine without a GPU.
 //
 // This header must be included after Sampler.h has been included with its private section
 // opened (host/overlay/kima.h does that).
@@ -40,6 +43,7 @@
 #include <stdexcept>
 #include <string>
 #include <thread>
+#include <type_traits>
 #include <vector>
 #include "LanePool.h"
 
@@ -683,6 +687,11 @@ class BatchedSampler : public Sampler<ModelType> {
         }
     }
 
+    // an evaluator without the device-side sampler (has_device_sampler = std::false_type: the CPU evaluator of
+    // tests/cpp/) never instantiates run_device() and what it calls
+    bool run_device_if(std::true_type) { return run_device(); }
+    bool run_device_if(std::false_type) { return false; }
+
     // false = the model has a prior without a device counterpart: the caller runs host proposals
     bool run_device()
     {
@@ -910,7 +919,7 @@ public:
         this->thin_print = thin;
         const double t_run0 = now();
         ensure_evaluator();
-        if (device_proposals_requested() && run_device()) {
+        if (device_proposals_requested() && run_device_if(typename Evaluator::has_device_sampler())) {
             if (std::getenv("KIMA_PROFILE")) std::cerr << "# run() " << now() - t_run0 << " s (device proposals)" << std::endl;
             return;
         }

@@ -21,9 +21,11 @@
 #include <thread>
 #include <iostream>
 #include <limits>
+#include <type_traits>
 #include <vector>
 #include "kima_cuda.hpp"
 #include "LanePool.h"
+#include "LanePriors.h"
 #include "PriorTable.h"
 
 // the nine model flags every kima_setup.cpp defines (src/RVmodel.h:16-34)
@@ -39,6 +41,8 @@ public:
     // Two contexts on the same GPU (own stream, own pinned staging block each): while one
     // group of lanes is being scored, the host perturbs the other (BatchedSampler.h).
     static constexpr int GROUPS = 2;
+    // BatchedSampler::run(): this evaluator can also run the proposals on the GPU (include/kima_sampler.h)
+    typedef std::true_type has_device_sampler;
 
     explicit RVmodelEvaluator(int max_batch)
     {
@@ -169,33 +173,9 @@ public:
         }
     }
 
-    // ---- hyperpriors: one pair of planet-prior objects per lane -------------------------------
-    // With hyperpriors the reference re-parameterises the period and amplitude priors before every use
-    // (Pprior->setpars(center, width); Kprior->setpars(muK): src/RVConditionalPrior.cpp:111-112, 135-136,
-    // 150-151) -- and those objects are shared: every copy of a particle (SamplerImpl.h:184, 208, and
-    // kill_lagging_particles' copies between threads, :487) aliases the shared_ptr of its source
-    // (RVConditionalPrior.h:30-32).  Two host threads that perturb descendants of one particle then race
-    // between one's setpars() and the other's cdf(): a period drawn with another particle's centre.  The
-    // reference's own -t threads have that race too; here it made one run in ten at 4096 lanes differ from
-    // the next.  Each lane therefore gets objects of its own (default-constructed as the reference's are,
-    // src/RVConditionalPrior.cpp:43-44; their state is overwritten by setpars before every read), and a
-    // proposal is pointed at its lane's pair before perturb() runs: the values are those of a serial run.
-    void reserve_lane_priors(size_t lanes)
-    {
-        if (!hyperpriors || lane_Pprior_.size() == lanes) return;
-        lane_Pprior_.resize(lanes);
-        lane_Kprior_.resize(lanes);
-        for (size_t k = 0; k < lanes; k++) {
-            lane_Pprior_[k] = std::make_shared<DNest4::Laplace>();
-            lane_Kprior_[k] = std::make_shared<DNest4::Exponential>();
-        }
-    }
-    void own_lane_priors(RVmodel& m, size_t lane) const
-    {
-        if (!hyperpriors || lane >= lane_Pprior_.size()) return;
-        m.planets.conditional_prior.Pprior = lane_Pprior_[lane];
-        m.planets.conditional_prior.Kprior = lane_Kprior_[lane];
-    }
+    // ---- hyperpriors: one pair of planet-prior objects per lane (host/LanePriors.h says why) ----
+    void reserve_lane_priors(size_t lanes) { lane_priors_.reserve(hyperpriors, lanes); }
+    void own_lane_priors(RVmodel& m, size_t lane) const { lane_priors_.own(m, lane); }
 
     int max_batch() const { return ctx_[0]->max_batch(); }
     int max_batch(int g) const { return ctx_[g]->max_batch(); }
@@ -440,7 +420,7 @@ public:
 
 private:
     std::shared_ptr<kima_b200::LanePool> host_pool_;
-    std::vector<std::shared_ptr<DNest4::ContinuousDistribution>> lane_Pprior_, lane_Kprior_;
+    LanePriors lane_priors_;
     void for_range(size_t n, const std::function<void(size_t, size_t)>& f)
     {
         if (host_pool_ && n >= 1024)

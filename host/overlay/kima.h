@@ -70,13 +70,19 @@ using ind = std::vector<char*>;
 std::vector<std::string> indicators;
 using namespace DNest4;
 
-#include "RVmodelDevice.h"
+// the evaluator behind the batched sampler: the GPU library, unless a test names another one
+// (tests/cpp/RefEvaluator.h: the reference's own log_likelihood(), to test the sampler without a GPU)
+#ifndef KIMA_B200_EVALUATOR_HEADER
+#define KIMA_B200_EVALUATOR_HEADER "RVmodelDevice.h"
+#define KIMA_B200_EVALUATOR RVmodelEvaluator
+#endif
+#include KIMA_B200_EVALUATOR_HEADER
 #include "BatchedSampler.h"
 
 namespace kima_b200 {
 
 template <class ModelType>
-using GpuSampler = DNest4::BatchedSampler<ModelType, RVmodelEvaluator>;
+using GpuSampler = DNest4::BatchedSampler<ModelType, KIMA_B200_EVALUATOR>;
 
 // DNest4::setup (StartImpl.h:12-40) for the batched sampler: same messages, same order
 template <class ModelType>

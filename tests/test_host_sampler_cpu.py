@@ -1,0 +1,117 @@
+"""CPU: the lock-step sampler itself (host/BatchedSampler.h, host/LanePool.h, host/LanePriors.h), without a GPU.
+
+tests/cpp/RefEvaluator.h is a test-only Evaluator that scores the staged particles with the reference's own
+RVmodel::log_likelihood(); built with it, the UNMODIFIED examples/*/kima_setup.cpp run through the batched
+sampler on the host cores and must write, byte for byte, the files of the reference's sampler
+(DNest4/code/SamplerImpl.h) started with the same -t and -s.  What this covers that the GPU tests cannot reach
+on this machine: update_particle split around the likelihood call, the two lane groups, lanes on pool threads,
+the level bookkeeping, and the per-lane hyperprior objects.  Needs /root/reference (build container only)."""
+import os
+import shutil
+import subprocess
+from concurrent.futures import ThreadPoolExecutor
+
+import pytest
+
+from conftest import ROOT
+
+REF = "/root/reference"
+OBJ = os.path.join(ROOT, "oracle", "_ref", "obj")
+HOST_BUILD = os.path.join(ROOT, "host", "_build")
+OUT = os.path.join(ROOT, "tests", "cpp", "_build")
+E2E = os.path.join(ROOT, "tests", "golden", "e2e")
+DATA = {"BL2009": ["BL2009_dataset2.kms.rv"], "CoRoT7": ["corot7.txt"], "many_planets": ["HD10180.kms.rv"]}
+FILES = ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt")
+CI_OPTIONS = "2\n50\n10\n5\n0\n10\n100\n100\n"   # the reference's CI options (tests/golden/e2e/OPTIONS)
+INC = ["-I" + os.path.join(REF, d) for d in ("src", "DNest4/code", "eigen", "celerite/cpp/include")]
+SKIP_OBJS = ("ref_harness.o", "ref_flags.o", "philox_rng.o", "ref_sampler_harness.o")
+
+
+def _ref_objs():
+    return sorted(os.path.join(OBJ, f) for f in os.listdir(OBJ) if f.endswith(".o") and f not in SKIP_OBJS)
+
+
+def _compile(args):
+    r = subprocess.run(args, capture_output=True, text=True)
+    assert r.returncode == 0, " ".join(args[:6]) + " ...\n" + r.stderr[-3000:]
+
+
+@pytest.fixture(scope="module")
+def built():
+    cxx = shutil.which("g++")
+    if not cxx or not os.path.isdir(REF) or not os.path.isdir(OBJ):
+        pytest.skip("needs g++, /root/reference and the reference objects (oracle/Makefile)")
+    for n in DATA:
+        if not os.path.exists(os.path.join(HOST_BUILD, "kima_cpu_%s" % n)):
+            pytest.skip("host/_build/kima_cpu_%s is missing (make -C host)" % n)
+    os.makedirs(OUT, exist_ok=True)
+    flags = [cxx, "-pthread", "-std=c++11", "-w", "-DEIGEN_MPL2_ONLY"]
+    jobs = [flags + ["-O1", "-I" + os.path.join(ROOT, "host")] + INC +
+            ["-o", os.path.join(OUT, "lane_priors_check"), os.path.join(ROOT, "tests", "cpp", "lane_priors_check.cpp")] +
+            _ref_objs()]
+    for n in DATA:
+        # host/overlay FIRST: its kima.h stands in for the reference's src/kima.h (as in host/Makefile)
+        jobs.append(flags + ["-O2", "-DNDEBUG", '-DKIMA_B200_EVALUATOR_HEADER="RefEvaluator.h"',
+                             "-DKIMA_B200_EVALUATOR=RefEvaluator", "-I" + os.path.join(ROOT, "host", "overlay"),
+                             "-I" + os.path.join(ROOT, "tests", "cpp"), "-I" + os.path.join(ROOT, "host"),
+                             "-I" + os.path.join(ROOT, "include")] + INC +
+                            ["-o", os.path.join(OUT, "kima_batched_cpu_%s" % n),
+                             os.path.join(REF, "examples", n, "kima_setup.cpp")] + _ref_objs())
+    with ThreadPoolExecutor(4) as ex:
+        list(ex.map(_compile, jobs))
+    return OUT
+
+
+def _run(exe, name, d, lanes, options, env=None, seed=43):
+    d.mkdir()
+    for f in DATA[name]:
+        shutil.copy(os.path.join(E2E, f), d)
+    (d / "OPTIONS").write_text(options)
+    r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, capture_output=True, text=True, timeout=900,
+                       env=dict(os.environ, **(env or {})))
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    return d
+
+
+def test_the_binary_under_test_is_the_batched_sampler(built, tmp_path):
+    d = tmp_path / "probe"
+    d.mkdir()
+    shutil.copy(os.path.join(E2E, DATA["BL2009"][0]), d)
+    (d / "OPTIONS").write_text(CI_OPTIONS)
+    r = subprocess.run([os.path.join(built, "kima_batched_cpu_BL2009"), "-t", "4", "-s", "43"], cwd=d, capture_output=True,
+                       text=True, timeout=300, env=dict(os.environ, KIMA_PROFILE="1", KIMA_HOST_THREADS="2"))
+    assert r.returncode == 0 and "# host threads 2" in r.stderr, r.stderr[-1500:]   # BatchedSampler::run's profile line
+
+
+def _same(a, b, tag):
+    for f in FILES:
+        assert (a / f).read_bytes() == (b / f).read_bytes(), (tag, f)
+
+
+def test_lane_priors_against_the_reference_classes(built):
+    r = subprocess.run([os.path.join(built, "lane_priors_check"), os.path.join(E2E, "BL2009_dataset2.kms.rv")],
+                       capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("name", sorted(DATA))
+def test_batched_sampler_writes_the_reference_chain(built, tmp_path, name):
+    """-t 4 -s 43: 4 lanes in two groups, every step's proposals scored in one call per group."""
+    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 4, CI_OPTIONS)
+    bat = _run(os.path.join(built, "kima_batched_cpu_%s" % name), name, tmp_path / "bat", 4, CI_OPTIONS,
+               {"KIMA_HOST_THREADS": "2"})
+    _same(ref, bat, name)
+
+
+def test_lanes_on_pool_threads_write_the_reference_chain(built, tmp_path):
+    """32 lanes on 4 pool threads (the pool only splits ranges of at least two lanes per thread), hyperpriors
+    and up to 10 planets, enough steps for levels to be created and lagging particles replaced across lanes."""
+    name = "many_planets"
+    opts = "2\n2000\n1600\n50\n0\n10\n100\n60\n"
+    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 32, opts)
+    bat = _run(os.path.join(built, "kima_batched_cpu_%s" % name), name, tmp_path / "bat", 32, opts,
+               {"KIMA_HOST_THREADS": "4"})
+    _same(ref, bat, "32 lanes")
+    one = _run(os.path.join(built, "kima_batched_cpu_%s" % name), name, tmp_path / "one", 32, opts,
+               {"KIMA_HOST_THREADS": "1"})
+    _same(bat, one, "1 thread against 4")
