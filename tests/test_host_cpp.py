@@ -58,8 +58,12 @@ def run_example(kind, name, tmp_path, lanes=4, seed=43):
     for f in (CASES[name][0] if name in CASES else OWN_SETUPS[name]) + ["OPTIONS"]:
         src, dst = f if isinstance(f, tuple) else (f, f)
         shutil.copy(os.path.join(E2E, src), d / dst)
-    r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, capture_output=True,
-                       text=True, timeout=600)
+    cmd = [exe, "-t", str(lanes), "-s", str(seed)]
+    if kind == "cpu" and shutil.which("taskset"):
+        # the reference on ONE core: with hyperpriors its threads race on shared prior objects (host/LanePriors.h,
+        # tests/test_host_sampler_cpu.py); pinned, they never run at the same time and the chain is the serial one
+        cmd = ["taskset", "-c", str(sorted(os.sched_getaffinity(0))[0])] + cmd
+    r = subprocess.run(cmd, cwd=d, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     return d
 

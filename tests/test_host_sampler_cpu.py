@@ -62,12 +62,19 @@ def built():
     return OUT
 
 
-def _run(exe, name, d, lanes, options, env=None, seed=43):
+def _run(exe, name, d, lanes, options, env=None, seed=43, one_core=False):
+    """one_core: pin the process to one core.  The REFERENCE needs that to be reproducible with hyperpriors: its
+    threads share the prior objects the hyperprior code re-parameterises before every use (host/LanePriors.h), and
+    on several cores examples/CoRoT7 -t 8 writes a different chain every time (profiles/host_repro_r02.txt).  On
+    one core its threads never run at the same time and the chain is the serial one."""
     d.mkdir()
     for f in DATA[name]:
         shutil.copy(os.path.join(E2E, f), d)
     (d / "OPTIONS").write_text(options)
-    r = subprocess.run([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, capture_output=True, text=True, timeout=900,
+    cmd = [exe, "-t", str(lanes), "-s", str(seed)]
+    if one_core and shutil.which("taskset"):
+        cmd = ["taskset", "-c", str(sorted(os.sched_getaffinity(0))[0])] + cmd
+    r = subprocess.run(cmd, cwd=d, capture_output=True, text=True, timeout=900,
                        env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
     return d
@@ -97,7 +104,7 @@ def test_lane_priors_against_the_reference_classes(built):
 @pytest.mark.parametrize("name", sorted(DATA))
 def test_batched_sampler_writes_the_reference_chain(built, tmp_path, name):
     """-t 4 -s 43: 4 lanes in two groups, every step's proposals scored in one call per group."""
-    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 4, CI_OPTIONS)
+    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 4, CI_OPTIONS, one_core=True)
     bat = _run(os.path.join(built, "kima_batched_cpu_%s" % name), name, tmp_path / "bat", 4, CI_OPTIONS,
                {"KIMA_HOST_THREADS": "2"})
     _same(ref, bat, name)
@@ -108,10 +115,64 @@ def test_lanes_on_pool_threads_write_the_reference_chain(built, tmp_path):
     and up to 10 planets, enough steps for levels to be created and lagging particles replaced across lanes."""
     name = "many_planets"
     opts = "2\n2000\n1600\n50\n0\n10\n100\n60\n"
-    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 32, opts)
+    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 32, opts, one_core=True)
     bat = _run(os.path.join(built, "kima_batched_cpu_%s" % name), name, tmp_path / "bat", 32, opts,
                {"KIMA_HOST_THREADS": "4"})
     _same(ref, bat, "32 lanes")
     one = _run(os.path.join(built, "kima_batched_cpu_%s" % name), name, tmp_path / "one", 32, opts,
                {"KIMA_HOST_THREADS": "1"})
     _same(bat, one, "1 thread against 4")
+
+
+def _run_ranks(exe, name, d, world, lanes, options, port, seed=43):
+    """`world` processes in ONE run directory, as a torchrun-style launcher starts the GPU ranks
+    (RANK / WORLD_SIZE / MASTER_PORT); tests/cpp/RefEvaluator.h carries the collectives over TCP on 127.0.0.1."""
+    d.mkdir()
+    for f in DATA[name]:
+        shutil.copy(os.path.join(E2E, f), d)
+    (d / "OPTIONS").write_text(options)
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_PORT=str(port), KIMA_HOST_THREADS="2")
+        procs.append(subprocess.Popen([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=600) for p in procs]
+    for p, (so, se) in zip(procs, outs):
+        assert p.returncode == 0, so[-1500:] + se[-1500:]
+    return d, outs[0][0]
+
+
+@pytest.mark.parametrize("name,world,port", [("BL2009", 2, 29621), ("BL2009", 4, 29622), ("CoRoT7", 2, 29623)])
+def test_ranks_write_the_single_process_chain(built, tmp_path, name, world, port):
+    """One process per rank, lanes sharded, BatchedSampler::exchange at every barrier (particles of the owners'
+    lanes, likelihoods, level assignments and rank 0's bookkeeping RNG to everybody; `above` lists concatenated in
+    lane order; level counters summed): `world` ranks write the files of one process with the same -t, which are
+    the reference sampler's.  The multi-GPU runs use exactly this code with NCCL underneath
+    (tests/test_host_cpp.py::test_two_ranks_reproduce_the_single_process_chain, on 2 GPUs)."""
+    opts = "2\n50\n10\n5\n0\n1\n100\n300\n"   # lambda = 1: lagging particles get replaced early and often
+    exe = os.path.join(built, "kima_batched_cpu_%s" % name)
+    ref = _run(os.path.join(HOST_BUILD, "kima_cpu_%s" % name), name, tmp_path / "ref", 8, opts, one_core=True)
+    one = _run(exe, name, tmp_path / "one", 8, opts, {"KIMA_HOST_THREADS": "2"})
+    ranks, out0 = _run_ranks(exe, name, tmp_path / "ranks", world, 8, opts, port)
+    assert "Replacing lagging particle" in out0     # copies between lanes (and ranks) happened
+    _same(ref, one, "reference against one process")
+    _same(one, ranks, "%d ranks against one process" % world)
+
+
+def test_the_reference_itself_is_not_reproducible_with_hyperpriors_on_several_cores(built, tmp_path):
+    """Not a requirement on this repository: a record of why the comparisons above pin the reference to one core.
+    examples/CoRoT7 (hyperpriors) with -t 8 and frequent copies between threads: the batched sampler writes the
+    same files on 1 and on 3 host threads; the reference, free to use all cores, usually does not repeat itself."""
+    if len(os.sched_getaffinity(0)) < 4:
+        pytest.skip("needs several cores")
+    opts = "2\n50\n10\n5\n0\n1\n100\n300\n"
+    exe = os.path.join(built, "kima_batched_cpu_CoRoT7")
+    a = _run(exe, "CoRoT7", tmp_path / "b1", 8, opts, {"KIMA_HOST_THREADS": "1"})
+    b = _run(exe, "CoRoT7", tmp_path / "b3", 8, opts, {"KIMA_HOST_THREADS": "3"})
+    _same(a, b, "batched, 1 thread against 3")
+    refexe = os.path.join(HOST_BUILD, "kima_cpu_CoRoT7")
+    states = {_run(refexe, "CoRoT7", tmp_path / ("r%d" % i), 8, opts).joinpath("sampler_state.txt").read_bytes()
+              for i in range(4)}
+    if len(states) == 1:
+        pytest.skip("the reference repeated itself four times on this machine")
+    assert len(states) > 1
