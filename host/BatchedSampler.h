@@ -239,11 +239,13 @@ class BatchedSampler : public Sampler<ModelType> {
     // (particles, likelihoods, level assignments) go to everybody, rank 0's RNG 0 (the one
     // do_bookkeeping draws from) too; `above` lists are concatenated in lane order and the
     // level counters summed.
-    void exchange(const std::vector<Level>& before)
+    void exchange(const std::vector<Level>& before, const bool with_particles)
     {
         const int R = world();
         const unsigned int T = this->num_threads, P = this->options.num_particles;
-        const size_t S = evaluator->state_doubles(), per = S + 3;
+        // with_particles = false: likelihoods and level assignments only; particles then travel when the
+        // bookkeeping asks for one (bookkeeping_ranks below)
+        const size_t S = with_particles ? evaluator->state_doubles() : 0, per = S + 3;
         const unsigned int lanes_per_rank = T / R;
         constexpr size_t RNG_BYTES = 16384;
         const size_t blob = sizeof(double) * per * P * lanes_per_rank + RNG_BYTES;
@@ -258,7 +260,7 @@ class BatchedSampler : public Sampler<ModelType> {
                 for (unsigned int q = 0; q < P; ++q) {
                     const size_t i = (size_t)k * P + q;
                     double* o = sd + ((size_t)(k - my_lo) * P + q) * per;
-                    evaluator->pack(this->particles[i], o);
+                    if (with_particles) evaluator->pack(this->particles[i], o);
                     o[S] = this->log_likelihoods[i].get_value();
                     o[S + 1] = this->log_likelihoods[i].get_tiebreaker();
                     o[S + 2] = (double)this->level_assignments[i];
@@ -281,7 +283,7 @@ class BatchedSampler : public Sampler<ModelType> {
                     for (unsigned int q = 0; q < P; ++q) {
                         const size_t i = (size_t)(lo + k) * P + q;
                         const double* o = rd + ((size_t)k * P + q) * per;
-                        evaluator->unpack(this->particles[i], o);
+                        if (with_particles) evaluator->unpack(this->particles[i], o);
                         this->log_likelihoods[i] = LikelihoodType(o[S], o[S + 1]);
                         this->level_assignments[i] = (unsigned int)o[S + 2];
                     }
@@ -326,6 +328,168 @@ class BatchedSampler : public Sampler<ModelType> {
         size_t tot = 0;
         for (int c : counts) tot += (size_t)c;
         for (size_t i = 0; i < tot; ++i) this->all_above.push_back(LikelihoodType(all[2 * i], all[2 * i + 1]));
+    }
+
+    // ---- host proposals over several ranks: particles travel only when the bookkeeping asks for one ----
+    // Every rank keeps likelihoods, level assignments, levels and rngs[0] of the whole run (exchange above), but
+    // a particle itself only where its lane is stepped: the copies of another rank's particles go stale after
+    // initialise().  do_bookkeeping (SamplerImpl.h:377-440) reads particles in three places -- the sources of
+    // kill_lagging_particles' copies (:575), the saved particle (:512) and the record holder (:437) -- and those
+    // are fetched from their owners; the end-of-run state file gathers everything once.  All-gathering every
+    // particle at every barrier (KIMA_FULL_EXCHANGE=1 keeps that) was the largest part of the barrier.
+    unsigned int deletions_ranks = 0;
+    int owner_of_particle(size_t i) const
+    {
+        return (int)((i / this->options.num_particles) / (this->num_threads / (unsigned int)world()));
+    }
+    // particles `which[0..K)` from their owners into every rank's copy
+    void fetch_host_particles(const std::vector<size_t>& which)
+    {
+        if (which.empty()) return;
+        const size_t S = evaluator->state_doubles(), K = which.size();
+        std::vector<double> mine(S * K, 0.0), all(S * K * (size_t)world());
+        for (size_t q = 0; q < K; ++q)
+            if (owner_of_particle(which[q]) == rank()) evaluator->pack(this->particles[which[q]], mine.data() + q * S);
+        evaluator->allgather_bytes(mine.data(), sizeof(double) * S * K, all.data());
+        for (size_t q = 0; q < K; ++q) {
+            const int own = owner_of_particle(which[q]);
+            if (own != rank()) evaluator->unpack(this->particles[which[q]], all.data() + ((size_t)own * K + q) * S);
+        }
+    }
+    // kill_lagging_particles (SamplerImpl.h:534-587): same draws from rngs[0] on every rank, same messages
+    void kill_lagging_ranks()
+    {
+        const size_t n = this->particles.size();
+        std::vector<bool> good(n, true);
+        double max_log_push = -std::numeric_limits<double>::max();
+        unsigned int num_bad = 0;
+        for (size_t i = 0; i < n; ++i) {
+            const double push = this->log_push(this->level_assignments[i]);
+            if (push > max_log_push) max_log_push = push;
+            const double kill_probability = pow(1.0 - 1.0 / (1.0 + exp(-push - 4.0)), 3);
+            if (this->rngs[0].rand() <= kill_probability) {
+                good[i] = false;
+                ++num_bad;
+            }
+        }
+        if (num_bad >= n) return;
+        std::vector<size_t> dst, src;
+        for (size_t i = 0; i < n; ++i) {
+            if (good[i]) continue;
+            int i_copy;
+            do {
+                i_copy = this->rngs[0].rand_int((int)n);
+            } while (!good[i_copy] ||
+                     this->rngs[0].rand() >= exp(this->log_push(this->level_assignments[i_copy]) - max_log_push));
+            dst.push_back(i);
+            src.push_back((size_t)i_copy);
+            this->log_likelihoods[i] = this->log_likelihoods[i_copy];
+            this->level_assignments[i] = this->level_assignments[i_copy];
+            ++deletions_ranks;
+            if (rank() == 0)
+                std::cout << "# Replacing lagging particle. This has happened " << deletions_ranks << " times." << std::endl;
+        }
+        // sources are good particles and never overwritten: the copies are independent of their order.  A source
+        // on another rank than its destination travels first.
+        std::vector<size_t> remote;
+        for (size_t k = 0; k < dst.size(); ++k)
+            if (owner_of_particle(dst[k]) != owner_of_particle(src[k])) remote.push_back(src[k]);
+        fetch_host_particles(remote);
+        for (size_t k = 0; k < dst.size(); ++k)
+            if (owner_of_particle(dst[k]) == rank()) this->particles[dst[k]] = this->particles[src[k]];
+    }
+    // save_particle (SamplerImpl.h:503-531): every rank draws `which` (rngs[0] is replicated), rank 0 prints
+    void save_particle_ranks()
+    {
+        ++this->count_saves;
+        this->count_mcmc_steps_since_save = 0;
+        if (rank() == 0 && this->save_to_disk && this->count_saves % this->thin_print == 0)
+            std::cout << "# Saving particle to disk. N = " << this->count_saves << "." << std::endl;
+        const int which = this->rngs[0].rand_int((int)this->particles.size());
+        fetch_host_particles(std::vector<size_t>(1, (size_t)which));
+        if (!this->save_to_disk) return;
+        std::fstream fout;
+        fout.open(this->options.sample_file, std::ios::out | std::ios::app);
+        this->particles[which].print(fout);
+        fout << std::endl;
+        fout.close();
+        fout.open(this->options.sample_info_file, std::ios::out | std::ios::app);
+        fout << std::setprecision(12);
+        fout << this->level_assignments[which] << ' ';
+        fout << this->log_likelihoods[which].get_value() << ' ';
+        fout << this->log_likelihoods[which].get_tiebreaker() << ' ';
+        fout << which << std::endl;
+        fout.close();
+    }
+    // do_bookkeeping (SamplerImpl.h:377-440)
+    void bookkeeping_ranks()
+    {
+        bool created_level = false;
+        if (!this->enough_levels(this->levels) && (this->all_above.size() >= this->options.new_level_interval)) {
+            std::sort(this->all_above.begin(), this->all_above.end());
+            const int index = static_cast<int>((1. - 1. / this->compression) * this->all_above.size());
+            if (rank() == 0) {
+                std::cout << "# Creating level " << this->levels.size() << " with log likelihood = ";
+                std::cout << std::setprecision(12);
+                std::cout << this->all_above[index].get_value() << "." << std::endl;
+            }
+            this->levels.push_back(Level(this->all_above[index]));
+            this->all_above.erase(this->all_above.begin(), this->all_above.begin() + index + 1);
+            for (auto& a : this->above) a.clear();
+            if (this->enough_levels(this->levels)) {
+                const double reg = this->options.new_level_interval * sqrt(this->options.lambda);
+                Level::renormalise_visits(this->levels, static_cast<int>(reg));
+                this->all_above.clear();
+                this->options.max_num_levels = this->levels.size();
+                if (rank() == 0) std::cout << "# Done creating levels." << std::endl;
+            } else {
+                kill_lagging_ranks();
+            }
+            created_level = true;
+        }
+        Level::recalculate_log_X(this->levels, this->compression,
+                                 this->options.new_level_interval * sqrt(this->options.lambda));
+        if (created_level) this->save_levels();
+        if (this->count_mcmc_steps_since_save >= this->options.save_interval) {
+            save_particle_ranks();
+            if (!created_level) this->save_levels();
+        }
+        // record holder (:433-439): the largest likelihood; its particle comes from its owner
+        size_t best = 0;
+        for (size_t i = 1; i < this->log_likelihoods.size(); ++i)
+            if (this->log_likelihoods[best] < this->log_likelihoods[i]) best = i;
+        if (this->best_ever_log_likelihood < this->log_likelihoods[best]) {
+            fetch_host_particles(std::vector<size_t>(1, best));
+            this->best_ever_particle = this->particles[best];
+            this->best_ever_log_likelihood = this->log_likelihoods[best];
+        }
+    }
+    // the end-of-run state file holds every particle: the owners' lanes go to everybody, once
+    void gather_particles()
+    {
+        const int R = world();
+        const unsigned int T = this->num_threads, P = this->options.num_particles;
+        const size_t S = evaluator->state_doubles();
+        const unsigned int lanes_per_rank = T / R;
+        const size_t blob = S * P * lanes_per_rank;
+        std::vector<double> send(blob), recv(blob * (size_t)R);
+        const unsigned int my_lo = lane_lo();
+        pool->run((int)lane_lo(), (int)lane_hi(), [&](int a, int b) {
+            for (int k = a; k < b; ++k)
+                for (unsigned int q = 0; q < P; ++q)
+                    evaluator->pack(this->particles[(size_t)k * P + q], send.data() + ((size_t)(k - my_lo) * P + q) * S);
+        });
+        evaluator->allgather_bytes(send.data(), sizeof(double) * blob, recv.data());
+        for (int r = 0; r < R; ++r) {
+            if (r == rank()) continue;
+            const double* rd = recv.data() + blob * (size_t)r;
+            const unsigned int lo = (unsigned int)((unsigned long long)T * r / R);
+            pool->run(0, (int)lanes_per_rank, [&](int a, int b) {
+                for (int k = a; k < b; ++k)
+                    for (unsigned int q = 0; q < P; ++q)
+                        evaluator->unpack(this->particles[(size_t)(lo + k) * P + q], rd + ((size_t)k * P + q) * S);
+            });
+        }
     }
 
     // thread_steps lock-step MCMC steps of all lanes (mcmc_thread for every thread at once).
@@ -926,6 +1090,9 @@ public:
         const unsigned int T = this->num_threads;
         if (T % (unsigned int)world() != 0)
             throw std::invalid_argument("the number of lanes (-t) must be a multiple of the number of ranks");
+        // several ranks: every particle to everybody at every barrier (the first version), or only those the
+        // bookkeeping reads (bookkeeping_ranks)
+        const bool full_exchange = std::getenv("KIMA_FULL_EXCHANGE") != nullptr;
         while (true) {
             {
                 // each lane's own copy of the levels (SamplerImpl.h:283-284); only the lanes this
@@ -947,7 +1114,7 @@ public:
             const std::vector<Level> before = this->levels;
             if (world() > 1) {
                 const double te = now();
-                exchange(before);
+                exchange(before, full_exchange);
                 prof[6] += now() - te;
             } else {
                 for (const auto& lv : this->copies_of_levels)
@@ -963,9 +1130,11 @@ public:
                 }
             }
             const double tb = now();
-            this->do_bookkeeping();
+            if (world() > 1 && !full_exchange) bookkeeping_ranks();
+            else this->do_bookkeeping();
             prof[5] += now() - tb;
         }
+        if (world() > 1 && !full_exchange) gather_particles();
         if (std::getenv("KIMA_PROFILE"))
             std::cerr << "# run() " << now() - t_run0 << " s" << std::endl;
         if (std::getenv("KIMA_PROFILE"))
