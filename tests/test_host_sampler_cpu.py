@@ -124,7 +124,7 @@ def test_lanes_on_pool_threads_write_the_reference_chain(built, tmp_path):
     _same(bat, one, "1 thread against 4")
 
 
-def _run_ranks(exe, name, d, world, lanes, options, port, seed=43):
+def _run_ranks(exe, name, d, world, lanes, options, port, seed=43, extra_env=None):
     """`world` processes in ONE run directory, as a torchrun-style launcher starts the GPU ranks
     (RANK / WORLD_SIZE / MASTER_PORT); tests/cpp/RefEvaluator.h carries the collectives over TCP on 127.0.0.1."""
     d.mkdir()
@@ -134,6 +134,7 @@ def _run_ranks(exe, name, d, world, lanes, options, port, seed=43):
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_PORT=str(port), KIMA_HOST_THREADS="2")
+        env.update(extra_env or {})
         procs.append(subprocess.Popen([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.PIPE, text=True))
     outs = [p.communicate(timeout=600) for p in procs]
@@ -144,10 +145,10 @@ def _run_ranks(exe, name, d, world, lanes, options, port, seed=43):
 
 @pytest.mark.parametrize("name,world,port", [("BL2009", 2, 29621), ("BL2009", 4, 29622), ("CoRoT7", 2, 29623)])
 def test_ranks_write_the_single_process_chain(built, tmp_path, name, world, port):
-    """One process per rank, lanes sharded, BatchedSampler::exchange at every barrier (particles of the owners'
-    lanes, likelihoods, level assignments and rank 0's bookkeeping RNG to everybody; `above` lists concatenated in
-    lane order; level counters summed): `world` ranks write the files of one process with the same -t, which are
-    the reference sampler's.  The multi-GPU runs use exactly this code with NCCL underneath
+    """One process per rank, lanes sharded, BatchedSampler::exchange at every barrier (likelihoods, level
+    assignments and rank 0's bookkeeping RNG to everybody; `above` lists concatenated in lane order; level counters
+    summed), particles fetched from their owners where the bookkeeping reads one (bookkeeping_ranks): `world` ranks
+    write the files of one process with the same -t, which are the reference sampler's.  The multi-GPU runs use exactly this code with NCCL underneath
     (tests/test_host_cpp.py::test_two_ranks_reproduce_the_single_process_chain, on 2 GPUs)."""
     opts = "2\n50\n10\n5\n0\n1\n100\n300\n"   # lambda = 1: lagging particles get replaced early and often
     exe = os.path.join(built, "kima_batched_cpu_%s" % name)
@@ -157,6 +158,10 @@ def test_ranks_write_the_single_process_chain(built, tmp_path, name, world, port
     assert "Replacing lagging particle" in out0     # copies between lanes (and ranks) happened
     _same(ref, one, "reference against one process")
     _same(one, ranks, "%d ranks against one process" % world)
+    if name == "BL2009" and world == 2:
+        # the first version of the barrier (every particle to everybody, the inherited do_bookkeeping): same files
+        full, _ = _run_ranks(exe, name, tmp_path / "full", world, 8, opts, port + 50, extra_env={"KIMA_FULL_EXCHANGE": "1"})
+        _same(one, full, "2 ranks, full exchange")
 
 
 def test_the_reference_itself_is_not_reproducible_with_hyperpriors_on_several_cores(built, tmp_path):
