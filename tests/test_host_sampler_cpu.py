@@ -20,7 +20,8 @@ OBJ = os.path.join(ROOT, "oracle", "_ref", "obj")
 HOST_BUILD = os.path.join(ROOT, "host", "_build")
 OUT = os.path.join(ROOT, "tests", "cpp", "_build")
 E2E = os.path.join(ROOT, "tests", "golden", "e2e")
-DATA = {"BL2009": ["BL2009_dataset2.kms.rv"], "CoRoT7": ["corot7.txt"], "many_planets": ["HD10180.kms.rv"]}
+DATA = {"BL2009": ["BL2009_dataset2.kms.rv"], "CoRoT7": ["corot7.txt"], "many_planets": ["HD10180.kms.rv"],
+        "multi_instrument": ["HD106252_ELODIE.txt", "HD106252_HET.txt", "HD106252_HJS.txt", "HD106252_Lick.txt"]}
 FILES = ("sample.txt", "sample_info.txt", "levels.txt", "sampler_state.txt")
 CI_OPTIONS = "2\n50\n10\n5\n0\n10\n100\n100\n"   # the reference's CI options (tests/golden/e2e/OPTIONS)
 INC = ["-I" + os.path.join(REF, d) for d in ("src", "DNest4/code", "eigen", "celerite/cpp/include")]
@@ -57,7 +58,7 @@ def built():
                              "-I" + os.path.join(ROOT, "include")] + INC +
                             ["-o", os.path.join(OUT, "kima_batched_cpu_%s" % n),
                              os.path.join(REF, "examples", n, "kima_setup.cpp")] + _ref_objs())
-    with ThreadPoolExecutor(4) as ex:
+    with ThreadPoolExecutor(min(5, os.cpu_count() or 2)) as ex:
         list(ex.map(_compile, jobs))
     return OUT
 
@@ -143,7 +144,8 @@ def _run_ranks(exe, name, d, world, lanes, options, port, seed=43, extra_env=Non
     return d, outs[0][0]
 
 
-@pytest.mark.parametrize("name,world,port", [("BL2009", 2, 29621), ("BL2009", 4, 29622), ("CoRoT7", 2, 29623)])
+@pytest.mark.parametrize("name,world,port", [("BL2009", 2, 29621), ("BL2009", 4, 29622), ("CoRoT7", 2, 29623),
+                                             ("multi_instrument", 2, 29624)])
 def test_ranks_write_the_single_process_chain(built, tmp_path, name, world, port):
     """One process per rank, lanes sharded, BatchedSampler::exchange at every barrier (likelihoods, level
     assignments and rank 0's bookkeeping RNG to everybody; `above` lists concatenated in lane order; level counters
