@@ -49,6 +49,19 @@ def test_product_never_imports_oracle():
                     assert not re.search(pat, src), (f, pat)
 
 
+def test_product_host_build_uses_the_gpu_evaluator_only():
+    """host/overlay/kima.h lets a TEST name another Evaluator (tests/cpp/RefEvaluator.h: the reference's CPU
+    likelihood, to test the sampler without a GPU); the product build never does."""
+    mk = open(os.path.join(ROOT, "host", "Makefile")).read()
+    assert "KIMA_B200_EVALUATOR" not in mk and "tests/cpp" not in mk and "RefEvaluator" not in mk
+    for f in os.listdir(os.path.join(ROOT, "host")):
+        if f.endswith((".h", ".hpp", ".cpp")):
+            src = open(os.path.join(ROOT, "host", f)).read()
+            assert not re.search(r'#\s*include\s*"RefEvaluator.h"', src), f
+    overlay = open(os.path.join(ROOT, "host", "overlay", "kima.h")).read()
+    assert '#define KIMA_B200_EVALUATOR_HEADER "RVmodelDevice.h"' in overlay   # the default
+
+
 @pytest.mark.parametrize("flags,n_inst,n_ind", [
     (ModelFlags(), 1, 0), (ModelFlags(npmax=10, hyperpriors=True), 1, 0),
     (ModelFlags(GP=True, npmax=5), 1, 0), (ModelFlags(npmax=2, multi_instrument=True), 4, 0),
