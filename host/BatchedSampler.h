@@ -360,27 +360,21 @@ class BatchedSampler : public Sampler<ModelType> {
     void kill_lagging_ranks()
     {
         const size_t n = this->particles.size();
-        std::vector<bool> good(n, true);
-        double max_log_push = -std::numeric_limits<double>::max();
-        unsigned int num_bad = 0;
-        for (size_t i = 0; i < n; ++i) {
-            const double push = this->log_push(this->level_assignments[i]);
-            if (push > max_log_push) max_log_push = push;
-            const double kill_probability = pow(1.0 - 1.0 / (1.0 + exp(-push - 4.0)), 3);
-            if (this->rngs[0].rand() <= kill_probability) {
-                good[i] = false;
-                ++num_bad;
-            }
-        }
+        std::vector<bool> good;
+        std::vector<uint32_t> lagging;
+        double max_log_push = 0;
+        std::vector<double> push, kill;
+        level_push_and_kill(push, kill);
+        const unsigned int num_bad = flag_lagging(push, kill, good, lagging, max_log_push);
         if (num_bad >= n) return;
+        std::vector<double> keep(push.size());
+        for (size_t j = 0; j < push.size(); ++j) keep[j] = exp(push[j] - max_log_push);
         std::vector<size_t> dst, src;
-        for (size_t i = 0; i < n; ++i) {
-            if (good[i]) continue;
+        for (const uint32_t i : lagging) {
             int i_copy;
             do {
                 i_copy = this->rngs[0].rand_int((int)n);
-            } while (!good[i_copy] ||
-                     this->rngs[0].rand() >= exp(this->log_push(this->level_assignments[i_copy]) - max_log_push));
+            } while (!good[i_copy] || this->rngs[0].rand() >= keep[this->level_assignments[i_copy]]);
             dst.push_back(i);
             src.push_back((size_t)i_copy);
             this->log_likelihoods[i] = this->log_likelihoods[i_copy];
@@ -599,31 +593,25 @@ class BatchedSampler : public Sampler<ModelType> {
         return k;
     }
 
-    // kill_lagging_particles (SamplerImpl.h:534-587) with the copies done in HBM: same draws from
-    // rngs[0], same messages; a replacement taken from another rank's lane travels as one column
-    void kill_lagging_device()
+    // The first loop of kill_lagging_particles (SamplerImpl.h:543-558) for both proposal paths: which particles
+    // lag (good[], and their indices in particle order), and the largest log_push.  push / kill: log_push and the
+    // kill probability per LEVEL (they depend on the level alone: one evaluation per level instead of four per
+    // particle; same values, same draws from rngs[0] in the same order).  Returns the number of lagging particles.
+    unsigned int flag_lagging(const std::vector<double>& push, const std::vector<double>& kill, std::vector<bool>& good,
+                              std::vector<uint32_t>& lagging, double& max_log_push)
     {
         const size_t n = this->particles.size();
-        std::vector<bool> good(n, true);
-        std::vector<uint32_t> lagging;  // several ranks: the indices in particle order, so that nobody scans good[]
-        double max_log_push = -std::numeric_limits<double>::max();
+        good.assign(n, true);
+        lagging.clear();
+        max_log_push = -std::numeric_limits<double>::max();
         unsigned int num_bad = 0;
-        // log_push and the kill probability depend on the level alone: one evaluation per level instead of
-        // four per particle (log_push walks the level table through enough_levels each time); same values,
-        // same draws from rngs[0] in the same order (SamplerImpl.h:543-558)
-        const size_t L = this->levels.size();
-        std::vector<double> push(L), kill(L);
-        for (size_t j = 0; j < L; ++j) {
-            push[j] = this->log_push((unsigned int)j);
-            kill[j] = pow(1.0 - 1.0 / (1.0 + exp(-push[j] - 4.0)), 3);
-        }
         const int per_draw = world() > 1 ? engine_outputs_per_rand() : 0;
         if (per_draw > 0) {
-            // Several ranks: the first loop is one draw per particle in particle order (:543-558), i.e. a fixed
-            // number of engine outputs per particle, so each rank draws for the particles it owns and steps the
-            // (replicated) engine over the others' -- mt19937_64::discard skips the tempering and the
-            // conversion, a tenth of a draw.  Same good[] and the same engine state afterwards as the serial
-            // loop; with millions of particles that loop was most of the replicated bookkeeping.
+            // Several ranks: the loop is one draw per particle in particle order, i.e. a fixed number of engine
+            // outputs per particle, so each rank draws for the particles it owns and steps the (replicated)
+            // engine over the others' -- mt19937_64::discard skips the tempering and the conversion, a tenth of
+            // a draw.  Same good[] and the same engine state afterwards as the serial loop; with millions of
+            // particles that loop was most of the replicated bookkeeping.
             const size_t a = part_lo(), b = part_hi();
             auto& tw = this->rngs[0].twister;
             const auto check_engine = tw;  // KIMA_CHECK_SHARDED_KILL: the serial loop on a copy, below
@@ -678,18 +666,42 @@ class BatchedSampler : public Sampler<ModelType> {
                 if (push[lv] > max_log_push) max_log_push = push[lv];
                 if (this->rngs[0].rand() <= kill[lv]) {
                     good[i] = false;
+                    lagging.push_back((uint32_t)i);
                     ++num_bad;
                 }
             }
         }
+        return num_bad;
+    }
+    // log_push and the kill probability of every level (SamplerImpl.h:547-550)
+    void level_push_and_kill(std::vector<double>& push, std::vector<double>& kill) const
+    {
+        const size_t L = this->levels.size();
+        push.resize(L);
+        kill.resize(L);
+        for (size_t j = 0; j < L; ++j) {
+            push[j] = this->log_push((unsigned int)j);
+            kill[j] = pow(1.0 - 1.0 / (1.0 + exp(-push[j] - 4.0)), 3);
+        }
+    }
+
+    // kill_lagging_particles (SamplerImpl.h:534-587) with the copies done in HBM: same draws from
+    // rngs[0], same messages; a replacement taken from another rank's lane travels as one column
+    void kill_lagging_device()
+    {
+        const size_t n = this->particles.size();
+        std::vector<bool> good;
+        std::vector<uint32_t> lagging;  // the lagging particles in particle order
+        double max_log_push = 0;
+        std::vector<double> push, kill;
+        level_push_and_kill(push, kill);
+        const size_t L = push.size();
+        const unsigned int num_bad = flag_lagging(push, kill, good, lagging, max_log_push);
         if (num_bad >= n) return;
         std::vector<double> keep(L);
         for (size_t j = 0; j < L; ++j) keep[j] = exp(push[j] - max_log_push);
         std::vector<size_t> dst, src;
         std::ostringstream msg;
-        if (per_draw <= 0)
-            for (size_t i = 0; i < n; ++i)
-                if (!good[i]) lagging.push_back((uint32_t)i);
         for (const uint32_t i : lagging) {
             int i_copy;
             do {

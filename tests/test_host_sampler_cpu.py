@@ -134,7 +134,9 @@ def _run_ranks(exe, name, d, world, lanes, options, port, seed=43, extra_env=Non
     (d / "OPTIONS").write_text(options)
     procs = []
     for r in range(world):
-        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_PORT=str(port), KIMA_HOST_THREADS="2")
+        # KIMA_CHECK_SHARDED_KILL: every rank also runs the serial flagging loop on a copy of the engine and compares
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_PORT=str(port), KIMA_HOST_THREADS="2",
+                   KIMA_CHECK_SHARDED_KILL="1")
         env.update(extra_env or {})
         procs.append(subprocess.Popen([exe, "-t", str(lanes), "-s", str(seed)], cwd=d, env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.PIPE, text=True))
